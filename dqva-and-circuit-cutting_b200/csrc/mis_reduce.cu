@@ -1,0 +1,300 @@
+// K8: MIS objective reduction + candidate emission + top-k (HBM-bound).
+//
+// Replaces, per output bitstring, strip_ancillas (utils/helper_funcs.py:3-16), hamming_weight
+// (:18-19), is_indset (utils/graph_funcs.py:107-118) as summed by avg_cost (mis.py:125-126) and
+// filtered/sorted by top_probs (mis.py:232-233).
+//
+// Algorithmic bytes: sizeof(T) per output read once; nothing written but 3 doubles per CTA.
+#include "qdc_common.cuh"
+
+// ------------------------------------------------------------------------------------------
+// tables
+// ------------------------------------------------------------------------------------------
+struct BitTable {
+    int nbits;
+    int bitpos[64];
+    uint64_t adj[64];
+    uint64_t node_mask;
+};
+
+__global__ void mis_table_kernel(BitTable t, int bit_lo, long long count, uint64_t* __restrict__ xs,
+                                 uint64_t* __restrict__ forb, uint32_t* __restrict__ wok) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+         i += (long long)gridDim.x * blockDim.x) {
+        uint64_t x = 0;
+        for (int b = 0; b < t.nbits; ++b)
+            if ((i >> b) & 1) x |= 1ull << t.bitpos[bit_lo + b];
+        const uint64_t nodes = x & t.node_mask;
+        uint64_t f = 0;
+        uint64_t rem = nodes;
+        while (rem) {
+            const int a = __ffsll((long long)rem) - 1;
+            rem &= rem - 1;
+            f |= t.adj[a];
+        }
+        const uint32_t ok = (nodes & f) == 0ull ? 1u : 0u;
+        xs[i] = x;
+        if (forb) forb[i] = f & t.node_mask;
+        wok[i] = (uint32_t)__popcll((long long)nodes) | (ok << 8);
+    }
+}
+
+extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bitpos,
+                                    const uint64_t* h_adj, int n_wires, uint64_t node_mask,
+                                    uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
+                                    uint64_t* d_col_x, uint32_t* d_col_wok, void* stream) {
+    QDC_REQUIRE(row_bits >= 0 && col_bits >= 0 && row_bits + col_bits <= 62, "bit counts");
+    QDC_REQUIRE(n_wires >= 0 && n_wires <= 64, "n_wires");
+    QDC_REQUIRE(h_bitpos && h_adj, "null tables");
+    BitTable t;
+    for (int i = 0; i < 64; ++i) { t.bitpos[i] = 0; t.adj[i] = 0; }
+    uint64_t seen = 0;
+    for (int b = 0; b < row_bits + col_bits; ++b) {
+        QDC_REQUIRE(h_bitpos[b] >= 0 && h_bitpos[b] < 64, "bitpos range");
+        QDC_REQUIRE(!((seen >> h_bitpos[b]) & 1), "bitpos must be injective");
+        seen |= 1ull << h_bitpos[b];
+        t.bitpos[b] = h_bitpos[b];
+    }
+    for (int i = 0; i < n_wires; ++i) t.adj[i] = h_adj[i];
+    t.node_mask = node_mask;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int threads = 256;
+    {
+        const long long n = 1ll << col_bits;
+        t.nbits = col_bits;
+        int blocks = (int)((n + threads - 1) / threads);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        mis_table_kernel<<<blocks, threads, 0, s>>>(t, 0, n, d_col_x, nullptr, d_col_wok);
+        QDC_CHECK_LAUNCH();
+    }
+    {
+        const long long n = 1ll << row_bits;
+        t.nbits = row_bits;
+        int blocks = (int)((n + threads - 1) / threads);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        mis_table_kernel<<<blocks, threads, 0, s>>>(t, col_bits, n, d_row_x, d_row_forb, d_row_wok);
+        QDC_CHECK_LAUNCH();
+    }
+    return QDC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// reduction over a materialised slab
+// ------------------------------------------------------------------------------------------
+template <typename T> struct Vec;
+template <> struct Vec<double> { using type = double2; static constexpr int N = 2; };
+template <> struct Vec<float>  { using type = float4;  static constexpr int N = 4; };
+
+template <typename T>
+__device__ __forceinline__ typename Vec<T>::type ld_stream(const T* p);
+template <> __device__ __forceinline__ double2 ld_stream<double>(const double* p) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+template <> __device__ __forceinline__ float4 ld_stream<float>(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void unpack(const double2& v, double* o) { o[0] = v.x; o[1] = v.y; }
+__device__ __forceinline__ void unpack(const float4& v, double* o) {
+    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+}
+
+// One CTA walks whole 16-byte vectors; n_cols is a power of two >= Vec<T>::N so a vector never
+// straddles a row.  UNROLL independent 16-byte loads are issued before any is consumed.
+template <typename T, int UNROLL>
+__global__ void __launch_bounds__(256) mis_reduce_kernel(
+    const T* __restrict__ P, long long row_lo, long long n_rows, int col_shift,
+    const double* __restrict__ d_norm, MisTables tab, CandSink sink, double* __restrict__ partials) {
+    constexpr int VN = Vec<T>::N;
+    using V = typename Vec<T>::type;
+    __shared__ double scratch[3 * 8];
+    const double inv_norm = d_norm ? 1.0 / *d_norm : 1.0;
+    const long long n_vec = (n_rows << col_shift) / VN;
+    const long long col_mask = (1ll << col_shift) - 1;
+    MisAccum acc = {0.0, 0.0, 0.0};
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    for (; v0 < n_vec; v0 += stride * UNROLL) {
+        V vals[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const long long vi = v0 + u * stride;
+            if (vi < n_vec) vals[u] = ld_stream<T>(P + vi * VN);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const long long vi = v0 + u * stride;
+            if (vi >= n_vec) break;
+            const long long e = vi * VN;
+            const long long r = row_lo + (e >> col_shift);
+            const long long c = e & col_mask;
+            const uint64_t rx = __ldg(tab.row_x + r), rf = __ldg(tab.row_forb + r);
+            const uint32_t rw = __ldg(tab.row_wok + r);
+            double p[VN];
+            unpack(vals[u], p);
+#pragma unroll
+            for (int j = 0; j < VN; ++j)
+                mis_accumulate(acc, p[j] * inv_norm, rx, rf, rw, __ldg(tab.col_x + c + j),
+                               __ldg(tab.col_wok + c + j), sink);
+        }
+    }
+    mis_block_store(acc, scratch, partials);
+}
+
+// scalar fallback for tiny tables (n_cols < vector width)
+template <typename T>
+__global__ void __launch_bounds__(256) mis_reduce_small_kernel(
+    const T* __restrict__ P, long long row_lo, long long n_rows, int col_shift,
+    const double* __restrict__ d_norm, MisTables tab, CandSink sink, double* __restrict__ partials) {
+    __shared__ double scratch[3 * 8];
+    const double inv_norm = d_norm ? 1.0 / *d_norm : 1.0;
+    const long long n = n_rows << col_shift;
+    MisAccum acc = {0.0, 0.0, 0.0};
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n;
+         e += (long long)gridDim.x * blockDim.x) {
+        const long long r = row_lo + (e >> col_shift), c = e & ((1ll << col_shift) - 1);
+        mis_accumulate(acc, (double)P[e] * inv_norm, tab.row_x[r], tab.row_forb[r], tab.row_wok[r],
+                       tab.col_x[c], tab.col_wok[c], sink);
+    }
+    mis_block_store(acc, scratch, partials);
+}
+
+__global__ void finalize_sums_kernel(const double* __restrict__ partials, int n, double* sums) {
+    __shared__ double scratch[3 * 8];
+    double a = 0, b = 0, c = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        a += partials[3 * i]; b += partials[3 * i + 1]; c += partials[3 * i + 2];
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+    if (lane == 0) { scratch[warp] = a; scratch[8 + warp] = b; scratch[16 + warp] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double x = 0, y = 0, z = 0;
+        for (int w = 0; w < 8; ++w) { x += scratch[w]; y += scratch[8 + w]; z += scratch[16 + w]; }
+        sums[0] += x; sums[1] += y; sums[2] += z;
+    }
+}
+
+int qdc_launch_finalize_sums(const double* d_partials, int n_partials, double* d_sums,
+                             cudaStream_t stream) {
+    finalize_sums_kernel<<<1, 256, 0, stream>>>(d_partials, n_partials, d_sums);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+extern "C" int qdc_reduce_partials(void) { return QDC_MAX_PARTIALS; }
+
+extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_t n_rows,
+                              int64_t n_cols, const double* d_norm, double threshold,
+                              const uint64_t* d_row_x, const uint64_t* d_row_forb,
+                              const uint32_t* d_row_wok, const uint64_t* d_col_x,
+                              const uint32_t* d_col_wok, double* d_sums, uint64_t* d_cand_x,
+                              double* d_cand_p, unsigned long long* d_cand_count,
+                              int64_t cand_cap, double* d_partials, void* stream) {
+    QDC_REQUIRE(d_P && d_sums && d_partials, "null buffer");
+    QDC_REQUIRE(dtype == 0 || dtype == 1, "dtype");
+    QDC_REQUIRE(n_rows >= 0 && n_cols > 0 && (n_cols & (n_cols - 1)) == 0, "n_cols power of two");
+    QDC_REQUIRE(d_cand_x && d_cand_p && d_cand_count && cand_cap >= 0, "candidate sink");
+    if (n_rows == 0) return QDC_OK;
+    int col_shift = 0;
+    while ((1ll << col_shift) < n_cols) ++col_shift;
+    MisTables tab = {d_row_x, d_row_forb, d_row_wok, d_col_x, d_col_wok};
+    CandSink sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long total = n_rows * n_cols;
+    const int vn = dtype == 0 ? 2 : 4;
+    int blocks;
+    if (n_cols >= vn && (((uintptr_t)d_P) & 15) == 0) {
+        constexpr int UNROLL = 4;
+        const long long per_pass = 256ll * UNROLL * vn;
+        long long want = (total + per_pass - 1) / per_pass;
+        const long long cap = (long long)qdc_sm_count() * 8;      // 8 x 256 threads per SM
+        blocks = (int)(want < cap ? want : cap);
+        if (blocks < 1) blocks = 1;
+        if (dtype == 0)
+            mis_reduce_kernel<double, UNROLL><<<blocks, 256, 0, s>>>(
+                (const double*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+        else
+            mis_reduce_kernel<float, UNROLL><<<blocks, 256, 0, s>>>(
+                (const float*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+    } else {
+        blocks = (int)((total + 255) / 256);
+        if (blocks > 1024) blocks = 1024;
+        if (dtype == 0)
+            mis_reduce_small_kernel<double><<<blocks, 256, 0, s>>>(
+                (const double*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+        else
+            mis_reduce_small_kernel<float><<<blocks, 256, 0, s>>>(
+                (const float*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+    }
+    QDC_CHECK_LAUNCH();
+    return qdc_launch_finalize_sums(d_partials, blocks, d_sums, s);
+}
+
+// ------------------------------------------------------------------------------------------
+// top-k: k rounds of a single-CTA arg-max with (p desc, x asc) order
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool better(double p, uint64_t x, double q, uint64_t y) {
+    return p > q || (p == q && x < y);
+}
+
+__global__ void __launch_bounds__(1024) topk_kernel(const uint64_t* __restrict__ cx, double* cp,
+                                                    const unsigned long long* __restrict__ count,
+                                                    long long cap, int k, uint64_t* top_x,
+                                                    double* top_p) {
+    const long long n = (long long)*count < cap ? (long long)*count : cap;
+    __shared__ double sp[32];
+    __shared__ uint64_t sx[32];
+    __shared__ long long si[32];
+    const double NEG = -1.0 / 0.0;
+    for (int round = 0; round < k; ++round) {
+        double bp = NEG; uint64_t bx = ~0ull; long long bi = -1;
+        for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+            const double p = cp[i]; const uint64_t x = cx[i];
+            if (p != NEG && (bi < 0 || better(p, x, bp, bx))) { bp = p; bx = x; bi = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double q = __shfl_xor_sync(0xffffffffu, bp, o);
+            const uint64_t y = __shfl_xor_sync(0xffffffffu, bx, o);
+            const long long j = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (j >= 0 && (bi < 0 || better(q, y, bp, bx))) { bp = q; bx = y; bi = j; }
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) { sp[warp] = bp; sx[warp] = bx; si[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            bp = sp[lane]; bx = sx[lane]; bi = si[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double q = __shfl_xor_sync(0xffffffffu, bp, o);
+                const uint64_t y = __shfl_xor_sync(0xffffffffu, bx, o);
+                const long long j = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (j >= 0 && (bi < 0 || better(q, y, bp, bx))) { bp = q; bx = y; bi = j; }
+            }
+            if (lane == 0) {
+                if (bi >= 0) { top_x[round] = bx; top_p[round] = bp; cp[bi] = NEG; }
+                else { top_x[round] = ~0ull; top_p[round] = NEG; }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+extern "C" int qdc_topk_select(const uint64_t* d_cand_x, double* d_cand_p,
+                               const unsigned long long* d_cand_count, int64_t cand_cap, int k,
+                               uint64_t* d_top_x, double* d_top_p, void* stream) {
+    QDC_REQUIRE(k >= 1 && k <= 1024, "k");
+    QDC_REQUIRE(cand_cap >= 0 && d_top_x && d_top_p && d_cand_count, "buffers");
+    QDC_REQUIRE(d_cand_x && d_cand_p, "candidates");
+    topk_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(d_cand_x, d_cand_p, d_cand_count, cand_cap, k,
+                                                      d_top_x, d_top_p);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}

@@ -1,0 +1,220 @@
+"""Device pipeline for the 4^K contraction (K5) fused with MIS scoring / top-k (K8).
+
+Host-side orchestration only: torch owns the device buffers and the stream, every number is
+produced by the kernels in csrc/contract.cu and csrc/mis_reduce.cu through the C-ABI.
+
+Replaces `recombine_fragment_models` (qsplit/qsplit_mlrecon_methods.py:463-472) followed by
+`strip_ancillas` / `avg_cost` / `top_probs` (mis.py:114-134, 232-233) of the reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+
+__all__ = ["MisTables", "ScoreResult", "build_tables", "contract_and_score", "reduce_and_score",
+           "pad_kdim"]
+
+
+def _dev(device):
+    return torch.device(device if device is not None else "cuda")
+
+
+@dataclass
+class MisTables:
+    """Per-row / per-column scoring tables for a united index u = row * 2^col_bits + col."""
+    row_bits: int
+    col_bits: int
+    row_x: torch.Tensor
+    row_forb: torch.Tensor
+    row_wok: torch.Tensor
+    col_x: torch.Tensor
+    col_wok: torch.Tensor
+    bitpos: tuple
+    node_mask: int
+
+
+def build_tables(row_bits: int, col_bits: int, bitpos: Sequence[int], adj: Sequence[int],
+                 node_mask: int, device=None, stream=None) -> MisTables:
+    """bitpos[b] = full-circuit wire of united bit b (b < col_bits: column bits);
+    adj[i] = neighbour mask of wire i; node_mask = wires that are graph nodes."""
+    lib = _lib.load()
+    dev = _dev(device)
+    nb = row_bits + col_bits
+    assert len(bitpos) == nb
+    i64 = dict(dtype=torch.int64, device=dev)
+    row_x = torch.empty(1 << row_bits, **i64)
+    row_forb = torch.empty(1 << row_bits, **i64)
+    row_wok = torch.empty(1 << row_bits, dtype=torch.int32, device=dev)
+    col_x = torch.empty(1 << col_bits, **i64)
+    col_wok = torch.empty(1 << col_bits, dtype=torch.int32, device=dev)
+    h_bitpos = (C.c_int * max(nb, 1))(*[int(b) for b in bitpos])
+    n_wires = len(adj)
+    h_adj = (C.c_uint64 * max(n_wires, 1))(*[int(a) for a in adj])
+    with torch.cuda.device(dev):
+        _lib.check(lib.qdc_mis_build_tables(row_bits, col_bits, h_bitpos, h_adj, n_wires,
+                                            C.c_uint64(node_mask), _lib.ptr(row_x),
+                                            _lib.ptr(row_forb), _lib.ptr(row_wok),
+                                            _lib.ptr(col_x), _lib.ptr(col_wok),
+                                            _lib.stream_ptr(stream)), "qdc_mis_build_tables")
+    return MisTables(row_bits, col_bits, row_x, row_forb, row_wok, col_x, col_wok,
+                     tuple(int(b) for b in bitpos), int(node_mask))
+
+
+@dataclass
+class ScoreResult:
+    """Device-resident result of one scoring pass; `.get()` copies the few scalars to host."""
+    sums: torch.Tensor          # [sum p, sum p*w*indset, sum p*w]
+    top_x: torch.Tensor         # int64[k]  (circuit-order integer, -1 = none)
+    top_p: torch.Tensor         # float64[k]
+    cand_count: torch.Tensor    # int64[1]
+    cand_cap: int
+    P: Optional[torch.Tensor] = None
+    norm: Optional[torch.Tensor] = None
+
+    def get(self):
+        sums = self.sums.cpu().numpy()
+        n_cand = int(self.cand_count.item())
+        if n_cand > self.cand_cap:
+            raise _lib.QdcError(f"top-k candidate buffer overflow: {n_cand} entries above the "
+                                f"threshold, capacity {self.cand_cap}")
+        xs = self.top_x.cpu().numpy()
+        ps = self.top_p.cpu().numpy()
+        top = [(int(x), float(p)) for x, p in zip(xs, ps) if x != -1]
+        return {"sum_p": float(sums[0]), "sum_pw_indset": float(sums[1]),
+                "sum_pw": float(sums[2]), "top": top, "n_candidates": n_cand}
+
+
+def pad_kdim(t: torch.Tensor, multiple: int = 16) -> torch.Tensor:
+    """Zero-pad the contraction axis (last) of a [rows, kdim] operand to a multiple of 16."""
+    k = t.shape[-1]
+    if k % multiple == 0:
+        return t.contiguous()
+    out = torch.zeros(t.shape[0], (k + multiple - 1) // multiple * multiple, dtype=t.dtype,
+                      device=t.device)
+    out[:, :k] = t
+    return out
+
+
+class _Workspace:
+    """Scratch buffers reused across calls (per device)."""
+    _cache = {}
+
+    @classmethod
+    def get(cls, dev, kdim, cand_cap, k):
+        lib = _lib.load()
+        key = (str(dev), kdim, cand_cap, k)
+        ws = cls._cache.get(key)
+        if ws is None:
+            f64 = dict(dtype=torch.float64, device=dev)
+            ws = {
+                "partials": torch.empty(3 * lib.qdc_reduce_partials(), **f64),
+                "colsums": torch.empty(max(lib.qdc_norm_workspace_doubles(max(kdim, 1)), 1), **f64),
+                "cand_x": torch.empty(max(cand_cap, 1), dtype=torch.int64, device=dev),
+                "cand_p": torch.empty(max(cand_cap, 1), **f64),
+            }
+            cls._cache[key] = ws
+        return ws
+
+
+def _default_cap(total: int, threshold: float) -> int:
+    if threshold > 0:
+        bound = int(2.0 / threshold) + 1024
+    else:
+        bound = 1 << 22
+    return int(min(total, bound, 1 << 24))
+
+
+def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, scale: float = 1.0,
+                       threshold: float = 1e-5, k: int = 1, normalize: bool = True,
+                       row_lo: int = 0, n_rows: Optional[int] = None,
+                       store: Optional[str] = None, out_dtype=torch.float64,
+                       out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
+                       stream=None) -> ScoreResult:
+    """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
+
+    A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
+    store: None (never materialise), "united" (slab [n_rows, n_cols]) or "circuit"
+    (full-circuit order, length 2^(row_bits+col_bits), scatter).
+    """
+    lib = _lib.load()
+    dev = A.device
+    assert A.dtype == torch.float64 and Bt.dtype == torch.float64 and A.is_contiguous() \
+        and Bt.is_contiguous()
+    M, kdim = A.shape
+    N = Bt.shape[0]
+    assert Bt.shape[1] == kdim and M == 1 << tables.row_bits and N == 1 << tables.col_bits
+    if n_rows is None:
+        n_rows = M - row_lo
+    if cand_cap is None:
+        cand_cap = _default_cap(n_rows * N, threshold)
+    ws = _Workspace.get(dev, kdim, cand_cap, k)
+    f64 = dict(dtype=torch.float64, device=dev)
+    sums = torch.zeros(3, **f64)
+    cand_count = torch.zeros(1, dtype=torch.int64, device=dev)
+    top_x = torch.empty(k, dtype=torch.int64, device=dev)
+    top_p = torch.empty(k, **f64)
+    norm = torch.empty(1, **f64) if normalize else None
+    store_mode = {None: 0, "united": 1, "circuit": 2}[store]
+    odt = 0 if out_dtype == torch.float64 else 1
+    if store_mode and out is None:
+        if store_mode == 1:
+            out = torch.empty(n_rows, N, dtype=out_dtype, device=dev)
+        else:
+            out = torch.zeros(M * N, dtype=out_dtype, device=dev)
+    sp = _lib.stream_ptr(stream)
+    with torch.cuda.device(dev):
+        if normalize:
+            _lib.check(lib.qdc_contract_norm(_lib.ptr(A), M, _lib.ptr(Bt), N, kdim, scale,
+                                             _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
+                       "qdc_contract_norm")
+        _lib.check(lib.qdc_contract_f64(
+            _lib.ptr(A), _lib.ptr(Bt), row_lo, n_rows, N, kdim, scale, _lib.ptr(norm), threshold,
+            _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
+            _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), store_mode, odt,
+            _lib.ptr(sums), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
+            _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp), "qdc_contract_f64")
+        _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
+    return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
+
+
+def _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp):
+    # the candidate count stays on the device: no host sync between scoring and selection
+    _lib.check(lib.qdc_topk_select(_lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
+                                   _lib.ptr(cand_count), cand_cap, k,
+                                   _lib.ptr(top_x), _lib.ptr(top_p), sp), "qdc_topk_select")
+
+
+def reduce_and_score(P: torch.Tensor, tables: MisTables, threshold: float = 1e-5, k: int = 1,
+                     norm: Optional[torch.Tensor] = None, row_lo: int = 0,
+                     cand_cap: Optional[int] = None, stream=None) -> ScoreResult:
+    """Score a materialised slab P[n_rows, 2^col_bits] (united order; float64 or float32)."""
+    lib = _lib.load()
+    dev = P.device
+    assert P.is_contiguous() and P.dtype in (torch.float64, torch.float32)
+    N = 1 << tables.col_bits
+    P2 = P.reshape(-1, N)
+    n_rows = P2.shape[0]
+    if cand_cap is None:
+        cand_cap = _default_cap(n_rows * N, threshold)
+    ws = _Workspace.get(dev, 0, cand_cap, k)
+    f64 = dict(dtype=torch.float64, device=dev)
+    sums = torch.zeros(3, **f64)
+    cand_count = torch.zeros(1, dtype=torch.int64, device=dev)
+    top_x = torch.empty(k, dtype=torch.int64, device=dev)
+    top_p = torch.empty(k, **f64)
+    sp = _lib.stream_ptr(stream)
+    with torch.cuda.device(dev):
+        _lib.check(lib.qdc_mis_reduce(
+            _lib.ptr(P2), 0 if P.dtype == torch.float64 else 1, row_lo, n_rows, N,
+            _lib.ptr(norm), threshold, _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb),
+            _lib.ptr(tables.row_wok), _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok),
+            _lib.ptr(sums), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
+            _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp), "qdc_mis_reduce")
+        _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
+    return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, P, norm)

@@ -1,0 +1,128 @@
+"""GPU parity: K5 (DMMA contraction, fused MIS epilogue) and K8 (standalone reduction, top-k)
+against the numpy oracle (oracle/mis_oracle.py) on seeded inputs.  Tolerance: 1e-10 max-abs on
+probabilities and expectations (north_star FP64 bar); bit-exact on top-k indices and masks."""
+import networkx as nx
+import numpy as np
+import pytest
+import torch
+
+from oracle import mis_oracle as mo
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _problem(row_bits, col_bits, kdim, seed, n_anc=0, concentrate=False):
+    rng = np.random.default_rng(seed)
+    nb = row_bits + col_bits
+    A = rng.random((1 << row_bits, kdim)) - 0.3
+    Bt = rng.random((1 << col_bits, kdim)) - 0.3
+    if concentrate:
+        A[rng.integers(0, 1 << row_bits)] *= 50
+        Bt[rng.integers(0, 1 << col_bits)] *= 50
+    bitpos = [int(b) for b in rng.permutation(nb)]
+    n = nb - n_anc
+    if n >= 4 and n % 2 == 0:
+        G = nx.random_regular_graph(3, n, seed=int(seed))
+    else:
+        G = nx.path_graph(max(n, 1))
+    adj = [int(a) for a in mo.adjacency_masks(G, n)] + [0] * n_anc
+    node_mask = (1 << n) - 1
+    return A, Bt, bitpos, adj, node_mask, n, G
+
+
+def _oracle(A, Bt, bitpos, adj, n, n_anc, scale, threshold, k):
+    P = scale * (A @ Bt.T)                      # united [row, col]
+    u = np.arange(P.size, dtype=np.uint64)
+    x = np.zeros(P.size, dtype=np.uint64)
+    for b, pos in enumerate(bitpos):
+        x |= ((u >> np.uint64(b)) & np.uint64(1)) << np.uint64(pos)
+    full = np.zeros(P.size)
+    full[x.astype(np.int64)] = P.reshape(-1)
+    full /= full.sum()
+    adj_n = np.array(adj[:n], dtype=np.uint64)
+    s_p, s_pwok = mo.score_array(full, n, n_anc, adj_n, masked=True)
+    _, s_pw = mo.score_array(full, n, n_anc, adj_n, masked=False)
+    idx = np.nonzero(full > threshold)[0]
+    order = np.lexsort((idx, -full[idx]))[:k]
+    top = [(int(idx[i]), float(full[idx[i]])) for i in order]
+    return full, s_p, s_pwok, s_pw, top
+
+
+@pytest.mark.parametrize("row_bits,col_bits,kdim,n_anc,store", [
+    (3, 4, 16, 0, "circuit"), (7, 7, 64, 0, "circuit"), (8, 9, 256, 2, "united"),
+    (1, 1, 16, 0, "circuit"), (0, 5, 16, 0, None), (9, 8, 256, 0, None), (10, 3, 16, 1, "circuit"),
+    (5, 0, 16, 0, "circuit"),
+])
+def test_contract_and_score_matches_oracle(cuda, row_bits, col_bits, kdim, n_anc, store):
+    from qdc_b200 import recombine as rc
+    A, Bt, bitpos, adj, node_mask, n, G = _problem(row_bits, col_bits, kdim, 7 + row_bits, n_anc)
+    scale, thr, k = 0.5 ** 3, 1e-5, 5
+    full, s_p, s_pwok, s_pw, top = _oracle(A, Bt, bitpos, adj, n, n_anc, scale, thr, k)
+    tabs = rc.build_tables(row_bits, col_bits, bitpos, adj, node_mask, device=cuda)
+    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(Bt).to(cuda)
+    res = rc.contract_and_score(dA, dB, tabs, scale=scale, threshold=thr, k=k, store=store)
+    out = res.get()
+    assert abs(out["sum_p"] - s_p) < TOL
+    assert abs(out["sum_pw_indset"] - s_pwok) < TOL * 10
+    assert abs(out["sum_pw"] - s_pw) < TOL * 10
+    assert [x for x, _ in out["top"]] == [x for x, _ in top]
+    assert np.allclose([p for _, p in out["top"]], [p for _, p in top], atol=TOL, rtol=0)
+    if store == "circuit":
+        assert np.abs(res.P.cpu().numpy() - full).max() < TOL
+    elif store == "united":
+        P = scale * (A @ Bt.T)
+        P /= P.sum()
+        assert np.abs(res.P.cpu().numpy() - P).max() < TOL
+
+
+def test_row_sharding_adds_up(cuda):
+    """Prefix sharding: per-slab sums add to the whole; top-k merges."""
+    from qdc_b200 import recombine as rc
+    A, Bt, bitpos, adj, node_mask, n, G = _problem(9, 8, 64, 3)
+    tabs = rc.build_tables(9, 8, bitpos, adj, node_mask, device=cuda)
+    dA, dB = torch.from_numpy(A).to(cuda), torch.from_numpy(Bt).to(cuda)
+    whole = rc.contract_and_score(dA, dB, tabs, k=4).get()
+    parts = [rc.contract_and_score(dA, dB, tabs, k=4, row_lo=lo, n_rows=128).get()
+             for lo in range(0, 512, 128)]
+    for key in ("sum_p", "sum_pw_indset", "sum_pw"):
+        assert abs(sum(p[key] for p in parts) - whole[key]) < 1e-12
+    merged = sorted((t for p in parts for t in p["top"]), key=lambda t: (-t[1], t[0]))[:4]
+    assert [x for x, _ in merged] == [x for x, _ in whole["top"]]
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("row_bits,col_bits", [(6, 6), (0, 1), (11, 10), (3, 0)])
+def test_reduce_matches_oracle(cuda, dtype, row_bits, col_bits):
+    from qdc_b200 import recombine as rc
+    A, Bt, bitpos, adj, node_mask, n, G = _problem(row_bits, col_bits, 16, 11, concentrate=True)
+    nb = row_bits + col_bits
+    full, *_ = _oracle(A, Bt, list(range(nb)), adj, n, 0, 1.0, 1e-5, 3)
+    tabs = rc.build_tables(row_bits, col_bits, list(range(nb)), adj, node_mask, device=cuda)
+    P = torch.from_numpy(full).to(cuda).to(dtype)
+    ref = P.double().cpu().numpy()
+    s_p, s_pwok = mo.score_array(ref, n, 0, np.array(adj, dtype=np.uint64), masked=True)
+    out = rc.reduce_and_score(P, tabs, threshold=1e-5, k=3).get()
+    assert abs(out["sum_p"] - s_p) < TOL and abs(out["sum_pw_indset"] - s_pwok) < TOL * 10
+    idx = np.nonzero(ref > 1e-5)[0]
+    order = np.lexsort((idx, -ref[idx]))[:3]
+    assert [x for x, _ in out["top"]] == [int(idx[i]) for i in order]
+
+
+def test_indset_mask_against_python_is_indset(cuda):
+    """Bit-exact: the table-driven mask/weight equal the reference's string algorithms
+    (utils/graph_funcs.py:107-118, utils/helper_funcs.py:18-19) for every 12-bit string."""
+    from qdc_b200 import recombine as rc
+    n = 12
+    G = nx.random_regular_graph(3, n, seed=5)
+    adj = [int(a) for a in mo.adjacency_masks(G, n)]
+    tabs = rc.build_tables(7, 5, list(range(n)), adj, (1 << n) - 1, device=cuda)
+    rx = tabs.row_x.cpu().numpy(); rf = tabs.row_forb.cpu().numpy()
+    rw = tabs.row_wok.cpu().numpy(); cx = tabs.col_x.cpu().numpy(); cw = tabs.col_wok.cpu().numpy()
+    for u in range(1 << n):
+        r, c = u >> 5, u & 31
+        ok = bool((rw[r] >> 8) & (cw[c] >> 8) & 1) and (int(cx[c]) & int(rf[r])) == 0
+        w = (rw[r] & 255) + (cw[c] & 255)
+        s = format(u, f"0{n}b")
+        assert ok == mo.is_indset(s, G) and w == mo.hamming_weight(s)
+        assert int(rx[r]) | int(cx[c]) == u
