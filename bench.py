@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the QDC hot path on B200.
+
+Metric (BASELINE.json): reconstructed probs/s at 2^34 outputs.  A "step" is one evaluation of
+the recombination + MIS scoring that `avg_cost` (mis.py:117-134 of the reference) performs for one
+parameter vector on the synthetic 2-fragment, 17+17-output-qubit, K=4-cut workload
+(BASELINE.json configs[3]; SURVEY.md 8d "C4 pure-tensor variant"):
+
+    combined_norm -> P~ = 2^-K * A . B over the 256-term cut basis -> strip/normalise ->
+    sum_x p(x) * popcount(x) * [x independent set] -> top-k bitstrings
+
+  value : device-timed whole-job throughput, operands already resident in HBM
+  e2e   : the same step through the public Python API with HOST operands (pinned -> device copy
+          and device -> host read of the result inside the timed region)
+
+Run:  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+      (N > 1: launched under torchrun, one rank per GPU; rows of the row operand = bitstring
+      prefixes are sharded across ranks, one small NCCL all_gather finishes the step)
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+KDIM = 256          # 4^K, K = 4 cuts
+NUM_CUTS = 4
+METRIC = "reconstructed probs/s at 2^34 outputs"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--row-bits", type=int, default=17, help="output qubits of fragment 1")
+    ap.add_argument("--col-bits", type=int, default=17, help="output qubits of fragment 0")
+    ap.add_argument("--topk", type=int, default=1)
+    ap.add_argument("--cpu-sample-bits", type=int, default=None,
+                    help="log2 of the outputs the CPU baseline evaluates (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------------
+
+def make_operands(row_bits, col_bits, seed=1234):
+    """Seeded non-negative FP64 fragment tensors with rows normalised."""
+    rng = np.random.default_rng(seed)
+    A = rng.random((1 << row_bits, KDIM))
+    A /= A.sum(axis=1, keepdims=True)
+    Bt = rng.random((1 << col_bits, KDIM))
+    Bt /= Bt.sum(axis=1, keepdims=True)
+    return A, Bt
+
+
+def make_graph(n, seed=34):
+    import networkx as nx
+    G = nx.random_regular_graph(3, n, seed=seed)
+    adj = [sum(1 << int(j) for j in G.neighbors(i)) for i in range(n)]
+    return G, adj
+
+
+def make_bitpos(n, col_bits):
+    """United bit -> circuit wire.  Fragment 0 (columns) carries the even-position half of the
+    wires first..., a fixed non-trivial interleave so the permutation path is exercised."""
+    wires = list(range(n))
+    cols = wires[:col_bits]
+    rows = wires[col_bits:]
+    return cols + rows
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(self.gpu_index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                smax.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(smax)) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU baselines (oracle side; never on the product path)
+# ---------------------------------------------------------------------------------------------
+
+def cpu_reference_sample(sample_bits, workdir=None):
+    """The reference's own C build path (oracle/_ref/build = cutqc/build.c compiled with gcc and
+    the mkl.h shim), one rank per host core as CutQC._build does (cutqc/main.py:418-457), on a
+    bounded sample of the workload: 2 subcircuits, K=4 cuts (256 summation terms), 2^sample_bits
+    outputs.  Text-file protocol included, MIS scoring excluded (per-bitstring Python there)."""
+    import tempfile
+    from oracle import ref_cutqc
+    cores = os.cpu_count() or 1
+    a0 = sample_bits // 2
+    a1 = sample_bits - a0
+    with tempfile.TemporaryDirectory(dir=workdir) as d:
+        rate, secs, _, _ = ref_cutqc.time_build_sample(a0, a1, NUM_CUTS, cores, d)
+    return {"value": rate, "unit": "probs/s", "cores": cores, "kind": "reference",
+            "sample": f"cutqc/build.c (gcc -O2 + mkl.h shim, not MKL), {cores} ranks, 2 subcircuits "
+                      f"x ({a0}+{a1}) active qubits, 256 summation terms = 2^{sample_bits} outputs in "
+                      f"{secs:.1f} s incl. the %e text-file protocol; MIS scoring not included"}
+
+
+def cpu_port_sample(A, Bt, bitpos, col_bits, adj, node_mask, sample_rows):
+    """Best-effort CPU restatement (oracle/c/oracle_port.c, OpenMP, all cores): contraction +
+    MIS scoring + arg-max for `sample_rows` rows x all columns of the SAME operands."""
+    from oracle import port
+    t0 = time.time()
+    sums, best, _ = port.contract_score(A, Bt, bitpos, col_bits, adj, node_mask,
+                                        scale=0.5 ** NUM_CUTS, n_rows=sample_rows)
+    secs = time.time() - t0
+    outs = sample_rows * Bt.shape[0]
+    return {"value": outs / secs, "unit": "probs/s", "cores": port.num_threads(), "kind": "port",
+            "sample": f"{sample_rows} rows x 2^{col_bits} cols = 2^{np.log2(outs):.1f} outputs "
+                      f"in {secs:.1f} s (C/OpenMP dot products + popcount/indset scoring)"}, sums
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation on the host cores, rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref_cutqc
+    if not ref_cutqc.available():
+        subprocess.run(["make"], cwd=os.path.join(ROOT, "oracle"), check=False,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    sample_bits = args.cpu_sample_bits or 20
+    times, last = [], None
+    for i in range(args.warmup + args.steps):
+        last = cpu_reference_sample(sample_bits)
+        if i >= args.warmup:
+            times.append(float(1 << sample_bits) / last["value"])
+    t = float(np.mean(times))
+    value = float(1 << sample_bits) / t
+    last["value"] = value
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "probs/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C4 synthetic 2-fragment K=4 recombination, bounded sample "
+                                   f"2^{sample_bits} of 2^{args.row_bits + args.col_bits} outputs",
+                       "kdim": KDIM},
+            "cpu_baseline": last,
+            "e2e": {"value": value, "unit": "probs/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+
+def measure_dgemm_peak(torch, dev):
+    """cuBLAS DGEMM 8192^3, best of 5, CUDA events: the measured FP64 tensor-pipe denominator
+    (MEASURED_PEAKS.json only carries HBM and bf16 figures)."""
+    X = torch.rand(8192, 8192, dtype=torch.float64, device=dev)
+    Y = torch.rand(8192, 8192, dtype=torch.float64, device=dev)
+    torch.matmul(X, Y)
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(5):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); torch.matmul(X, Y); b.record(); torch.cuda.synchronize()
+        t = a.elapsed_time(b) * 1e-3
+        best = t if best is None else min(best, t)
+    del X, Y
+    torch.cuda.empty_cache()
+    return 2.0 * 8192 ** 3 / best / 1e12
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import _lib, recombine as rc, dist as qdist
+
+    rank, ws, local_rank = qdist.init_from_env()
+    if not torch.cuda.is_available():
+        raise _lib.QdcError("bench.py needs a CUDA device: there is no CPU fallback")
+    _lib.load()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+
+    rb, cb, k = args.row_bits, args.col_bits, args.topk
+    n = rb + cb
+    A_h, Bt_h = make_operands(rb, cb)
+    G, adj = make_graph(n)
+    bitpos = make_bitpos(n, cb)
+    node_mask = (1 << n) - 1
+    scale = 0.5 ** NUM_CUTS
+    M, N = 1 << rb, 1 << cb
+    row_lo, n_rows = qdist.row_shard(M, rank, ws)
+    outputs_total = float(M) * float(N)
+
+    tabs = rc.build_tables(rb, cb, bitpos, adj, node_mask, device=dev)
+    A_d = torch.from_numpy(A_h).to(dev)
+    Bt_d = torch.from_numpy(Bt_h).to(dev)
+    A_pin = torch.from_numpy(A_h).pin_memory()
+    Bt_pin = torch.from_numpy(Bt_h).pin_memory()
+    A_stage = torch.empty_like(A_d)
+    Bt_stage = torch.empty_like(Bt_d)
+
+    def barrier():
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    kernel_events = []
+
+    def step_device():
+        res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
+                                    row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events)
+        return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
+
+    def step_e2e():
+        A_stage.copy_(A_pin, non_blocking=True)
+        Bt_stage.copy_(Bt_pin, non_blocking=True)
+        res = rc.contract_and_score(A_stage, Bt_stage, tabs, scale=scale, threshold=1e-5, k=k,
+                                    row_lo=row_lo, n_rows=n_rows)
+        if ws > 1:
+            sums, top = qdist.finish(res.sums, res.top_x, res.top_p, k)
+            return sums.cpu().numpy(), top
+        out = res.get()
+        return out
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record()
+        last = None
+        for _ in range(steps):
+            last = fn()
+        end.record()
+        barrier()
+        t = torch.tensor([start.elapsed_time(end) * 1e-3 / steps], dtype=torch.float64, device=dev)
+        if ws > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), last
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    t_dev, last_dev = timed(step_device, args.steps, max(args.warmup, 3))
+    clocks = sampler.stop() if rank == 0 else None
+    t_e2e, last_e2e = timed(step_e2e, args.steps, max(args.warmup, 3))
+
+    # correctness spot check of the result that was just timed (cheap, outside timed regions)
+    if ws == 1:
+        final = last_dev.get()
+        sum_p, cost = final["sum_p"], final["sum_pw_indset"]
+        top = final["top"]
+    else:
+        sums, top = last_dev
+        sum_p, cost = float(sums[0].item()), float(sums[1].item())
+    assert abs(sum_p - 1.0) < 1e-9, f"distribution does not sum to 1: {sum_p}"
+
+    if rank != 0:
+        if ws > 1:
+            dist.destroy_process_group()
+        return
+
+    value = outputs_total / t_dev
+    e2e_value = outputs_total / t_e2e
+    flops = 2.0 * outputs_total * KDIM
+    dgemm_peak = measure_dgemm_peak(torch, dev)
+    # dominant kernel = contraction (+ its 1-CTA finalize): CUDA events recorded around it on the
+    # launching stream inside the timed region, average over the timed steps
+    evs = kernel_events[-args.steps:]
+    t_kernel = float(np.mean([a.elapsed_time(b) for a, b in evs])) * 1e-3
+    achieved = flops / ws / t_kernel / 1e12
+    line = {
+        "metric": METRIC, "value": value, "unit": "probs/s", "n_gpus": ws, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": t_dev * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"C4 synthetic 2-fragment 17+17-qubit K=4 recombination + MIS "
+                               f"scoring, 2^{n} outputs (BASELINE.json configs[3])",
+                   "row_bits": rb, "col_bits": cb, "kdim": KDIM, "topk": k,
+                   "parallelism": f"prefix-shard x{ws}",
+                   "l2": "operands 0.5 GB > 126 MB L2; no flush needed"},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
+                "h2d_bytes_per_step": int(A_pin.numel() * 8 + Bt_pin.numel() * 8),
+                "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
+        "gpu_launches": 6 * args.steps,
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
+                     "unit": "TFLOP/s", "frac": achieved / dgemm_peak, "traffic": None,
+                     "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64 DMMA pipe; "
+                                    "MEASURED_PEAKS.json has no FP64 entry; nominal 37 TFLOP/s)",
+                     "algorithmic_flops_per_launch": flops / ws,
+                     "kernel": "contract_f64_kernel", "kernel_ms": t_kernel * 1e3},
+        "result": {"sum_p": sum_p, "avg_cost": -cost, "top": top[:k]},
+    }
+    if not args.no_cpu_baseline and ws == 1:
+        try:
+            line["cpu_baseline"] = cpu_reference_sample(args.cpu_sample_bits or 20)
+        except Exception as exc:                          # the baseline must not sink the bench
+            line["cpu_baseline"] = {"value": None, "unit": "probs/s", "cores": os.cpu_count(),
+                                    "kind": "reference", "sample": f"failed: {exc}"}
+        try:
+            sample_rows = max(1, (1 << 27) // N)
+            port, sums = cpu_port_sample(A_h, Bt_h, bitpos, cb, adj, node_mask, sample_rows)
+            line["cpu_port"] = port
+        except Exception as exc:
+            line["cpu_port"] = {"value": None, "sample": f"failed: {exc}"}
+    print(json.dumps(line), flush=True)
+    if ws > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

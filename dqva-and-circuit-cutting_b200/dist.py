@@ -1,0 +1,84 @@
+"""Multi-GPU plumbing for the QDC hot path: one process per GPU, `torch.distributed`.
+
+The path shards without any bulk exchange: fragment variants x parameter sets
+are independent, and the reconstructed distribution is partitioned by bitstring prefix (rows of
+the row operand).  The only collective is the finish: every rank contributes three partial sums
+and its local top-k; one small all_gather makes the global scalars and global top-k available on
+every rank.  NCCL on GPUs, gloo in the CPU tests.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "merge_topk"]
+
+
+def init_from_env(backend: str | None = None) -> Tuple[int, int, int]:
+    """Initialise the default process group from RANK/WORLD_SIZE/MASTER_* (torchrun) if
+    WORLD_SIZE > 1.  Returns (rank, world_size, local_rank)."""
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world_size > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kwargs = {}
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+            kwargs["device_id"] = torch.device("cuda", local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world_size, **kwargs)
+    return rank, world_size, local_rank
+
+
+def world() -> Tuple[int, int]:
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def row_shard(n_rows: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Contiguous prefix slab [lo, lo + count) of the row operand owned by `rank`.
+    Rows are the most significant united bits, so a slab is a set of bitstring prefixes."""
+    base, rem = divmod(n_rows, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, base + (1 if rank < rem else 0)
+
+
+def round_robin(n_items: int, rank: int, world_size: int) -> List[int]:
+    """Indices of the (fragment variant x parameter set) work items owned by `rank`."""
+    return list(range(rank, n_items, world_size))
+
+
+def merge_topk(cands: Sequence[Tuple[int, float]], k: int) -> List[Tuple[int, float]]:
+    """Global top-k with the library's order: probability descending, then index ascending."""
+    return sorted(cands, key=lambda t: (-t[1], t[0]))[:k]
+
+
+def finish(sums: torch.Tensor, top_x: torch.Tensor, top_p: torch.Tensor, k: int):
+    """All-gather [3 sums | k probs | k indices] from every rank; returns
+    (global sums tensor[3], global top-k list) on every rank.  With world_size 1 this is a
+    local repack and no collective is issued."""
+    rank, ws = world()
+    if ws == 1:
+        xs, ps = top_x.cpu().tolist(), top_p.cpu().tolist()
+        return sums.clone(), merge_topk([(x, p) for x, p in zip(xs, ps) if x != -1], k)
+    # float64 carries 2^53 exactly, enough for indices of up to 53 bits
+    packed = torch.cat([sums.to(torch.float64), top_p.to(torch.float64),
+                        top_x.to(torch.float64)])
+    gathered = torch.empty(ws * packed.numel(), dtype=torch.float64, device=packed.device)
+    dist.all_gather_into_tensor(gathered, packed)
+    g = gathered.view(ws, -1)
+    total = g[:, :3].sum(dim=0)
+    host = g.cpu()
+    cands = []
+    for r in range(ws):
+        ps = host[r, 3:3 + k].tolist()
+        xs = host[r, 3 + k:3 + 2 * k].tolist()
+        cands += [(int(x), p) for x, p in zip(xs, ps) if x >= 0]
+    return total, merge_topk(cands, k)

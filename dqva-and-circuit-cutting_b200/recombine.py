@@ -135,12 +135,14 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                        row_lo: int = 0, n_rows: Optional[int] = None,
                        store: Optional[str] = None, out_dtype=torch.float64,
                        out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
-                       stream=None) -> ScoreResult:
+                       stream=None, kernel_events: Optional[list] = None) -> ScoreResult:
     """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
 
     A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
     store: None (never materialise), "united" (slab [n_rows, n_cols]) or "circuit"
     (full-circuit order, length 2^(row_bits+col_bits), scatter).
+    kernel_events: if a list, a (start, end) CUDA event pair bracketing the contraction kernel
+    alone (recorded on the launching stream) is appended to it.
     """
     lib = _lib.load()
     dev = A.device
@@ -173,12 +175,19 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             _lib.check(lib.qdc_contract_norm(_lib.ptr(A), M, _lib.ptr(Bt), N, kdim, scale,
                                              _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
                        "qdc_contract_norm")
+        if kernel_events is not None:
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev0.record(stream)
         _lib.check(lib.qdc_contract_f64(
             _lib.ptr(A), _lib.ptr(Bt), row_lo, n_rows, N, kdim, scale, _lib.ptr(norm), threshold,
             _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
             _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), store_mode, odt,
             _lib.ptr(sums), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
             _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp), "qdc_contract_f64")
+        if kernel_events is not None:
+            ev1.record(stream)
+            kernel_events.append((ev0, ev1))
         _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
     return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
 

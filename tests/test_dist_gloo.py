@@ -1,0 +1,55 @@
+"""world_size-2 gloo test of the multi-GPU finish (the only collective on the path) and of the
+prefix / round-robin sharding helpers."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from qdc_b200 import dist as qdist
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, ws, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
+    import importlib, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import dist as qd
+    r, w, _ = qd.init_from_env(backend="gloo")
+    k = 3
+    sums = torch.tensor([0.25 * (rank + 1), 1.0 * rank, 2.0], dtype=torch.float64)
+    top_x = torch.tensor([10 + rank, 20 + rank, -1], dtype=torch.int64)
+    top_p = torch.tensor([0.5 - 0.1 * rank, 0.3, float("-inf")], dtype=torch.float64)
+    total, top = qd.finish(sums, top_x, top_p, k)
+    out[rank] = (total.tolist(), top)
+    dist.destroy_process_group()
+
+
+def test_finish_world_size_2():
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    for rank in range(ws):
+        total, top = out[rank]
+        assert total == [0.75, 1.0, 4.0]
+        assert top == [(10, 0.5), (11, 0.4), (20, 0.3)]
+
+
+def test_sharding_helpers():
+    for n, ws in [(1 << 17, 8), (10, 4), (3, 8), (7, 1)]:
+        slabs = [qdist.row_shard(n, r, ws) for r in range(ws)]
+        assert slabs[0][0] == 0 and sum(c for _, c in slabs) == n
+        for (lo, c), (lo2, _) in zip(slabs, slabs[1:]):
+            assert lo + c == lo2
+    items = sorted(i for r in range(3) for i in qdist.round_robin(10, r, 3))
+    assert items == list(range(10))
+    assert qdist.merge_topk([(5, 0.2), (3, 0.2), (9, 0.7)], 2) == [(9, 0.7), (3, 0.2)]

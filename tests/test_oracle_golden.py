@@ -1,0 +1,164 @@
+"""Pins the CPU oracle (the checker used by every GPU parity test) against the reference's own
+known answers:
+
+  * test_cutting.py:7-40 of the reference: 3-qubit H/CX/CX circuit cut on q1 after the first
+    CNOT -> recombined distribution {000: 0.5, 111: 0.5};
+  * benchmark_graphs/brute_force_outputs/*/G*_brute_force.out: optimal MIS size and strings;
+  * the invariant every reference scenario reduces to: recombined == uncut statevector
+    distribution (qsplit_dqva_demo.py:94-121 checks it statistically; here exactly).
+"""
+import glob
+import os
+import random
+import re
+
+import networkx as nx
+import numpy as np
+import pytest
+
+from oracle import mis_oracle as mo
+from oracle import qsplit_oracle as qo
+from oracle import statevector as sv
+from qdc_b200.ansatz import dqv_cut_ansatz
+from qdc_b200.circuit import QuantumCircuit
+from qdc_b200.qsplit import qsplit_circuit_cutter as qcc
+from qdc_b200.utils import graph_funcs, helper_funcs
+from qdc_b200.utils.cutting_funcs import simple_choose_nodes
+
+
+def _ghz3():
+    circ = QuantumCircuit(3, name='q')
+    circ.h(0)
+    circ.cx(0, 1)
+    circ.cx(1, 2)
+    return circ, [(circ.qubits[1], 1)]
+
+
+@pytest.mark.parametrize("mode", ["direct", "likely"])
+@pytest.mark.parametrize("method", ["network", "insertion"])
+def test_reference_test_cutting_known_answer(mode, method):
+    circ, cuts = _ghz3()
+    frags, wpm = qcc.cut_circuit(circ, cuts)
+    assert qo.fragment_variants(wpm) == 7            # 3 (meas side) + 4 (prep side)
+    data = qo.collect_fragment_data(frags, wpm)
+    models = qo.direct_fragment_model(data)
+    if mode == "likely":
+        models = qo.maximum_likelihood_model(models)
+    dist = qo.recombine_fragment_models(models, wpm, method=method)
+    assert abs(dist["000"] - 0.5) < 1e-12 and abs(dist["111"] - 0.5) < 1e-12
+    assert all(abs(v) < 1e-12 for k, v in dist.items() if k not in ("000", "111"))
+
+
+def _golden_cases(golden_dir):
+    for out in sorted(glob.glob(os.path.join(golden_dir, "brute_force", "*_brute_force.out"))):
+        name = os.path.basename(out)[:-len("_brute_force.out")]
+        yield name, out, os.path.join(golden_dir, "graphs", name + ".txt")
+
+
+def _parse_brute_force(path):
+    with open(path) as f:
+        lines = f.read().strip().split("\n")
+    size = int(re.search(r"Optimal MIS is (\d+)", lines[1]).group(1))
+    strs = [ln.strip().split(",")[0] for ln in lines[3:]]
+    return size, strs
+
+
+def test_brute_force_golden_files(golden_dir):
+    cases = list(_golden_cases(golden_dir))
+    assert len(cases) >= 8
+    for name, out, gfile in cases:
+        size, strs = _parse_brute_force(out)
+        G = graph_funcs.graph_from_file(gfile)
+        n = G.number_of_nodes()
+        adj = mo.adjacency_masks(G, n)
+        for s in strs:
+            assert len(s) == n
+            # string algorithms (oracle restatement and product host helper)
+            assert mo.is_indset(s, G) and graph_funcs.is_indset(s, G)
+            assert mo.hamming_weight(s) == size == helper_funcs.hamming_weight(s)
+            # integer/mask form used on the device
+            x = np.array([int(s, 2)], dtype=np.uint64)
+            assert bool(mo.indset_mask(x, adj)[0]) and int(mo.popcount64(x)[0]) == size
+        if n <= 16:
+            # exhaustive: the optimum and the full optimal set are reproduced
+            xs = np.arange(1 << n, dtype=np.uint64)
+            ok = mo.indset_mask(xs, adj)
+            w = mo.popcount64(xs)
+            best = int(w[ok].max())
+            assert best == size
+            found = sorted(format(int(x), f"0{n}b") for x in xs[ok & (w == best)])
+            assert found == sorted(strs)
+
+
+def test_brute_force_search_small(golden_dir):
+    name, out, gfile = next(c for c in _golden_cases(golden_dir) if c[0].startswith("N8_"))
+    size, strs = _parse_brute_force(out)
+    G = graph_funcs.graph_from_file(gfile)
+    got_strs, got = mo.brute_force_search_memory_efficient(G)
+    assert got == size and sorted(got_strs) == sorted(strs)
+    got_strs2, got2 = helper_funcs.brute_force_search(G)
+    assert got2 == size and sorted(got_strs2) == sorted(strs)
+
+
+def _cut_dqva(G, partition, max_cuts, seed, fused):
+    random.seed(seed)
+    np.random.seed(seed)
+    n = G.number_of_nodes()
+    subgraphs, cut_edges = graph_funcs.get_subgraphs(G, partition)
+    cut_nodes, hot_nodes = simple_choose_nodes(G, partition, cut_edges, max_cuts)
+    order = []
+    for part in partition:
+        order += [int(v) for v in np.random.permutation(part)]
+    params = list(np.random.uniform(0, 2 * np.pi, n + 1))
+    init = "".join(np.random.choice(["0", "1"], p=[0.8, 0.2]) for _ in range(n))
+    circ, cuts = dqv_cut_ansatz.gen_dqva(G, partition, cut_nodes, hot_nodes, order,
+                                         params=params, init_state=init, fused=fused)
+    frags, wpm = qcc.cut_circuit(circ, cuts)
+    return circ, cuts, frags, wpm
+
+
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("max_cuts,seed", [(1, 0), (2, 1), (2, 5)])
+def test_cut_dqva_recombined_equals_uncut(fused, max_cuts, seed):
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4)])
+    circ, cuts, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5]], max_cuts, seed, fused)
+    assert 1 <= len(cuts) <= max_cuts and len(frags) == 2
+    N = circ.num_qubits
+    full = sv.probabilities(sv.simulate(N, circ.to_instructions()))
+    dist = qo.sim_with_cutting(frags, wpm, mode="likely")
+    for x in range(1 << N):
+        assert abs(dist.get(format(x, f"0{N}b"), 0.0) - full[x]) < 1e-10
+    # array ("GEMM") form == dict form
+    ft = qo.identify_frag_targets(wpm)
+    Rs = [qo.fragment_pauli_tensor(f, ft[i]["prep"], ft[i]["meas"]) for i, f in enumerate(frags)]
+    assert np.abs(qo.recombine_arrays(Rs, wpm) - full).max() < 1e-10
+    # MIS scoring: dict form == array form
+    stripped = mo.strip_ancillas(dist, 2)
+    cost = mo.avg_cost(stripped, G)
+    n = G.number_of_nodes()
+    s_p, s_pwok = mo.score_array(full, n, 2, mo.adjacency_masks(G, n))
+    assert abs(-cost - s_pwok) < 1e-10 and abs(s_p - 1) < 1e-10
+
+
+def test_three_fragments_recombined_equals_uncut():
+    """3 subgraphs in a chain -> 3 fragments (config 3 shape in miniature)."""
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 7), (7, 8), (0, 2),
+                      (3, 5), (6, 8)])
+    circ, cuts, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5], [6, 7, 8]], 2, 3, True)
+    assert len(frags) == 3
+    N = circ.num_qubits
+    full = sv.probabilities(sv.simulate(N, circ.to_instructions()))
+    ft = qo.identify_frag_targets(wpm)
+    Rs = [qo.fragment_pauli_tensor(f, ft[i]["prep"], ft[i]["meas"]) for i, f in enumerate(frags)]
+    assert np.abs(qo.recombine_arrays(Rs, wpm) - full).max() < 1e-10
+
+
+def test_top_probs_and_better_strs():
+    probs = {"0101": 0.4, "1010": 0.4, "0000": 0.1, "1111": 0.1, "0001": 1e-6}
+    G = nx.cycle_graph(4)
+    top = mo.top_probs(probs, threshold=1e-5, cutoff=2)
+    assert [t[0] for t in top] == ["0101", "1010"]            # stable: insertion order on ties
+    assert mo.better_strs(top, G, "0001") == [("0101", 2), ("1010", 2)]
+    assert abs(mo.avg_cost(probs, G) + (0.4 * 2 + 0.4 * 2 + 1e-6)) < 1e-15
