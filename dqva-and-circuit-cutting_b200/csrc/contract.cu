@@ -40,16 +40,20 @@ __device__ __forceinline__ void dmma_8x8x4(double& c0, double& c1, double a, dou
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+constexpr uint64_t FLAG_ROW_BAD = 1ull << 63, FLAG_COL_BAD = 1ull << 62;
+
 struct TileCoord { long long r0, c0; };
 
-__device__ __forceinline__ TileCoord tile_coord(long long t, long long tiles_m, long long tiles_n) {
-    // column panels of PANEL_W tiles; inside a panel walk rows, then the panel's columns
-    const long long per_panel = tiles_m * PANEL_W;
-    const long long panel = t / per_panel;
-    const long long rem = t - panel * per_panel;
-    const long long pw = (tiles_n - panel * PANEL_W) < PANEL_W ? (tiles_n - panel * PANEL_W) : PANEL_W;
-    const long long r = rem / pw, c = panel * PANEL_W + rem % pw;
-    return {r * TM, c * TN};
+// 32-bit tile walk (n_tiles < 2^31 is checked on the host): column panels of PANEL_W tiles;
+// inside a panel walk rows, then the panel's columns.
+__device__ __forceinline__ TileCoord tile_coord(int t, int tiles_m, int tiles_n) {
+    const int per_panel = tiles_m * PANEL_W;
+    const int panel = t / per_panel;
+    const int rem = t - panel * per_panel;
+    const int left = tiles_n - panel * PANEL_W;
+    const int pw = left < PANEL_W ? left : PANEL_W;
+    const int r = rem / pw, c = panel * PANEL_W + (rem - r * pw);
+    return {(long long)r * TM, (long long)c * TN};
 }
 
 struct ContractArgs {
@@ -65,6 +69,112 @@ struct ContractArgs {
     double* partials;
 };
 
+__device__ __forceinline__ double opaque(double x) {
+    asm volatile("" : "+d"(x));          // keeps the weights in FP64 (no I2F per output)
+    return x;
+}
+
+// Epilogue of one 128x128 tile from the 4x4x2 accumulators of this thread.  FULL: the tile lies
+// entirely inside the slab, no per-output bounds tests.  The independence test is folded into one
+// AND: bit 63 is set in every column mask and in the row mask of a row that is not itself
+// independent; bit 62 the other way round, so (cf & rf) == 0 <=> row ok, column ok, no edge.
+template <bool FULL, int STORE, bool OUT32>
+__device__ __forceinline__ void tile_epilogue(const ContractArgs& a, double (&acc)[4][4][2],
+                                              MisAccum& m0, MisAccum& m1, const TileCoord tc,
+                                              const double out_scale, int wm, int wn, int lane) {
+    const long long cbase = tc.c0 + wn * 32 + 2 * (lane & 3);
+    const long long rbase = tc.r0 + wm * 32 + (lane >> 2);
+    const double thr = a.sink.threshold;
+    uint64_t rf[4];
+    double rwd[4];
+    uint32_t hit = 0;                           // bit i*8 + j*2 + h: output above the threshold
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const long long r = rbase + i * 8;
+        const long long rg = a.row_lo + ((FULL || r < a.n_rows) ? r : 0);
+        const uint32_t rw = __ldg(a.tab.row_wok + rg);
+        rf[i] = __ldg(a.tab.row_forb + rg) | FLAG_COL_BAD | ((rw >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
+        rwd[i] = opaque((double)(rw & 0xffu));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const long long c = cbase + j * 8;
+        const bool cok = FULL || c < a.n_cols;
+        const bool two = FULL || c + 1 < a.n_cols;   // n_cols even or 1
+        const long long c0i = cok ? c : 0, c1i = two ? c + 1 : 0;
+        uint32_t cw0, cw1;
+        uint64_t cx0, cx1;
+        if (FULL) {                                  // c is even: one 8- and one 16-byte load
+            const uint2 cw = __ldg(reinterpret_cast<const uint2*>(a.tab.col_wok + c));
+            const ulonglong2 cx = __ldg(reinterpret_cast<const ulonglong2*>(a.tab.col_x + c));
+            cw0 = cw.x; cw1 = cw.y; cx0 = cx.x; cx1 = cx.y;
+        } else {
+            cw0 = __ldg(a.tab.col_wok + c0i); cw1 = __ldg(a.tab.col_wok + c1i);
+            cx0 = __ldg(a.tab.col_x + c0i); cx1 = __ldg(a.tab.col_x + c1i);
+        }
+        const uint64_t cf0 = cx0 | FLAG_ROW_BAD | ((cw0 >> 8) & 1u ? 0ull : FLAG_COL_BAD);
+        const uint64_t cf1 = cx1 | FLAG_ROW_BAD | ((cw1 >> 8) & 1u ? 0ull : FLAG_COL_BAD);
+        const double cwd0 = opaque((double)(cw0 & 0xffu)), cwd1 = opaque((double)(cw1 & 0xffu));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const double p0 = acc[i][j][0] * out_scale, p1 = acc[i][j][1] * out_scale;
+            const long long r = rbase + i * 8;
+            if (FULL || (r < a.n_rows && cok)) {
+                const double w0 = rwd[i] + cwd0;
+                m0.s_p += p0;
+                m0.s_pw = fma(p0, w0, m0.s_pw);
+                if ((cf0 & rf[i]) == 0ull) m0.s_pwok = fma(p0, w0, m0.s_pwok);
+                if (p0 > thr) hit |= 1u << (i * 8 + j * 2);
+                if (two) {
+                    const double w1 = rwd[i] + cwd1;
+                    m1.s_p += p1;
+                    m1.s_pw = fma(p1, w1, m1.s_pw);
+                    if ((cf1 & rf[i]) == 0ull) m1.s_pwok = fma(p1, w1, m1.s_pwok);
+                    if (p1 > thr) hit |= 2u << (i * 8 + j * 2);
+                }
+                if (STORE == 1) {
+                    const long long o = r * a.n_cols + c;
+                    if (OUT32) {
+                        float* out = (float*)a.P_out;
+                        if (two) *reinterpret_cast<float2*>(out + o) = make_float2((float)p0, (float)p1);
+                        else out[o] = (float)p0;
+                    } else {
+                        double* out = (double*)a.P_out;
+                        if (two) *reinterpret_cast<double2*>(out + o) = make_double2(p0, p1);
+                        else out[o] = p0;
+                    }
+                } else if (STORE == 2) {
+                    const uint64_t rx = __ldg(a.tab.row_x + a.row_lo + r);
+                    if (OUT32) {
+                        float* out = (float*)a.P_out;
+                        out[rx | cx0] = (float)p0;
+                        if (two) out[rx | cx1] = (float)p1;
+                    } else {
+                        double* out = (double*)a.P_out;
+                        out[rx | cx0] = p0;
+                        if (two) out[rx | cx1] = p1;
+                    }
+                }
+            }
+        }
+    }
+    // rare path: emit candidates, selecting the accumulator by a predicated scan
+    while (hit) {
+        const int b = __ffs(hit) - 1;
+        hit &= hit - 1;
+        double v = 0.0;
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+            if (b == q) v = acc[q >> 3][(q >> 1) & 3][q & 1];
+        const long long r = rbase + (b >> 3) * 8, c = cbase + ((b >> 1) & 3) * 8 + (b & 1);
+        cand_emit(a.sink, __ldg(a.tab.row_x + a.row_lo + r) | __ldg(a.tab.col_x + c), v * out_scale);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+}
+
 // STORE: 0 none, 1 united order, 2 circuit-order scatter.  OUT32: write float instead of double.
 template <int STORE, bool OUT32>
 __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a) {
@@ -73,21 +183,18 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp >> 2, wn = warp & 3;
-    const long long tiles_m = (a.n_rows + TM - 1) / TM, tiles_n = (a.n_cols + TN - 1) / TN;
-    // tiles_n is padded to whole panels only logically: the last panel may be narrower
-    const long long n_tiles = tiles_m * tiles_n;
+    const int tiles_m = (int)((a.n_rows + TM - 1) / TM), tiles_n = (int)((a.n_cols + TN - 1) / TN);
+    const int n_tiles = tiles_m * tiles_n;
     const int kchunks = a.kdim / BK;
-    const long long my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const long long total = my_tiles * kchunks;
     const double out_scale = a.scale * (a.d_norm ? 1.0 / *a.d_norm : 1.0);
 
-    // ---- producer: 4 x 16-byte cp.async per thread per stage --------------------------------
-    auto issue = [&](long long g) {
-        if (g < total) {
-            const long long ti = g / kchunks;
-            const int kc = (int)(g - ti * kchunks);
-            const TileCoord tc = tile_coord(blockIdx.x + ti * gridDim.x, tiles_m, tiles_n);
-            double* st = smem + (g % STAGES) * STAGE_DOUBLES;
+    // ---- producer: 4 x 16-byte cp.async per thread per stage; its (tile, k chunk, stage)
+    // cursor is advanced incrementally (no divisions in the steady state) ----------------------
+    int p_tile = blockIdx.x, p_kc = 0, p_stage = 0;
+    TileCoord p_tc = tile_coord(p_tile < n_tiles ? p_tile : 0, tiles_m, tiles_n);
+    auto issue = [&]() {
+        if (p_tile < n_tiles) {
+            double* st = smem + p_stage * STAGE_DOUBLES;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int q = tid + j * THREADS;             // 0..2047
@@ -96,19 +203,25 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
                 const int row = qq >> 3, c16 = qq & 7;       // 8 x 16 B per row slice
                 const int kg = c16 >> 1, within = (c16 & 1) * 2;
                 double* dst = st + op * OPERAND_DOUBLES + (kg * TM + row) * 4 + within;
-                const long long grow = (op == 0 ? tc.r0 : tc.c0) + row;
+                const long long grow = (op == 0 ? p_tc.r0 : p_tc.c0) + row;
                 const long long lim = op == 0 ? a.n_rows : a.n_cols;
                 const double* base = op == 0 ? a.A : a.Bt;
                 const bool ok = grow < lim;
-                const double* src = base + (ok ? grow : 0) * (long long)a.kdim + kc * BK + c16 * 2;
+                const double* src = base + (ok ? grow : 0) * (long long)a.kdim + p_kc * BK + c16 * 2;
                 cp_async16(dst, src, ok ? 16 : 0);
             }
+            if (++p_kc == kchunks) {
+                p_kc = 0;
+                p_tile += gridDim.x;
+                if (p_tile < n_tiles) p_tc = tile_coord(p_tile, tiles_m, tiles_n);
+            }
         }
+        p_stage = p_stage + 1 == STAGES ? 0 : p_stage + 1;
         cp_async_commit();
     };
 
 #pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) issue(s);
+    for (int s = 0; s < STAGES - 1; ++s) issue();
 
     double acc[4][4][2];
 #pragma unroll
@@ -116,14 +229,17 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    MisAccum macc = {0.0, 0.0, 0.0};
+    MisAccum macc = {0.0, 0.0, 0.0}, macc2 = {0.0, 0.0, 0.0};
+    int c_stage = 0;
 
-    for (long long g = 0; g < total; ++g) {
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (int kc = 0; kc < kchunks; ++kc) {
         cp_async_wait<STAGES - 2>();
         __syncthreads();
-        issue(g + STAGES - 1);
+        issue();
 
-        const double* sA = smem + (g % STAGES) * STAGE_DOUBLES;
+        const double* sA = smem + c_stage * STAGE_DOUBLES;
+        c_stage = c_stage + 1 == STAGES ? 0 : c_stage + 1;
         const double* sB = sA + OPERAND_DOUBLES;
 #pragma unroll
         for (int kk = 0; kk < BK / 4; ++kk) {
@@ -138,60 +254,17 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
                 for (int j = 0; j < 4; ++j) dmma_8x8x4(acc[i][j][0], acc[i][j][1], fa[i], fb[j]);
         }
 
-        const long long ti = g / kchunks;
-        if (g - ti * kchunks == kchunks - 1) {
-            // ---- epilogue of tile ti, registers only --------------------------------------
-            const TileCoord tc = tile_coord(blockIdx.x + ti * gridDim.x, tiles_m, tiles_n);
-            const long long cbase = tc.c0 + wn * 32 + 2 * (lane & 3);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const long long r = tc.r0 + wm * 32 + i * 8 + (lane >> 2);
-                const bool rok = r < a.n_rows;
-                const long long rg = a.row_lo + (rok ? r : 0);
-                const uint64_t rx = __ldg(a.tab.row_x + rg), rf = __ldg(a.tab.row_forb + rg);
-                const uint32_t rw = __ldg(a.tab.row_wok + rg);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const long long c = cbase + j * 8;
-                    const double p0 = acc[i][j][0] * out_scale, p1 = acc[i][j][1] * out_scale;
-                    acc[i][j][0] = acc[i][j][1] = 0.0;
-                    if (rok && c < a.n_cols) {        // n_cols even or 1: c+1 valid unless n_cols==1
-                        const bool two = c + 1 < a.n_cols;
-                        const uint64_t cx0 = __ldg(a.tab.col_x + c);
-                        const uint32_t cw0 = __ldg(a.tab.col_wok + c);
-                        mis_accumulate(macc, p0, rx, rf, rw, cx0, cw0, a.sink);
-                        uint64_t cx1 = 0;
-                        if (two) {
-                            cx1 = __ldg(a.tab.col_x + c + 1);
-                            mis_accumulate(macc, p1, rx, rf, rw, cx1, __ldg(a.tab.col_wok + c + 1), a.sink);
-                        }
-                        if (STORE == 1) {
-                            const long long o = r * a.n_cols + c;
-                            if (OUT32) {
-                                float* out = (float*)a.P_out;
-                                if (two) *reinterpret_cast<float2*>(out + o) = make_float2((float)p0, (float)p1);
-                                else out[o] = (float)p0;
-                            } else {
-                                double* out = (double*)a.P_out;
-                                if (two) *reinterpret_cast<double2*>(out + o) = make_double2(p0, p1);
-                                else out[o] = p0;
-                            }
-                        } else if (STORE == 2) {
-                            if (OUT32) {
-                                float* out = (float*)a.P_out;
-                                out[rx | cx0] = (float)p0;
-                                if (two) out[rx | cx1] = (float)p1;
-                            } else {
-                                double* out = (double*)a.P_out;
-                                out[rx | cx0] = p0;
-                                if (two) out[rx | cx1] = p1;
-                            }
-                        }
-                    }
-                }
-            }
-        }
+      }
+      // ---- epilogue of this tile, registers only; interior tiles take the guard-free path ----
+      {
+        const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
+        if (tc.r0 + TM <= a.n_rows && tc.c0 + TN <= a.n_cols)
+            tile_epilogue<true, STORE, OUT32>(a, acc, macc, macc2, tc, out_scale, wm, wn, lane);
+        else
+            tile_epilogue<false, STORE, OUT32>(a, acc, macc, macc2, tc, out_scale, wm, wn, lane);
+      }
     }
+    macc.s_p += macc2.s_p; macc.s_pw += macc2.s_pw; macc.s_pwok += macc2.s_pwok;
     cp_async_wait<0>();
     mis_block_store(macc, scratch, a.partials);
 }
@@ -301,6 +374,7 @@ extern "C" int qdc_contract_f64(const double* d_A, const double* d_Bt, int64_t r
     args.sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
     args.P_out = d_P_out; args.partials = d_partials;
     const long long n_tiles = ((n_rows + TM - 1) / TM) * ((n_cols + TN - 1) / TN);
+    QDC_REQUIRE(n_tiles < (1ll << 31) - 4096, "too many output tiles for one launch");
     const int sms = qdc_sm_count();
     const int grid = (int)(n_tiles < sms ? n_tiles : sms);
     int rc;

@@ -44,13 +44,14 @@ extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bit
                                     uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
                                     uint64_t* d_col_x, uint32_t* d_col_wok, void* stream) {
     QDC_REQUIRE(row_bits >= 0 && col_bits >= 0 && row_bits + col_bits <= 62, "bit counts");
-    QDC_REQUIRE(n_wires >= 0 && n_wires <= 64, "n_wires");
+    QDC_REQUIRE(n_wires >= 0 && n_wires <= 62, "n_wires");
+    QDC_REQUIRE((node_mask >> 62) == 0, "node_mask uses reserved bits");
     QDC_REQUIRE(h_bitpos && h_adj, "null tables");
     BitTable t;
     for (int i = 0; i < 64; ++i) { t.bitpos[i] = 0; t.adj[i] = 0; }
     uint64_t seen = 0;
     for (int b = 0; b < row_bits + col_bits; ++b) {
-        QDC_REQUIRE(h_bitpos[b] >= 0 && h_bitpos[b] < 64, "bitpos range");
+        QDC_REQUIRE(h_bitpos[b] >= 0 && h_bitpos[b] < 62, "bitpos range (wires 62, 63 are reserved flag bits)");
         QDC_REQUIRE(!((seen >> h_bitpos[b]) & 1), "bitpos must be injective");
         seen |= 1ull << h_bitpos[b];
         t.bitpos[b] = h_bitpos[b];

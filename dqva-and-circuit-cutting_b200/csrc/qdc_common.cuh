@@ -56,6 +56,14 @@ struct CandSink {
     double threshold;
 };
 
+__device__ __forceinline__ void cand_emit(const CandSink& sink, uint64_t x, double p) {
+    unsigned long long slot = atomicAdd(sink.count, 1ull);
+    if ((long long)slot < sink.cap) {
+        sink.x[slot] = x;
+        sink.p[slot] = p;
+    }
+}
+
 __device__ __forceinline__ void mis_accumulate(MisAccum& acc, double p, uint64_t rx, uint64_t rforb,
                                                uint32_t rwok, uint64_t cx, uint32_t cwok,
                                                const CandSink& sink) {
