@@ -26,7 +26,19 @@ SIGNATURES = {
     "qdc_last_error": (C.c_char_p, []),
     "qdc_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3),
     "qdc_mis_build_tables": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_int), c_u64p, C.c_int,
-                                       C.c_uint64, vp, vp, vp, vp, vp, vp]),
+                                       C.c_uint64, C.c_uint64, vp, vp, vp, vp, vp, vp]),
+    "qdc_sv_compile": (C.c_int, [C.c_int, vp, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int,
+                                 C.POINTER(vp)]),
+    "qdc_sv_free": (None, [vp]),
+    "qdc_sv_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                              C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]),
+    "qdc_sv_dump": (C.c_int, [vp] * 9),
+    "qdc_sv_run": (C.c_int, [vp, vp, c_i64, c_i64, c_i64, vp, C.c_int, C.POINTER(C.c_int32),
+                             C.c_int, C.POINTER(C.c_double), C.c_int, vp, vp]),
+    "qdc_sv_probs": (C.c_int, [vp, C.c_int, c_i64, C.c_uint64, vp, vp]),
+    "qdc_sv_pauli_tensor": (C.c_int, [vp, C.c_int, c_i64, C.c_uint64, C.c_int, C.c_int,
+                                      C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int,
+                                      C.POINTER(c_i64), vp, c_i64, vp]),
     "qdc_reduce_partials": (C.c_int, []),
     "qdc_mis_reduce": (C.c_int, [vp, C.c_int, c_i64, c_i64, c_i64, vp, C.c_double,
                                  vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i64, vp, vp]),

@@ -17,13 +17,13 @@ struct BitTable {
     uint64_t node_mask;
 };
 
-__global__ void mis_table_kernel(BitTable t, int bit_lo, long long count, uint64_t* __restrict__ xs,
+__global__ void mis_table_kernel(BitTable t, int bit_lo, long long count, uint64_t flip, uint64_t* __restrict__ xs,
                                  uint64_t* __restrict__ forb, uint32_t* __restrict__ wok) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
          i += (long long)gridDim.x * blockDim.x) {
         uint64_t x = 0;
         for (int b = 0; b < t.nbits; ++b)
-            if ((i >> b) & 1) x |= 1ull << t.bitpos[bit_lo + b];
+            if (((i ^ (long long)flip) >> b) & 1) x |= 1ull << t.bitpos[bit_lo + b];
         const uint64_t nodes = x & t.node_mask;
         uint64_t f = 0;
         uint64_t rem = nodes;
@@ -41,12 +41,13 @@ __global__ void mis_table_kernel(BitTable t, int bit_lo, long long count, uint64
 
 extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bitpos,
                                     const uint64_t* h_adj, int n_wires, uint64_t node_mask,
-                                    uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
+                                    uint64_t index_flip, uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
                                     uint64_t* d_col_x, uint32_t* d_col_wok, void* stream) {
     QDC_REQUIRE(row_bits >= 0 && col_bits >= 0 && row_bits + col_bits <= 62, "bit counts");
     QDC_REQUIRE(n_wires >= 0 && n_wires <= 62, "n_wires");
     QDC_REQUIRE((node_mask >> 62) == 0, "node_mask uses reserved bits");
     QDC_REQUIRE(h_bitpos && h_adj, "null tables");
+    QDC_REQUIRE((index_flip >> (row_bits + col_bits)) == 0, "index_flip");
     BitTable t;
     for (int i = 0; i < 64; ++i) { t.bitpos[i] = 0; t.adj[i] = 0; }
     uint64_t seen = 0;
@@ -65,7 +66,7 @@ extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bit
         t.nbits = col_bits;
         int blocks = (int)((n + threads - 1) / threads);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        mis_table_kernel<<<blocks, threads, 0, s>>>(t, 0, n, d_col_x, nullptr, d_col_wok);
+        mis_table_kernel<<<blocks, threads, 0, s>>>(t, 0, n, index_flip & (uint64_t)(n - 1), d_col_x, nullptr, d_col_wok);
         QDC_CHECK_LAUNCH();
     }
     {
@@ -73,7 +74,7 @@ extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bit
         t.nbits = row_bits;
         int blocks = (int)((n + threads - 1) / threads);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        mis_table_kernel<<<blocks, threads, 0, s>>>(t, col_bits, n, d_row_x, d_row_forb, d_row_wok);
+        mis_table_kernel<<<blocks, threads, 0, s>>>(t, col_bits, n, (index_flip >> col_bits) & (uint64_t)(n - 1), d_row_x, d_row_forb, d_row_wok);
         QDC_CHECK_LAUNCH();
     }
     return QDC_OK;
@@ -85,6 +86,8 @@ extern "C" int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bit
 template <typename T> struct Vec;
 template <> struct Vec<double> { using type = double2; static constexpr int N = 2; };
 template <> struct Vec<float>  { using type = float4;  static constexpr int N = 4; };
+struct Amp { double re, im; };            // complex128 amplitude: p = |amp|^2 (uncut cost, mis.py:639-665)
+template <> struct Vec<Amp>    { using type = double2; static constexpr int N = 1; };
 
 template <typename T>
 __device__ __forceinline__ typename Vec<T>::type ld_stream(const T* p);
@@ -100,8 +103,14 @@ template <> __device__ __forceinline__ float4 ld_stream<float>(const float* p) {
     return v;
 }
 
-__device__ __forceinline__ void unpack(const double2& v, double* o) { o[0] = v.x; o[1] = v.y; }
-__device__ __forceinline__ void unpack(const float4& v, double* o) {
+template <> __device__ __forceinline__ double2 ld_stream<Amp>(const Amp* p) {
+    return ld_stream<double>(reinterpret_cast<const double*>(p));
+}
+
+template <typename T> __device__ __forceinline__ void unpack(const typename Vec<T>::type& v, double* o);
+template <> __device__ __forceinline__ void unpack<double>(const double2& v, double* o) { o[0] = v.x; o[1] = v.y; }
+template <> __device__ __forceinline__ void unpack<Amp>(const double2& v, double* o) { o[0] = v.x * v.x + v.y * v.y; }
+template <> __device__ __forceinline__ void unpack<float>(const float4& v, double* o) {
     o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
 }
 
@@ -137,7 +146,7 @@ __global__ void __launch_bounds__(256) mis_reduce_kernel(
             const uint64_t rx = __ldg(tab.row_x + r), rf = __ldg(tab.row_forb + r);
             const uint32_t rw = __ldg(tab.row_wok + r);
             double p[VN];
-            unpack(vals[u], p);
+            unpack<T>(vals[u], p);
 #pragma unroll
             for (int j = 0; j < VN; ++j)
                 mis_accumulate(acc, p[j] * inv_norm, rx, rf, rw, __ldg(tab.col_x + c + j),
@@ -199,7 +208,7 @@ extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_
                               double* d_cand_p, unsigned long long* d_cand_count,
                               int64_t cand_cap, double* d_partials, void* stream) {
     QDC_REQUIRE(d_P && d_sums && d_partials, "null buffer");
-    QDC_REQUIRE(dtype == 0 || dtype == 1, "dtype");
+    QDC_REQUIRE(dtype >= 0 && dtype <= 2, "dtype");
     QDC_REQUIRE(n_rows >= 0 && n_cols > 0 && (n_cols & (n_cols - 1)) == 0, "n_cols power of two");
     QDC_REQUIRE(d_cand_x && d_cand_p && d_cand_count && cand_cap >= 0, "candidate sink");
     if (n_rows == 0) return QDC_OK;
@@ -209,8 +218,9 @@ extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_
     CandSink sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
     cudaStream_t s = (cudaStream_t)stream;
     const long long total = n_rows * n_cols;
-    const int vn = dtype == 0 ? 2 : 4;
+    const int vn = dtype == 0 ? 2 : dtype == 1 ? 4 : 1;
     int blocks;
+    QDC_REQUIRE(dtype != 2 || (((uintptr_t)d_P) & 15) == 0, "complex128 input must be 16-byte aligned");
     if (n_cols >= vn && (((uintptr_t)d_P) & 15) == 0) {
         constexpr int UNROLL = 4;
         const long long per_pass = 256ll * UNROLL * vn;
@@ -221,6 +231,9 @@ extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_
         if (dtype == 0)
             mis_reduce_kernel<double, UNROLL><<<blocks, 256, 0, s>>>(
                 (const double*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+        else if (dtype == 2)
+            mis_reduce_kernel<Amp, UNROLL><<<blocks, 256, 0, s>>>(
+                (const Amp*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
         else
             mis_reduce_kernel<float, UNROLL><<<blocks, 256, 0, s>>>(
                 (const float*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);

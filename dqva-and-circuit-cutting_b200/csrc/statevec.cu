@@ -1,0 +1,741 @@
+// K1-K3: batched statevector engine (complex128), batch = initial-state variant x parameter set.
+//
+// Replaces the simulator behind qiskit.execute(circuits, backend, shots) on the reference's hot
+// path (qsplit/qsplit_mlrecon_methods.py:20-42, 116-162; mis.py:649) for the gate set of its
+// ansatz modules (ansatz/dqv_cut_ansatz.py:127-171; ansatz/qaoa_plus.py:8-37): every gate is a
+// 2x2 on one target applied where the control qubits hold given values.
+//
+// Design (B200): the gate list is compiled on the host into GROUPS.  One group = the gates whose
+// non-diagonal targets all lie in a set L of `t` qubits; a CTA owns one tile = the 2^t
+// amplitudes that differ only in the qubits of L, keeps it in shared memory, applies the whole
+// group there (controls outside L are constant per tile -> the gate is applied or skipped for the
+// whole tile; diagonal gates need no locality at all), and touches global memory once per group
+// (16 B read + 16 B write per amplitude; the first group builds the initial product state in
+// shared memory and reads nothing).  L always contains the lowest `c` qubits, so global accesses
+// are runs of 2^c * 16 B.  Fragments of <= t qubits run their whole circuit in ONE launch with
+// one CTA per batch element.  Bound: shared-memory bandwidth inside a group (32 B per amplitude
+// per non-diagonal gate), L2/HBM between groups (algorithmic bytes per group = 32 B * 2^n * batch).
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "qdc_common.cuh"
+
+namespace {
+
+constexpr int MAX_RUNS = 24;
+constexpr int MAX_FIXED = 16;
+constexpr int MAX_PREP = 10;
+constexpr int MAX_CODES = 6;
+constexpr int MAX_DIAG_RUN = 32;      // <= smallest CTA size
+
+struct __align__(16) SvOp {   // 64 bytes
+    uint32_t kind;            // 0 general 2x2, 1 diagonal
+    int32_t tbit;             // tile-local bit of the target, -1: diagonal on a non-local qubit
+    int32_t gtarget;          // full-index qubit of the target
+    int32_t mat;              // matrix slot
+    uint32_t lmask, lval;     // controls inside the tile (tile-local bit positions)
+    uint64_t gmask, gval;     // controls outside the tile (full-index positions)
+    uint8_t n_fixed;          // entries of fixed[]: (target bit for kind 0) + local control bits, ascending
+    uint8_t diag_run;         // kind 1 without controls: consecutive such ops starting here
+    uint8_t pad[2];
+    uint8_t fixed[MAX_FIXED];
+    uint32_t pad2;
+};
+static_assert(sizeof(SvOp) == 64, "SvOp layout");
+
+struct MatDesc {              // how to build matrix slot i for a parameter set
+    int32_t kind, slot, conj_x, pad;
+    double scale, offset;
+    double m[8];
+};
+
+struct Group {
+    int first_op, n_ops;
+    uint64_t local_mask;
+    int n_runs;
+    uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
+};
+
+struct GroupArgs {
+    double2* state;
+    const SvOp* ops;
+    const double* mats;       // [n_sets][n_mats][8]
+    long long n_tiles;        // tiles per state
+    long long init_lo;
+    uint64_t prep_mask;
+    int n, t, n_sets, n_mats, op_lo, op_hi, first, n_runs, n_prep, n_codes;
+    uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
+    uint8_t prep_q[MAX_PREP];
+    double code[MAX_CODES][4];
+};
+
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ double2 cfma(double2 a, double2 b, double2 c) {   // a*b + c
+    return make_double2(fma(a.x, b.x, fma(-a.y, b.y, c.x)), fma(a.x, b.y, fma(a.y, b.x, c.y)));
+}
+
+// tile-local index -> full index with zeros in the non-local positions
+__device__ __forceinline__ uint64_t expand_runs(uint64_t l, int n_runs, const uint8_t* pos,
+                                                const uint8_t* len) {
+    for (int r = 0; r < n_runs; ++r) {
+        const int p = pos[r], w = len[r];
+        l = ((l >> p) << (p + w)) | (l & ((1ull << p) - 1ull));
+    }
+    return l;
+}
+
+__device__ __forceinline__ uint32_t insert_fixed(uint32_t i, int n_fixed, const uint8_t* fixed) {
+    for (int f = 0; f < n_fixed; ++f) {
+        const int p = fixed[f];
+        i = ((i >> p) << (p + 1)) | (i & ((1u << p) - 1u));
+    }
+    return i;
+}
+
+__global__ void __launch_bounds__(1024) sv_group_kernel(const GroupArgs a) {
+    extern __shared__ double2 tile[];
+    __shared__ double2 sh_d0[MAX_DIAG_RUN], sh_d1[MAX_DIAG_RUN];
+    __shared__ int sh_tb[MAX_DIAG_RUN];
+    __shared__ double2 sh_gfac;
+
+    const long long blk = blockIdx.x;
+    const long long batch = blk / a.n_tiles;
+    const long long tile_id = blk - batch * a.n_tiles;
+    uint64_t base = 0;
+    {
+        uint64_t rem = (uint64_t)tile_id;
+        for (int r = 0; r < a.n_runs; ++r) {
+            const int w = a.run_len[r];
+            base |= (rem & ((1ull << w) - 1ull)) << a.run_pos[r];
+            rem >>= w;
+        }
+    }
+    double2* st = a.state + (batch << a.n);
+    const uint32_t T = 1u << a.t;
+    const int nthr = blockDim.x, tid = threadIdx.x;
+
+    if (a.first) {
+        // initial product state: prep qubit j in code[digit_j], every other qubit in |0>
+        long long v = a.init_lo + batch / a.n_sets;
+        int digit[MAX_PREP];
+        for (int j = a.n_prep - 1; j >= 0; --j) { digit[j] = (int)(v % a.n_codes); v /= a.n_codes; }
+        for (uint32_t l = tid; l < T; l += nthr) {
+            const uint64_t x = expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base;
+            double2 amp = make_double2(0.0, 0.0);
+            if ((x & ~a.prep_mask) == 0ull) {
+                amp = make_double2(1.0, 0.0);
+                for (int j = 0; j < a.n_prep; ++j) {
+                    const int bit = (int)((x >> a.prep_q[j]) & 1ull);
+                    amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
+                }
+            }
+            tile[l] = amp;
+        }
+    } else {
+        for (uint32_t l = tid; l < T; l += nthr)
+            tile[l] = st[expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base];
+    }
+    __syncthreads();
+
+    const double* mats = a.mats + (size_t)(batch % a.n_sets) * a.n_mats * 8;
+    for (int i = a.op_lo; i < a.op_hi;) {
+        const SvOp op = a.ops[i];
+        if ((base & op.gmask) != op.gval) { ++i; continue; }          // uniform over the CTA
+        if (op.kind == 0) {
+            const double* m = mats + (size_t)op.mat * 8;
+            const double2 m00 = make_double2(m[0], m[1]), m01 = make_double2(m[2], m[3]);
+            const double2 m10 = make_double2(m[4], m[5]), m11 = make_double2(m[6], m[7]);
+            const uint32_t count = 1u << (a.t - op.n_fixed), tb = 1u << op.tbit;
+            for (uint32_t k = tid; k < count; k += nthr) {
+                const uint32_t l0 = insert_fixed(k, op.n_fixed, op.fixed) | op.lval;
+                const uint32_t l1 = l0 | tb;
+                const double2 a0 = tile[l0], a1 = tile[l1];
+                tile[l0] = cfma(m00, a0, cmul(m01, a1));
+                tile[l1] = cfma(m10, a0, cmul(m11, a1));
+            }
+            ++i;
+        } else if (op.diag_run >= 1) {
+            // joint pass over a run of uncontrolled diagonal gates
+            const int run = op.diag_run;
+            if (tid < run) {
+                const SvOp o = a.ops[i + tid];
+                const double* m = mats + (size_t)o.mat * 8;
+                sh_d0[tid] = make_double2(m[0], m[1]);
+                sh_d1[tid] = make_double2(m[6], m[7]);
+                sh_tb[tid] = o.tbit >= 0 ? o.tbit : -1 - o.gtarget;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                double2 g = make_double2(1.0, 0.0);
+                for (int k = 0; k < run; ++k)
+                    if (sh_tb[k] < 0) g = cmul(g, ((base >> (-1 - sh_tb[k])) & 1ull) ? sh_d1[k] : sh_d0[k]);
+                sh_gfac = g;
+            }
+            __syncthreads();
+            const double2 g = sh_gfac;
+            for (uint32_t l = tid; l < T; l += nthr) {
+                double2 f = g;
+                for (int k = 0; k < run; ++k) {
+                    const int b = sh_tb[k];
+                    if (b >= 0) f = cmul(f, ((l >> b) & 1u) ? sh_d1[k] : sh_d0[k]);
+                }
+                tile[l] = cmul(tile[l], f);
+            }
+            i += run;
+        } else {
+            // controlled diagonal gate (or one too many for a run): fixed[] = local control bits
+            const double* m = mats + (size_t)op.mat * 8;
+            const double2 d0 = make_double2(m[0], m[1]), d1 = make_double2(m[6], m[7]);
+            const uint32_t count = 1u << (a.t - op.n_fixed);
+            const bool local = op.tbit >= 0;
+            const double2 dg = ((base >> op.gtarget) & 1ull) ? d1 : d0;
+            for (uint32_t k = tid; k < count; k += nthr) {
+                const uint32_t l = insert_fixed(k, op.n_fixed, op.fixed) | op.lval;
+                const double2 d = local ? (((l >> op.tbit) & 1u) ? d1 : d0) : dg;
+                tile[l] = cmul(tile[l], d);
+            }
+            ++i;
+        }
+        __syncthreads();
+    }
+
+    for (uint32_t l = tid; l < T; l += nthr)
+        st[expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base] = tile[l];
+}
+
+// one thread per (parameter set, matrix slot)
+__global__ void sv_matrix_kernel(const MatDesc* __restrict__ desc, int n_mats, long long n_sets,
+                                 const double* __restrict__ params, int n_params,
+                                 double* __restrict__ mats) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n_sets * n_mats) return;
+    const long long set = i / n_mats;
+    const MatDesc d = desc[i - set * n_mats];
+    const double ang = d.scale * (d.slot >= 0 ? params[set * n_params + d.slot] : 0.0) + d.offset;
+    double m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const double r = 0.70710678118654752440;
+    double s, c;
+    switch (d.kind) {
+        case QDC_G_ID: m[0] = 1; m[6] = 1; break;
+        case QDC_G_X: m[2] = 1; m[4] = 1; break;
+        case QDC_G_Y: m[3] = -1; m[5] = 1; break;
+        case QDC_G_Z: m[0] = 1; m[6] = -1; break;
+        case QDC_G_H: m[0] = r; m[2] = r; m[4] = r; m[6] = -r; break;
+        case QDC_G_S: m[0] = 1; m[7] = 1; break;
+        case QDC_G_SDG: m[0] = 1; m[7] = -1; break;
+        case QDC_G_T: m[0] = 1; m[6] = r; m[7] = r; break;
+        case QDC_G_TDG: m[0] = 1; m[6] = r; m[7] = -r; break;
+        case QDC_G_RX: sincos(0.5 * ang, &s, &c); m[0] = c; m[3] = -s; m[5] = -s; m[6] = c; break;
+        case QDC_G_RY: sincos(0.5 * ang, &s, &c); m[0] = c; m[2] = -s; m[4] = s; m[6] = c; break;
+        case QDC_G_RZ: sincos(0.5 * ang, &s, &c); m[0] = c; m[1] = -s; m[6] = c; m[7] = s; break;
+        case QDC_G_U1: sincos(ang, &s, &c); m[0] = 1; m[6] = c; m[7] = s; break;
+        default:
+            for (int k = 0; k < 8; ++k) m[k] = d.m[k];
+    }
+    if (d.conj_x) {                       // X.M.X: swap rows and columns
+        double t;
+        t = m[0]; m[0] = m[6]; m[6] = t;  t = m[1]; m[1] = m[7]; m[7] = t;
+        t = m[2]; m[2] = m[4]; m[4] = t;  t = m[3]; m[3] = m[5]; m[5] = t;
+    }
+    double* out = mats + i * 8;
+    for (int k = 0; k < 8; ++k) out[k] = m[k];
+}
+
+__global__ void __launch_bounds__(256) sv_probs_kernel(const double2* __restrict__ st, int n,
+                                                       long long total, uint64_t flip,
+                                                       double* __restrict__ probs) {
+    const uint64_t mask = (1ull << n) - 1ull;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const uint64_t x = (uint64_t)i & mask;
+        const double2 v = st[((uint64_t)i & ~mask) | (x ^ flip)];
+        probs[i] = v.x * v.x + v.y * v.y;
+    }
+}
+
+// ---- fragment tensor in the Pauli basis -----------------------------------------------------
+struct TensorArgs {
+    const double2* state;
+    double* T;
+    long long n_sets, n_b, ld;
+    uint64_t flip;
+    int n, n_prep, n_meas, bb;      // bb = final-bit values per CTA
+    int n_runs;                     // runs of measured-qubit positions (holes of the b deposit)
+    uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
+    uint8_t meas_q[8];
+    long long stride[12];           // kappa stride per axis (prep axes, then meas axes)
+    double frame[16];               // frame[a * 4 + s]
+};
+
+__global__ void __launch_bounds__(256) sv_pauli_tensor_kernel(const TensorArgs a) {
+    extern __shared__ double2 sh_raw[];
+    const int p = a.n_prep, m = a.n_meas;
+    const int n_s = 1 << (2 * p), n_mu = 1 << m, n_pm = 1 << (2 * m);
+    const int n_kappa = n_s * n_pm;
+    double2* amp = sh_raw;                                        // [bb][n_s][n_mu]
+    double* R = reinterpret_cast<double*>(sh_raw + (size_t)a.bb * n_s * n_mu);   // [bb][n_s][n_pm]
+    const long long set = blockIdx.y;
+    const long long b0 = (long long)blockIdx.x * a.bb;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+
+    // 1. gather amplitudes (bl fastest: neighbouring b are neighbouring addresses)
+    for (int idx = tid; idx < a.bb * n_s * n_mu; idx += nthr) {
+        const int bl = idx % a.bb, rest = idx / a.bb;
+        const int mu = rest % n_mu, s = rest / n_mu;
+        const long long b = b0 + bl;
+        double2 v = make_double2(0.0, 0.0);
+        if (b < a.n_b) {
+            uint64_t x = expand_runs((uint64_t)b, a.n_runs, a.run_pos, a.run_len);
+            for (int j = 0; j < m; ++j) x |= (uint64_t)((mu >> j) & 1) << a.meas_q[j];
+            v = a.state[(((long long)s * a.n_sets + set) << a.n) | (long long)(x ^ a.flip)];
+        }
+        amp[((size_t)bl * n_s + s) * n_mu + mu] = v;
+    }
+    __syncthreads();
+
+    // 2. Pauli expectation on the measured qubits: R[bl][s][pm] = <psi| P_pm |psi> restricted to b
+    for (int idx = tid; idx < a.bb * n_s * n_pm; idx += nthr) {
+        const int pm = idx % n_pm, rest = idx / n_pm;            // rest = bl * n_s + s
+        uint32_t xmask = 0, zmask = 0;
+        int n_y = 0;
+        for (int j = 0; j < m; ++j) {                             // axis j: digit j, most significant first
+            const int aj = (pm >> (2 * (m - 1 - j))) & 3;         // 0 I, 1 X, 2 Y, 3 Z
+            if (aj == 1 || aj == 2) xmask |= 1u << j;
+            if (aj == 2 || aj == 3) zmask |= 1u << j;
+            n_y += aj == 2;
+        }
+        const double2* v = amp + (size_t)rest * n_mu;
+        double re = 0.0, im = 0.0;
+        for (int mu = 0; mu < n_mu; ++mu) {
+            const double2 ket = v[mu], bra = v[mu ^ xmask];      // conj(bra) * ket
+            double tr = bra.x * ket.x + bra.y * ket.y, ti = bra.x * ket.y - bra.y * ket.x;
+            if (__popc(mu & zmask) & 1) { tr = -tr; ti = -ti; }
+            re += tr; im += ti;
+        }
+        const int ny = n_y & 3;                                   // multiply by i^n_y, keep Re
+        R[idx] = ny == 0 ? re : ny == 1 ? -im : ny == 2 ? -re : im;
+    }
+    __syncthreads();
+
+    // 3. preparation frame inverse along each prep axis: out[a] = sum_s frame[a][s] in[s]
+    for (int j = 0; j < p; ++j) {
+        const int inner = n_pm << (2 * (p - 1 - j));              // stride of digit j inside kappa
+        const int n_vec = a.bb * n_kappa / 4;
+        for (int idx = tid; idx < n_vec; idx += nthr) {
+            const int lo = idx % inner, hi = idx / inner;
+            double* q = R + (size_t)hi * inner * 4 + lo;
+            const double v0 = q[0], v1 = q[inner], v2 = q[2 * inner], v3 = q[3 * inner];
+#pragma unroll
+            for (int aa = 0; aa < 4; ++aa)
+                q[aa * inner] = a.frame[aa * 4] * v0 + a.frame[aa * 4 + 1] * v1 +
+                                a.frame[aa * 4 + 2] * v2 + a.frame[aa * 4 + 3] * v3;
+        }
+        __syncthreads();
+    }
+
+    // 4. write T[set][b][kappa_out]
+    const int n_axes = p + m;
+    for (int idx = tid; idx < a.bb * n_kappa; idx += nthr) {
+        const int kap = idx % n_kappa, bl = idx / n_kappa;
+        const long long b = b0 + bl;
+        if (b >= a.n_b) continue;
+        long long ko = 0;
+        for (int ax = 0; ax < n_axes; ++ax)
+            ko += (long long)((kap >> (2 * (n_axes - 1 - ax))) & 3) * a.stride[ax];
+        a.T[(set * a.n_b + b) * a.ld + ko] = R[idx];
+    }
+}
+
+// ---- host: compiler ---------------------------------------------------------------------------
+struct LGate {                 // lowered gate (after the X frame)
+    int src, kind, target, conj;
+    uint64_t cmask, cval;
+    bool diag, tgt_zero;
+};
+
+bool kind_is_diag(const qdc_gate& g) {
+    switch (g.kind) {
+        case QDC_G_ID: case QDC_G_Z: case QDC_G_S: case QDC_G_SDG: case QDC_G_T: case QDC_G_TDG:
+        case QDC_G_RZ: case QDC_G_U1: return true;
+        case QDC_G_U2: return g.m[2] == 0.0 && g.m[3] == 0.0 && g.m[4] == 0.0 && g.m[5] == 0.0;
+        default: return false;
+    }
+}
+
+}  // namespace
+
+struct qdc_sv_program {
+    int n, t, c;
+    uint64_t flip;
+    std::vector<SvOp> ops;
+    std::vector<MatDesc> mats;
+    std::vector<Group> groups;
+    std::vector<int> op_src, op_conj;        // for qdc_sv_dump
+    std::vector<uint64_t> op_cmask, op_cval;
+    SvOp* d_ops = nullptr;
+    MatDesc* d_mats = nullptr;
+};
+
+extern "C" void qdc_sv_free(qdc_sv_program* prog) {
+    if (!prog) return;
+    if (prog->d_ops) cudaFree(prog->d_ops);
+    if (prog->d_mats) cudaFree(prog->d_mats);
+    delete prog;
+}
+
+extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, uint64_t zero_mask,
+                              int tile_bits, int coalesce_bits, int flags, qdc_sv_program** out) {
+    QDC_REQUIRE(out != nullptr, "out");
+    *out = nullptr;
+    QDC_REQUIRE(n_qubits >= 1 && n_qubits <= 40, "n_qubits in [1, 40]");
+    QDC_REQUIRE(n_gates >= 0 && (gates != nullptr || n_gates == 0), "gates");
+    const int n = n_qubits;
+    int t = tile_bits <= 0 ? 12 : tile_bits;
+    if (t > n) t = n;
+    QDC_REQUIRE(t >= 1 && t <= 13, "tile_bits in [1, 13] (2^13 * 16 B = 128 KB of shared memory)");
+    int c = coalesce_bits < 0 ? 4 : coalesce_bits;
+    if (c > t) c = t;
+    if (t < n && c >= t) c = t - 1;      // leave room for at least one non-local target
+    const uint64_t all = n == 64 ? ~0ull : ((1ull << n) - 1ull);
+
+    // ---- pass 1: X frame ------------------------------------------------------------------
+    std::vector<LGate> lg;
+    uint64_t flip = 0;
+    for (int gi = 0; gi < n_gates; ++gi) {
+        const qdc_gate& g = gates[gi];
+        QDC_REQUIRE(g.kind >= QDC_G_ID && g.kind <= QDC_G_U2, "gate kind");
+        QDC_REQUIRE(g.target >= 0 && g.target < n, "gate target");
+        QDC_REQUIRE((g.ctrl_mask & ~all) == 0 && (g.ctrl_val & ~g.ctrl_mask) == 0, "gate controls");
+        QDC_REQUIRE(!((g.ctrl_mask >> g.target) & 1ull), "target among controls");
+        if (g.kind == QDC_G_ID) continue;
+        if (g.kind == QDC_G_X && g.ctrl_mask == 0) { flip ^= 1ull << g.target; continue; }
+        LGate l;
+        l.src = gi; l.kind = g.kind; l.target = g.target;
+        l.cmask = g.ctrl_mask; l.cval = g.ctrl_val ^ (flip & g.ctrl_mask);
+        l.conj = (int)((flip >> g.target) & 1ull);
+        l.diag = kind_is_diag(g);
+        l.tgt_zero = false;
+        lg.push_back(l);
+    }
+
+    // ---- pass 2: ancilla compute / act / uncompute -> one controlled gate -----------------
+    std::vector<LGate> fg;
+    {
+        uint64_t zero = zero_mask & all;          // stored-frame |0> qubits
+        for (size_t i = 0; i < lg.size();) {
+            const LGate& a = lg[i];
+            bool fused = false;
+            if ((flags & QDC_SV_FUSE_ANCILLA) && a.kind == QDC_G_X && a.cmask != 0 && !a.conj &&
+                ((zero >> a.target) & 1ull) && i + 2 < lg.size()) {
+                const LGate& b = lg[i + 1];
+                const LGate& cgate = lg[i + 2];
+                const uint64_t abit = 1ull << a.target;
+                if (b.cmask == abit && b.cval == abit && !((a.cmask >> b.target) & 1ull) &&
+                    b.target != a.target && cgate.kind == QDC_G_X && cgate.target == a.target &&
+                    cgate.cmask == a.cmask && cgate.cval == a.cval && !cgate.conj) {
+                    LGate f = b;
+                    f.cmask = a.cmask; f.cval = a.cval;
+                    fg.push_back(f);
+                    if (!f.diag) zero &= ~(1ull << f.target);
+                    i += 3;
+                    fused = true;
+                }
+            }
+            if (!fused) {
+                fg.push_back(a);
+                if (!a.diag) zero &= ~(1ull << a.target);
+                ++i;
+            }
+        }
+    }
+
+    // ---- pass 3: list scheduling into tile-local groups --------------------------------------
+    qdc_sv_program* prog = new (std::nothrow) qdc_sv_program();
+    QDC_REQUIRE(prog != nullptr, "out of host memory");
+    prog->n = n; prog->t = t; prog->c = c; prog->flip = flip;
+    const uint64_t low = c >= 64 ? ~0ull : ((1ull << c) - 1ull);
+    std::vector<char> done(fg.size(), 0);
+    size_t n_done = 0;
+    std::vector<std::vector<int>> group_gates;
+    std::vector<uint64_t> group_L;
+    while (n_done < fg.size()) {
+        uint64_t L = low & all, skipped_uses = 0, skipped_nd_targets = 0;
+        std::vector<int> mine;
+        for (size_t i = 0; i < fg.size(); ++i) {
+            if (done[i]) continue;
+            const LGate& g = fg[i];
+            const uint64_t tb = 1ull << g.target, uses = tb | g.cmask, nd = g.diag ? 0ull : tb;
+            bool take = !(nd & skipped_uses) && !(uses & skipped_nd_targets);
+            if (take && !g.diag && !(L & tb)) {
+                if (__builtin_popcountll(L) < t) L |= tb; else take = false;
+            }
+            if (take) { mine.push_back((int)i); done[i] = 1; ++n_done; }
+            else { skipped_uses |= uses; skipped_nd_targets |= nd; }
+        }
+        group_gates.push_back(mine);
+        group_L.push_back(L);
+    }
+    if (group_gates.empty()) { group_gates.push_back({}); group_L.push_back(low & all); }
+
+    for (size_t gidx = 0; gidx < group_gates.size(); ++gidx) {
+        uint64_t L = group_L[gidx];
+        for (int q = 0; q < n && __builtin_popcountll(L) < t; ++q) L |= 1ull << q;   // pad to t qubits
+        Group gr;
+        gr.first_op = (int)prog->ops.size();
+        gr.local_mask = L;
+        gr.n_runs = 0;
+        for (int q = 0; q < n;) {
+            if ((L >> q) & 1ull) { ++q; continue; }
+            int e = q;
+            while (e < n && !((L >> e) & 1ull)) ++e;
+            if (gr.n_runs >= MAX_RUNS) { qdc_sv_free(prog); QDC_REQUIRE(false, "too many tile runs"); }
+            gr.run_pos[gr.n_runs] = (uint8_t)q; gr.run_len[gr.n_runs] = (uint8_t)(e - q);
+            ++gr.n_runs;
+            q = e;
+        }
+        auto local_bit = [&](int q) { return __builtin_popcountll(L & ((1ull << q) - 1ull)); };
+        for (int gi : group_gates[gidx]) {
+            const LGate& g = fg[gi];
+            SvOp op;
+            memset(&op, 0, sizeof(op));
+            op.kind = g.diag ? 1u : 0u;
+            op.gtarget = g.target;
+            op.tbit = ((L >> g.target) & 1ull) ? local_bit(g.target) : -1;
+            op.mat = (int)prog->mats.size();
+            std::vector<int> fixed;
+            if (!g.diag) fixed.push_back(op.tbit);
+            for (int q = 0; q < n; ++q) {
+                if (!((g.cmask >> q) & 1ull)) continue;
+                if ((L >> q) & 1ull) {
+                    const int lb = local_bit(q);
+                    op.lmask |= 1u << lb;
+                    if ((g.cval >> q) & 1ull) op.lval |= 1u << lb;
+                    fixed.push_back(lb);
+                } else {
+                    op.gmask |= 1ull << q;
+                    op.gval |= g.cval & (1ull << q);
+                }
+            }
+            std::sort(fixed.begin(), fixed.end());
+            if ((int)fixed.size() > MAX_FIXED) { qdc_sv_free(prog); QDC_REQUIRE(false, "too many local controls"); }
+            op.n_fixed = (uint8_t)fixed.size();
+            for (size_t k = 0; k < fixed.size(); ++k) op.fixed[k] = (uint8_t)fixed[k];
+            prog->ops.push_back(op);
+            MatDesc md;
+            memset(&md, 0, sizeof(md));
+            const qdc_gate& src = gates[g.src];
+            md.kind = src.kind; md.slot = src.param_slot; md.conj_x = g.kind == QDC_G_X ? 0 : g.conj;
+            md.scale = src.scale; md.offset = src.offset;
+            for (int k = 0; k < 8; ++k) md.m[k] = src.m[k];
+            prog->mats.push_back(md);
+            prog->op_src.push_back(g.src);
+            prog->op_conj.push_back(md.conj_x);
+            prog->op_cmask.push_back(g.cmask);
+            prog->op_cval.push_back(g.cval);
+        }
+        gr.n_ops = (int)prog->ops.size() - gr.first_op;
+        // runs of uncontrolled diagonal ops (they commute with each other: one joint pass)
+        for (int i = gr.first_op; i < gr.first_op + gr.n_ops;) {
+            SvOp& o = prog->ops[i];
+            if (o.kind == 1 && o.lmask == 0 && o.gmask == 0) {
+                int e = i;
+                while (e < gr.first_op + gr.n_ops && e - i < MAX_DIAG_RUN && prog->ops[e].kind == 1 &&
+                       prog->ops[e].lmask == 0 && prog->ops[e].gmask == 0) ++e;
+                o.diag_run = (uint8_t)(e - i);
+                i = e;
+            } else {
+                ++i;
+            }
+        }
+        prog->groups.push_back(gr);
+    }
+
+    if (!prog->ops.empty()) {
+        cudaError_t e1 = cudaMalloc(&prog->d_ops, prog->ops.size() * sizeof(SvOp));
+        cudaError_t e2 = cudaMalloc(&prog->d_mats, prog->mats.size() * sizeof(MatDesc));
+        if (e1 == cudaSuccess && e2 == cudaSuccess) {
+            e1 = cudaMemcpy(prog->d_ops, prog->ops.data(), prog->ops.size() * sizeof(SvOp), cudaMemcpyHostToDevice);
+            e2 = cudaMemcpy(prog->d_mats, prog->mats.data(), prog->mats.size() * sizeof(MatDesc), cudaMemcpyHostToDevice);
+        }
+        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+            // no device (e.g. host-only schedule tests): keep the host schedule, run() will refuse
+            cudaGetLastError();
+            if (prog->d_ops) { cudaFree(prog->d_ops); prog->d_ops = nullptr; }
+            if (prog->d_mats) { cudaFree(prog->d_mats); prog->d_mats = nullptr; }
+            cudaGetLastError();
+        }
+    }
+    *out = prog;
+    return QDC_OK;
+}
+
+extern "C" int qdc_sv_info(const qdc_sv_program* prog, int* n_qubits, int* n_groups, int* n_ops,
+                           int* n_matrices, int* tile_bits, uint64_t* flip_mask) {
+    QDC_REQUIRE(prog != nullptr, "program");
+    if (n_qubits) *n_qubits = prog->n;
+    if (n_groups) *n_groups = (int)prog->groups.size();
+    if (n_ops) *n_ops = (int)prog->ops.size();
+    if (n_matrices) *n_matrices = (int)prog->mats.size();
+    if (tile_bits) *tile_bits = prog->t;
+    if (flip_mask) *flip_mask = prog->flip;
+    return QDC_OK;
+}
+
+extern "C" int qdc_sv_dump(const qdc_sv_program* prog, int32_t* group_first_op,
+                           uint64_t* group_local_mask, int32_t* op_kind, int32_t* op_target,
+                           uint64_t* op_ctrl_mask, uint64_t* op_ctrl_val, int32_t* op_src_gate,
+                           int32_t* op_conj_x) {
+    QDC_REQUIRE(prog != nullptr, "program");
+    const size_t ng = prog->groups.size();
+    for (size_t g = 0; g < ng; ++g) {
+        if (group_first_op) group_first_op[g] = prog->groups[g].first_op;
+        if (group_local_mask) group_local_mask[g] = prog->groups[g].local_mask;
+    }
+    if (group_first_op) group_first_op[ng] = (int32_t)prog->ops.size();
+    for (size_t i = 0; i < prog->ops.size(); ++i) {
+        if (op_kind) op_kind[i] = (int32_t)prog->ops[i].kind;
+        if (op_target) op_target[i] = prog->ops[i].gtarget;
+        if (op_ctrl_mask) op_ctrl_mask[i] = prog->op_cmask[i];
+        if (op_ctrl_val) op_ctrl_val[i] = prog->op_cval[i];
+        if (op_src_gate) op_src_gate[i] = prog->op_src[i];
+        if (op_conj_x) op_conj_x[i] = prog->op_conj[i];
+    }
+    return QDC_OK;
+}
+
+extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int64_t n_init,
+                          int64_t n_sets, const double* d_params, int n_params,
+                          const int32_t* h_prep_qubits, int n_prep, const double* h_code_table,
+                          int n_codes, double* d_matrices, void* stream) {
+    QDC_REQUIRE(prog != nullptr && d_state != nullptr, "program / state");
+    QDC_REQUIRE(n_init >= 1 && n_sets >= 1 && init_lo >= 0, "batch");
+    QDC_REQUIRE(n_prep >= 0 && n_prep <= MAX_PREP, "n_prep");
+    QDC_REQUIRE(n_prep == 0 || (h_prep_qubits && h_code_table && n_codes >= 1 && n_codes <= MAX_CODES),
+                "preparation table");
+    QDC_REQUIRE(prog->ops.empty() || (prog->d_ops && prog->d_mats), "program has no device copy (compiled without a GPU)");
+    QDC_REQUIRE(prog->mats.empty() || d_matrices != nullptr, "matrix workspace");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int n_mats = (int)prog->mats.size();
+    if (n_mats > 0) {
+        for (const MatDesc& md : prog->mats)
+            QDC_REQUIRE(md.slot < n_params && (md.slot < 0 || d_params != nullptr), "parameter slot out of range");
+        const long long total = n_sets * n_mats;
+        sv_matrix_kernel<<<(unsigned)((total + 127) / 128), 128, 0, s>>>(prog->d_mats, n_mats, n_sets,
+                                                                         d_params, n_params, d_matrices);
+        QDC_CHECK_LAUNCH();
+    }
+    GroupArgs a;
+    memset(&a, 0, sizeof(a));
+    a.state = (double2*)d_state;
+    a.ops = prog->d_ops;
+    a.mats = d_matrices;
+    a.n = prog->n; a.t = prog->t;
+    a.n_tiles = 1ll << (prog->n - prog->t);
+    a.init_lo = init_lo;
+    a.n_sets = (int)n_sets; a.n_mats = n_mats;
+    a.n_prep = n_prep; a.n_codes = n_prep ? n_codes : 1;
+    for (int j = 0; j < n_prep; ++j) {
+        QDC_REQUIRE(h_prep_qubits[j] >= 0 && h_prep_qubits[j] < prog->n, "prep qubit");
+        QDC_REQUIRE(!((a.prep_mask >> h_prep_qubits[j]) & 1ull), "duplicate prep qubit");
+        a.prep_q[j] = (uint8_t)h_prep_qubits[j];
+        a.prep_mask |= 1ull << h_prep_qubits[j];
+    }
+    if (n_prep)
+        for (int k = 0; k < n_codes; ++k)
+            for (int e = 0; e < 4; ++e) a.code[k][e] = h_code_table[4 * k + e];
+    const long long n_batch = n_init * n_sets;
+    const long long grid = n_batch * a.n_tiles;
+    QDC_REQUIRE(grid < (1ll << 31), "batch * tiles exceeds one grid: split the batch");
+    const size_t smem = (size_t)16 << prog->t;
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int threads = 1 << (prog->t > 1 ? prog->t - 1 : 0);
+    if (threads > 512) threads = 512;
+    if (threads < 32) threads = 32;
+    for (size_t g = 0; g < prog->groups.size(); ++g) {
+        const Group& gr = prog->groups[g];
+        a.op_lo = gr.first_op; a.op_hi = gr.first_op + gr.n_ops;
+        a.first = g == 0;
+        a.n_runs = gr.n_runs;
+        for (int r = 0; r < gr.n_runs; ++r) { a.run_pos[r] = gr.run_pos[r]; a.run_len[r] = gr.run_len[r]; }
+        sv_group_kernel<<<(unsigned)grid, threads, smem, s>>>(a);
+        QDC_CHECK_LAUNCH();
+    }
+    return QDC_OK;
+}
+
+extern "C" int qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t flip_mask,
+                            double* d_probs, void* stream) {
+    QDC_REQUIRE(d_state && d_probs, "null buffer");
+    QDC_REQUIRE(n_qubits >= 1 && n_qubits <= 40 && n_batch >= 1, "shape");
+    QDC_REQUIRE((flip_mask >> n_qubits) == 0, "flip_mask");
+    const long long total = n_batch << n_qubits;
+    long long blocks = (total + 255) / 256;
+    const long long cap = (long long)qdc_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    sv_probs_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const double2*)d_state, n_qubits,
+                                                                       total, flip_mask, d_probs);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets,
+                                   uint64_t flip_mask, int n_prep, int n_codes, const double* h_frame,
+                                   const int32_t* h_meas_qubits, int n_meas,
+                                   const int64_t* h_axis_stride, double* d_T, int64_t ld, void* stream) {
+    QDC_REQUIRE(d_state && d_T, "null buffer");
+    QDC_REQUIRE(n_qubits >= 1 && n_qubits <= 40 && n_sets >= 1, "shape");
+    QDC_REQUIRE(n_prep >= 0 && n_meas >= 0 && n_meas <= 6 && n_prep + n_meas <= 6, "at most 6 cut axes per fragment");
+    QDC_REQUIRE(n_meas <= n_qubits, "n_meas");
+    QDC_REQUIRE(n_prep == 0 || (n_codes == 4 && h_frame != nullptr), "4 preparation states and their frame required");
+    QDC_REQUIRE(n_meas == 0 || h_meas_qubits != nullptr, "meas qubits");
+    QDC_REQUIRE((flip_mask >> n_qubits) == 0, "flip_mask");
+    TensorArgs a;
+    memset(&a, 0, sizeof(a));
+    a.state = (const double2*)d_state; a.T = d_T;
+    a.n_sets = n_sets; a.n = n_qubits; a.n_prep = n_prep; a.n_meas = n_meas; a.flip = flip_mask;
+    a.n_b = 1ll << (n_qubits - n_meas);
+    const int n_axes = n_prep + n_meas;
+    const long long n_kappa = 1ll << (2 * n_axes);
+    QDC_REQUIRE(ld >= n_kappa, "ld");
+    uint64_t mm = 0;
+    for (int j = 0; j < n_meas; ++j) {
+        QDC_REQUIRE(h_meas_qubits[j] >= 0 && h_meas_qubits[j] < n_qubits && !((mm >> h_meas_qubits[j]) & 1ull), "meas qubit");
+        mm |= 1ull << h_meas_qubits[j];
+        a.meas_q[j] = (uint8_t)h_meas_qubits[j];
+    }
+    for (int q = 0; q < n_qubits;) {              // runs of measured positions = holes of the b deposit
+        if (!((mm >> q) & 1ull)) { ++q; continue; }
+        int e = q;
+        while (e < n_qubits && ((mm >> e) & 1ull)) ++e;
+        a.run_pos[a.n_runs] = (uint8_t)q; a.run_len[a.n_runs] = (uint8_t)(e - q);
+        ++a.n_runs;
+        q = e;
+    }
+    long long nat = n_kappa;
+    for (int ax = 0; ax < n_axes; ++ax) {
+        nat /= 4;
+        a.stride[ax] = h_axis_stride ? h_axis_stride[ax] : nat;
+        QDC_REQUIRE(a.stride[ax] >= 0 && 3 * a.stride[ax] < ld, "axis stride");
+    }
+    if (n_prep) for (int k = 0; k < 16; ++k) a.frame[k] = h_frame[k];
+    int bb = (int)(2048 / n_kappa);
+    if (bb < 1) bb = 1;
+    if (bb > a.n_b) bb = (int)a.n_b;
+    a.bb = bb;
+    const size_t n_s = (size_t)1 << (2 * n_prep), n_mu = (size_t)1 << n_meas;
+    const size_t smem = (size_t)bb * n_s * n_mu * 16 + (size_t)bb * n_kappa * 8;
+    QDC_REQUIRE(smem <= 200 * 1024, "shared memory");
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_pauli_tensor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long gx = (a.n_b + bb - 1) / bb;
+    QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
+    a.ld = ld;
+    dim3 grid((unsigned)gx, (unsigned)n_sets);
+    sv_pauli_tensor_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(a);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}

@@ -40,9 +40,10 @@ class MisTables:
 
 
 def build_tables(row_bits: int, col_bits: int, bitpos: Sequence[int], adj: Sequence[int],
-                 node_mask: int, device=None, stream=None) -> MisTables:
+                 node_mask: int, device=None, stream=None, index_flip: int = 0) -> MisTables:
     """bitpos[b] = full-circuit wire of united bit b (b < col_bits: column bits);
-    adj[i] = neighbour mask of wire i; node_mask = wires that are graph nodes."""
+    adj[i] = neighbour mask of wire i; node_mask = wires that are graph nodes;
+    index_flip: entry u of the scored array holds united index u ^ index_flip."""
     lib = _lib.load()
     dev = _dev(device)
     nb = row_bits + col_bits
@@ -58,7 +59,8 @@ def build_tables(row_bits: int, col_bits: int, bitpos: Sequence[int], adj: Seque
     h_adj = (C.c_uint64 * max(n_wires, 1))(*[int(a) for a in adj])
     with torch.cuda.device(dev):
         _lib.check(lib.qdc_mis_build_tables(row_bits, col_bits, h_bitpos, h_adj, n_wires,
-                                            C.c_uint64(node_mask), _lib.ptr(row_x),
+                                            C.c_uint64(node_mask), C.c_uint64(index_flip),
+                                            _lib.ptr(row_x),
                                             _lib.ptr(row_forb), _lib.ptr(row_wok),
                                             _lib.ptr(col_x), _lib.ptr(col_wok),
                                             _lib.stream_ptr(stream)), "qdc_mis_build_tables")
@@ -201,13 +203,20 @@ def _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp):
 
 def reduce_and_score(P: torch.Tensor, tables: MisTables, threshold: float = 1e-5, k: int = 1,
                      norm: Optional[torch.Tensor] = None, row_lo: int = 0,
-                     cand_cap: Optional[int] = None, stream=None) -> ScoreResult:
-    """Score a materialised slab P[n_rows, 2^col_bits] (united order; float64 or float32)."""
+                     cand_cap: Optional[int] = None, stream=None,
+                     amplitudes: bool = False) -> ScoreResult:
+    """Score a materialised slab P[n_rows, 2^col_bits] (united order; float64 or float32).
+    amplitudes=True: P is a float64 view of complex128 amplitudes (re, im interleaved, e.g.
+    `torch.view_as_real(states)`), scored as |amp|^2 without materialising probabilities."""
     lib = _lib.load()
     dev = P.device
     assert P.is_contiguous() and P.dtype in (torch.float64, torch.float32)
     N = 1 << tables.col_bits
-    P2 = P.reshape(-1, N)
+    if amplitudes:
+        assert P.dtype == torch.float64
+        P2 = P.reshape(-1, N, 2)
+    else:
+        P2 = P.reshape(-1, N)
     n_rows = P2.shape[0]
     if cand_cap is None:
         cand_cap = _default_cap(n_rows * N, threshold)
@@ -220,7 +229,8 @@ def reduce_and_score(P: torch.Tensor, tables: MisTables, threshold: float = 1e-5
     sp = _lib.stream_ptr(stream)
     with torch.cuda.device(dev):
         _lib.check(lib.qdc_mis_reduce(
-            _lib.ptr(P2), 0 if P.dtype == torch.float64 else 1, row_lo, n_rows, N,
+            _lib.ptr(P2), 2 if amplitudes else (0 if P.dtype == torch.float64 else 1), row_lo,
+            n_rows, N,
             _lib.ptr(norm), threshold, _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb),
             _lib.ptr(tables.row_wok), _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok),
             _lib.ptr(sums), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),

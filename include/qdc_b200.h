@@ -49,16 +49,18 @@ int         qdc_device_info(int* sm_count, int* cc_major, int* cc_minor);
  * d_row_forb[r] = OR of adj over the nodes set in row r; d_row_wok[r], d_col_wok[c] =
  * weight | (self-independent << 8).  Then for u=(r,c):
  *   x = row_x|col_x, weight = w_r + w_c, indset = ok_r & ok_c & !(col_x & row_forb).
+ * index_flip: entry u of the scored array holds united index u ^ index_flip (the flip frame of
+ * the statevector engine, qdc_sv_info); 0 for the contraction.
  */
 int qdc_mis_build_tables(int row_bits, int col_bits, const int* h_bitpos,
                          const uint64_t* h_adj, int n_wires, uint64_t node_mask,
-                         uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
+                         uint64_t index_flip, uint64_t* d_row_x, uint64_t* d_row_forb, uint32_t* d_row_wok,
                          uint64_t* d_col_x, uint32_t* d_col_wok, void* stream);
 
 /* ---- K8: fused MIS reduction over a materialised distribution -----------------------------
  * Replaces strip_ancillas + avg_cost + the p > threshold filter of top_probs
  * (mis.py:114, 125-126, 232).  d_P is rows x cols (row-major, united order), dtype 0 = f64,
- * 1 = f32; rows [row_lo, row_lo+n_rows) of the table are used (slab owned by this GPU).
+ * 1 = f32, 2 = complex128 amplitudes scored as |amp|^2 (the uncut cost f(params), mis.py:639-665); rows [row_lo, row_lo+n_rows) of the table are used (slab owned by this GPU).
  * Every entry is first divided by *d_norm (device scalar, NULL = 1; the combined_norm of
  * qsplit_mlrecon_methods.py:471-472) so no host synchronisation is needed between the two.
  * d_sums[0..2] += (sum p, sum p*weight*indset, sum p*weight); entries with p > threshold are
@@ -81,6 +83,103 @@ int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_t n_rows, i
 int qdc_topk_select(const uint64_t* d_cand_x, double* d_cand_p,
                     const unsigned long long* d_cand_count, int64_t cand_cap, int k,
                     uint64_t* d_top_x, double* d_top_p, void* stream);
+
+/* ---- K1-K3: batched statevector engine -----------------------------------------------------
+ * Replaces the simulator the reference reaches through qiskit.execute(circuits, backend, shots)
+ * (qsplit/qsplit_mlrecon_methods.py:20-42; mis.py:649) for the gate set its ansatz modules emit
+ * (ansatz/dqv_cut_ansatz.py:127-171, ansatz/qaoa_plus.py:8-37) and for the tomography
+ * preparation / basis-change gates of partial_tomography (qsplit_mlrecon_methods.py:116-162).
+ *
+ * Every gate of that set is "a 2x2 on one target, applied where the control qubits have given
+ * values": x/h/s/sdg/rx/ry/rz/u1/u3 (no controls), cx/mcx/crx/cz (controls = 1) and the
+ * open-controlled partial mixer (controls = 0).  The multi-qubit `Id` is a no-op.
+ * angle = scale * params[set][param_slot] + offset (param_slot < 0: angle = offset).
+ */
+#define QDC_G_ID   0
+#define QDC_G_X    1
+#define QDC_G_Y    2
+#define QDC_G_Z    3
+#define QDC_G_H    4
+#define QDC_G_S    5
+#define QDC_G_SDG  6
+#define QDC_G_T    7
+#define QDC_G_TDG  8
+#define QDC_G_RX   9
+#define QDC_G_RY   10
+#define QDC_G_RZ   11
+#define QDC_G_U1   12
+#define QDC_G_U2   13   /* explicit constant 2x2 in m[] (u3 with bound angles, SIC preparations) */
+
+typedef struct qdc_gate {
+    int32_t  kind;        /* QDC_G_* */
+    int32_t  target;      /* qubit the 2x2 acts on */
+    uint64_t ctrl_mask;   /* control qubits (bit q <-> qubit q) */
+    uint64_t ctrl_val;    /* required control values, subset of ctrl_mask */
+    int32_t  param_slot;  /* column of the parameter table, or -1 */
+    int32_t  reserved;
+    double   scale, offset;
+    double   m[8];        /* QDC_G_U2: row-major (re, im) of [[m00, m01], [m10, m11]] */
+} qdc_gate;
+
+typedef struct qdc_sv_program qdc_sv_program;   /* opaque: compiled gate schedule */
+
+/* Host-side compilation (no device work except one small upload):
+ *   1. X gates are absorbed into a per-qubit flip frame (control values toggle, targets are
+ *      conjugated); what is left of the frame at the end is returned as `flip_mask`:
+ *      amplitude of basis state x is stored at index x ^ flip_mask.
+ *   2. with QDC_SV_FUSE_ANCILLA, mcx(C -> a) . G(a -> q) . mcx(C -> a) on an ancilla `a` known
+ *      to be |0> becomes G on q controlled by C (the reference's partial mixer,
+ *      ansatz/dqv_cut_ansatz.py:127-151); `zero_mask` = qubits that start in |0>.
+ *   3. gates are list-scheduled (respecting commutation) into groups whose non-diagonal targets
+ *      fit a tile of 2^tile_bits amplitudes held in shared memory; the tile always contains the
+ *      `coalesce_bits` lowest qubits so global accesses are contiguous runs.
+ * tile_bits <= 0 selects the default (min(n_qubits, 12)); tile_bits is clamped to n_qubits. */
+#define QDC_SV_FUSE_ANCILLA 1
+int  qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, uint64_t zero_mask,
+                    int tile_bits, int coalesce_bits, int flags, qdc_sv_program** out);
+void qdc_sv_free(qdc_sv_program* prog);
+/* any pointer may be NULL */
+int  qdc_sv_info(const qdc_sv_program* prog, int* n_qubits, int* n_groups, int* n_ops,
+                 int* n_matrices, int* tile_bits, uint64_t* flip_mask);
+/* Schedule dump for host-side tests: group_first_op[n_groups + 1], group_local_mask[n_groups],
+ * and per op: op_kind (0 general, 1 diagonal), op_target, op_ctrl_mask, op_ctrl_val (full-index
+ * masks), op_src_gate (index into the input list of the gate that supplies the matrix) and
+ * op_conj_x (1: the matrix is X.M.X). */
+int  qdc_sv_dump(const qdc_sv_program* prog, int32_t* group_first_op, uint64_t* group_local_mask,
+                 int32_t* op_kind, int32_t* op_target, uint64_t* op_ctrl_mask,
+                 uint64_t* op_ctrl_val, int32_t* op_src_gate, int32_t* op_conj_x);
+
+/* Run the program on a batch of states.  Batch element b = init * n_sets + set, init in
+ * [0, n_init), uses parameter row `set` and the initial product state number init_lo + init:
+ * qubit h_prep_qubits[j] starts in the 2-vector h_code_table[digit_j] (re0, im0, re1, im1), digit_j
+ * = the j-th most significant base-n_codes digit of (init_lo + init) -- itertools.product order of
+ * the SIC / cutqc preparation labels (qsplit_mlrecon_methods.py:148; cutqc/evaluator.py:34-67);
+ * all other qubits start in |0>.  d_state: [n_init * n_sets][2^n_qubits] complex128 (written).
+ * d_matrices: workspace of n_sets * n_matrices * 8 doubles. */
+int  qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int64_t n_init,
+                int64_t n_sets, const double* d_params, int n_params,
+                const int32_t* h_prep_qubits, int n_prep, const double* h_code_table, int n_codes,
+                double* d_matrices, void* stream);
+
+/* p[b][x] = |amp_b(x)|^2, undoing the flip frame: d_probs[b * 2^n + x] (float64). */
+int  qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t flip_mask,
+                  double* d_probs, void* stream);
+
+/* ---- K3 + K4: fragment tensor in the Pauli basis straight from the amplitudes ---------------
+ * Replaces, in the exact (infinite-shot) limit, the 3^m measurement variants + organize +
+ * least-squares inversion + Choi reshaping of qsplit_mlrecon_methods.py:116-317, 428-440 (and
+ * cutqc's measure.c / vertical_collapse.c basis change, cutqc/post_process.py:20-30):
+ *   T[set][b][kappa] = sum_s prod_j frame[a_j][s_j] * <psi_{s,set}| Pi_b (x) P_(a') |psi_{s,set}>
+ * b = value of the non-measured qubits (ascending qubit order), a = Pauli index (I, X, Y, Z) per
+ * cut axis, prep axes first (order of h_prep_qubits used in qdc_sv_run) then meas axes
+ * (h_meas_qubits); kappa = sum_axis a_axis * h_axis_stride[axis].  h_frame[a * n_codes + s] are the
+ * expansion coefficients of Pauli a in the preparation projectors.  d_state holds
+ * n_codes^n_prep * n_sets states laid out as by qdc_sv_run (init_lo = 0).
+ * d_T: [n_sets][2^(n_qubits - n_meas)][ld] float64, ld >= 4^(n_prep + n_meas). */
+int  qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets, uint64_t flip_mask,
+                         int n_prep, int n_codes, const double* h_frame,
+                         const int32_t* h_meas_qubits, int n_meas, const int64_t* h_axis_stride,
+                         double* d_T, int64_t ld, void* stream);
 
 /* ---- K5: two-operand contraction over the cut-basis index ---------------------------------
  * Replaces the itertools.product loop of _recombine_using_networks

@@ -7,6 +7,8 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+if os.path.dirname(os.path.abspath(__file__)) not in sys.path:
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))   # test helper modules
 importlib.import_module("dqva-and-circuit-cutting_b200")   # registers the `qdc_b200` alias
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")

@@ -1,0 +1,155 @@
+"""GPU parity of the statevector engine (csrc/statevec.cu) against the numpy oracle
+(oracle/statevector.py, oracle/qsplit_oracle.py) on seeded circuits.  Tolerance 1e-10 max-abs on
+amplitudes / probabilities / tensor entries (north_star FP64 bar); the index bookkeeping (flip
+frame, tile <-> full index maps, batch order) is exact by construction of the comparison."""
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import qsplit_oracle as qo
+from oracle import statevector as sv
+from test_sv_compiler import _faithful_mixer, _random_circuit
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _backend(cuda, **kw):
+    from qdc_b200.engine import B200Backend
+    return B200Backend(device=cuda, **kw)
+
+
+def _unflip(states, flip):
+    idx = np.arange(states.shape[-1]) ^ flip
+    return states[..., idx]
+
+
+@pytest.mark.parametrize("n,tile_bits,coalesce,seed", [
+    (3, 0, -1, 0), (6, 3, 1, 1), (8, 4, 2, 2), (10, 0, -1, 3), (12, 12, 4, 4), (13, 13, 4, 5),
+    (14, 12, 4, 6), (14, 7, 3, 7), (16, 12, 5, 8), (11, 5, 0, 9), (1, 0, -1, 10),
+])
+def test_random_circuits_match_oracle(cuda, n, tile_bits, coalesce, seed):
+    rng = np.random.default_rng(seed)
+    insts = _random_circuit(rng, n, 80)
+    be = _backend(cuda, tile_bits=tile_bits, coalesce_bits=coalesce)
+    prog, auto = be.compile_instructions(n, insts)
+    states = be.run(prog, auto)
+    want = sv.simulate(n, insts)
+    got = _unflip(states.cpu().numpy(), prog.flip_mask)[0]
+    assert np.abs(got - want).max() < TOL
+    probs = be.probabilities(states, prog).cpu().numpy()[0]
+    assert np.abs(probs - sv.probabilities(want)).max() < TOL
+
+
+def test_parameter_sets_and_prep_variants(cuda):
+    """batch = prep variant x parameter set; symbolic angles come from the parameter table."""
+    from qdc_b200.circuit import Parameter
+    from qdc_b200.engine import SIC_KETS
+    n, prep = 9, [2, 7]
+    rng = np.random.default_rng(3)
+    pars = [Parameter(f"var_{i}") for i in range(4)]
+    insts = [("x", (0,), (), None)]
+    insts.append(("zcrx", (0, 1, 3), (2 * pars[0],), None))
+    insts.append(("rx", (2,), (pars[1],), None))
+    insts.append(("h", (5,), (), None))
+    insts.append(("crx", (2, 7), (2 * pars[2],), None))
+    insts.append(("zcrx", (7, 8, 6), (2 * pars[3],), None))
+    insts.append(("rz", (7,), (pars[1] / 2,), None))
+    insts.append(("rz", (2,), (-1 * pars[1] / 2,), None))
+    insts.append(("cx", (5, 4), (), None))
+    insts.append(("ry", (4,), (0.3,), None))
+    be = _backend(cuda, tile_bits=5, coalesce_bits=2)
+    prog, auto = be.compile_instructions(n, insts, param_order=pars, zero_mask=((1 << n) - 1) & ~0b10000100)
+    table = rng.uniform(0, 2 * np.pi, size=(3, 4))
+    states = be.run(prog, auto, params=table, prep_qubits=prep)
+    assert states.shape == (16 * 3, 1 << n)
+    got = _unflip(states.cpu().numpy(), prog.flip_mask)
+    for v, (c0, c1) in enumerate(itertools.product(range(4), repeat=2)):
+        init = np.zeros(1 << n, dtype=complex)
+        for b0 in range(2):
+            for b1 in range(2):
+                init[(b0 << prep[0]) | (b1 << prep[1])] = SIC_KETS[c0][b0] * SIC_KETS[c1][b1]
+        for s in range(3):
+            bound = [(nm, qs, tuple(p.bind(table[s][pars.index(p.param)]) if hasattr(p, "bind") else p
+                                    for p in ps), mt) for nm, qs, ps, mt in insts]
+            want = sv.simulate(n, bound, init=init)
+            assert np.abs(got[v * 3 + s] - want).max() < TOL, (v, s)
+
+
+def test_gate_faithful_mixers_equal_fused(cuda):
+    rng = np.random.default_rng(5)
+    n, anc = 12, 11
+    faithful, fused = [("x", (3,), (), None)], [("x", (3,), (), None)]
+    for q in range(11):
+        nb = [int(v) for v in rng.choice([k for k in range(11) if k != q], size=3, replace=False)]
+        a = float(rng.uniform(0, 2 * np.pi))
+        _faithful_mixer(faithful, nb, anc, q, a)
+        fused.append(("zcrx", tuple(nb) + (q,), (2 * a,), None))
+    for be in (_backend(cuda, tile_bits=6, fuse_ancilla=True), _backend(cuda, tile_bits=6, fuse_ancilla=False)):
+        prog, auto = be.compile_instructions(n, faithful)
+        got = _unflip(be.run(prog, auto).cpu().numpy(), prog.flip_mask)[0]
+        assert np.abs(got - sv.simulate(n, fused)).max() < TOL
+
+
+@pytest.mark.parametrize("n,prep,meas,tile_bits,seed", [
+    (6, [1], [4], 0, 0), (8, [], [2, 6], 4, 1), (8, [0, 5], [], 4, 2), (9, [3, 8], [1, 6], 5, 3),
+    (10, [2], [0, 9, 4], 12, 4), (7, [], [], 3, 5), (13, [], [12, 3, 7, 9], 13, 6),
+    (11, [10, 0, 4, 6], [], 6, 7),
+])
+def test_pauli_tensor_matches_oracle(cuda, n, prep, meas, tile_bits, seed):
+    """K3+K4 fused: tensor straight from amplitudes == oracle's 3^m measured variants combined
+    with signs and the SIC frame inverse (oracle.fragment_pauli_tensor)."""
+    rng = np.random.default_rng(seed)
+    insts = _random_circuit(rng, n, 50)
+    be = _backend(cuda, tile_bits=tile_bits)
+    zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in prep)
+    prog, auto = be.compile_instructions(n, insts, zero_mask=zero_mask)
+    states = be.run(prog, auto, prep_qubits=prep)
+    T = be.pauli_tensor(states, prog, 1, len(prep), meas).cpu().numpy()[0]
+    R = qo.fragment_pauli_tensor((n, insts), prep, meas)
+    assert T.shape == (1 << (n - len(meas)), 4 ** (len(prep) + len(meas)))
+    assert np.abs(T - R.reshape(T.shape)).max() < TOL
+
+
+def test_pauli_tensor_strides_and_sets(cuda):
+    rng = np.random.default_rng(9)
+    n, prep, meas = 7, [5], [2, 0]
+    insts = [(nm, qs, ps, mt) for nm, qs, ps, mt in _random_circuit(rng, n, 40)]
+    be = _backend(cuda, tile_bits=4)
+    prog, auto = be.compile_instructions(n, insts, zero_mask=((1 << n) - 1) & ~(1 << 5))
+    states = be.run(prog, auto, params=np.zeros((2, 0)), prep_qubits=prep)
+    strides = [1, 16, 4]                                   # axis order (prep0, meas0, meas1) -> custom layout
+    T = be.pauli_tensor(states, prog, 2, 1, meas, axis_strides=strides, ld=64).cpu().numpy()
+    R = qo.fragment_pauli_tensor((n, insts), prep, meas)   # [b, a_prep, a_m0, a_m1]
+    want = np.zeros((1 << (n - 2), 64))
+    for a0, a1, a2 in itertools.product(range(4), repeat=3):
+        want[:, a0 * 1 + a1 * 16 + a2 * 4] = R[:, a0, a1, a2]
+    assert np.abs(T[0] - want).max() < TOL and np.abs(T[1] - want).max() < TOL
+
+
+def test_amplitude_scoring_matches_oracle(cuda):
+    """Uncut cost f(params) (mis.py:639-665): sum p * popcount straight from amplitudes, with the
+    flip frame folded into the scoring tables."""
+    import networkx as nx
+    from oracle import mis_oracle as mo
+    from qdc_b200 import recombine as rc
+    n = 12
+    rng = np.random.default_rng(2)
+    insts = _random_circuit(rng, n, 70)
+    be = _backend(cuda, tile_bits=7)
+    prog, auto = be.compile_instructions(n, insts)
+    states = be.run(prog, auto)
+    G = nx.random_regular_graph(3, n - 1, seed=1) if (n - 1) % 2 == 0 else nx.path_graph(n - 1)
+    adj = [int(a) for a in mo.adjacency_masks(G, n - 1)] + [0]      # top wire = ancilla
+    tabs = rc.build_tables(6, 6, list(range(n)), adj, (1 << (n - 1)) - 1, device=cuda,
+                           index_flip=prog.flip_mask)
+    res = rc.reduce_and_score(torch.view_as_real(states[0]).reshape(-1), tabs, k=3, amplitudes=True).get()
+    p = sv.probabilities(sv.simulate(n, insts))
+    s_p, s_pwok = mo.score_array(p, n - 1, 1, np.array(adj[:n - 1], dtype=np.uint64), masked=True)
+    _, s_pw = mo.score_array(p, n - 1, 1, np.array(adj[:n - 1], dtype=np.uint64), masked=False)
+    assert abs(res["sum_p"] - s_p) < TOL and abs(res["sum_pw_indset"] - s_pwok) < TOL
+    assert abs(res["sum_pw"] - s_pw) < TOL
+    order = np.lexsort((np.arange(p.size), -p))[:3]
+    assert [x for x, _ in res["top"]] == [int(i) for i in order if p[i] > 1e-5]
