@@ -63,18 +63,22 @@ def simple_choose_nodes(graph: nx.Graph, partition: List[List[int]],
 
 
 def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely",
-                     verbose=0):
-    """Simulate a fragmented circuit and recombine: returns {bitstring: probability}.
+                     verbose=0, params=None, param_order=None, threshold=1e-5, topk=1,
+                     store=None):
+    """Simulate a fragmented circuit and recombine (utils/cutting_funcs.py:167-205).
 
-    `backend` must be a `qdc_b200.engine.B200Backend`; `frag_shots` is accepted for signature
-    compatibility (the engine evaluates the infinite-shot limit: exact variant probabilities
-    stand in for counts).
-    """
+    Returns the recombined distribution as a Mapping `{bitstring: probability}` that keeps the
+    device array and, when `backend.graph` is set, the fused MIS objective / top-k (`.score`).
+    `backend` must be a `qdc_b200.engine.B200Backend`; `frag_shots` only scales the dict views
+    (the engine evaluates the infinite-shot limit).  Extensions: `params`
+    [n_sets, n_params] + `param_order` evaluate a batch of parameter vectors of unbound fragments
+    in one pass and return a list of distributions."""
     from ..qsplit import qsplit_mlrecon_methods as qmm
 
     t0 = time.time()
     frag_data = qmm.collect_fragment_data(fragments, wire_path_map, shots=frag_shots,
-                                          tomography_backend=backend)
+                                          tomography_backend=backend, params=params,
+                                          param_order=param_order)
     direct_models = qmm.direct_fragment_model(frag_data)
     if mode == "direct":
         models = direct_models
@@ -85,7 +89,8 @@ def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely
     model_time = time.time() - t0
 
     t1 = time.time()
-    recombined_dist = qmm.recombine_fragment_models(models, wire_path_map)
+    recombined_dist = qmm.recombine_fragment_models(models, wire_path_map, backend=backend,
+                                                    threshold=threshold, topk=topk, store=store)
     recombine_time = time.time() - t1
     if verbose:
         print(f"\tModel time: {model_time:.3f}, Recombine time: {recombine_time:.3f}")

@@ -1,0 +1,142 @@
+"""GPU parity of the qsplit path end to end (collect -> model -> recombine -> MIS score) through
+the reference-named API, against the oracle restatement and the uncut statevector.  1e-10 max-abs
+on probabilities / costs, bit-exact keys and top-k bitstrings."""
+import networkx as nx
+import numpy as np
+import pytest
+import torch
+
+from oracle import mis_oracle as mo
+from oracle import qsplit_oracle as qo
+from oracle import statevector as sv
+from test_oracle_golden import _cut_dqva, _ghz3
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _be(cuda, **kw):
+    from qdc_b200.engine import B200Backend
+    return B200Backend(device=cuda, **kw)
+
+
+@pytest.mark.parametrize("mode", ["direct", "likely"])
+def test_reference_test_cutting_known_answer(cuda, mode):
+    """test_cutting.py:7-40 of the reference: {000: 0.5, 111: 0.5}."""
+    from qdc_b200.qsplit import qsplit_circuit_cutter as qcc
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    circ, cuts = _ghz3()
+    frags, wpm = qcc.cut_circuit(circ, cuts)
+    dist = sim_with_cutting(frags, wpm, 1000, _be(cuda), mode=mode)
+    assert abs(dist["000"] - 0.5) < TOL and abs(dist["111"] - 0.5) < TOL
+    assert all(abs(v) < TOL for k, v in dist.items() if k not in ("000", "111"))
+    with pytest.raises(Exception):
+        sim_with_cutting(frags, wpm, 1000, _be(cuda), mode="bogus")
+
+
+def test_stage_dict_views_match_oracle(cuda):
+    """collect_fragment_data / direct_fragment_model / maximum_likelihood_model as Mappings have
+    the reference's layouts and the oracle's numbers (counts = shots * probability)."""
+    from qdc_b200.qsplit import qsplit_mlrecon_methods as qmm
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4)])
+    _, _, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5]], 2, 1, False)     # gate-faithful
+    shots = 4096
+    data = qmm.collect_fragment_data(frags, wpm, shots=shots, tomography_backend=_be(cuda, tile_bits=4))
+    want = qo.collect_fragment_data(frags, wpm, drop_below=0.0)
+    for got_f, want_f in zip(data, want):
+        # outcomes whose exact probability is 0 up to rounding may or may not have a key
+        for bits, row in want_f.items():
+            if max(row.values()) < 1e-14:
+                continue
+            assert bits in got_f
+            for lab, v in row.items():
+                assert abs(got_f[bits][lab] / shots - v) < TOL
+    direct = qmm.direct_fragment_model(data)
+    want_direct = qo.direct_fragment_model(want)
+    for got_f, want_f in zip(direct, want_direct):
+        for bits, block in want_f.items():
+            if np.abs(block).max() < 1e-14:
+                continue
+            assert np.abs(got_f[bits] / shots - block).max() < TOL
+    # counts-dict entry point (one GEMM with the folded pseudo-inverse) == kernel path
+    from_counts = qmm.direct_fragment_model({k: dict(v) for k, v in data[0].items()})
+    for bits, block in direct[0].items():
+        assert np.abs(from_counts[bits] - block).max() < 1e-8 * shots
+    likely = qmm.maximum_likelihood_model(direct)
+    want_likely = qo.maximum_likelihood_model(want_direct)
+    for got_f, want_f in zip(likely, want_likely):
+        for bits, block in want_f.items():
+            if np.abs(block).max() < 1e-12:
+                continue
+            assert np.abs(got_f[bits] / shots - block).max() < 1e-9
+
+
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("max_cuts,seed", [(1, 0), (2, 1), (2, 5)])
+def test_cut_dqva_matches_uncut_and_oracle(cuda, fused, max_cuts, seed):
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4)])
+    circ, cuts, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5]], max_cuts, seed, fused)
+    N = circ.num_qubits
+    full = sv.probabilities(sv.simulate(N, circ.to_instructions()))
+    be = _be(cuda, graph=G, tile_bits=3)
+    dist = sim_with_cutting(frags, wpm, 1, be, mode="likely", topk=4)
+    assert np.abs(dist.P.cpu().numpy() - full).max() < TOL
+    want = qo.sim_with_cutting(frags, wpm, mode="likely")
+    for k, v in want.items():
+        assert abs(dist.get(k, 0.0) - v) < TOL
+    n = G.number_of_nodes()
+    s_p, s_pwok = mo.score_array(full, n, 2, mo.adjacency_masks(G, n))
+    out = dist.score.get()
+    assert abs(out["sum_p"] - 1) < TOL and abs(out["sum_pw_indset"] - s_pwok) < TOL
+    cost = mo.avg_cost(mo.strip_ancillas(dict(dist), 2), G)            # the reference's own loop
+    assert abs(-cost - out["sum_pw_indset"]) < TOL
+    idx = np.nonzero(full > 1e-5)[0]
+    order = idx[np.lexsort((idx, -full[idx]))][:4]
+    assert [x for x, _ in out["top"]] == [int(i) for i in order]
+
+
+def test_three_fragments(cuda):
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 7), (7, 8), (0, 2),
+                      (3, 5), (6, 8)])
+    circ, cuts, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5], [6, 7, 8]], 2, 3, True)
+    N = circ.num_qubits
+    full = sv.probabilities(sv.simulate(N, circ.to_instructions()))
+    dist = sim_with_cutting(frags, wpm, 1, _be(cuda, graph=G), mode="direct")
+    assert np.abs(dist.P.cpu().numpy() - full).max() < TOL
+
+
+def test_parameter_batch(cuda):
+    """Unbound fragments + a table of parameter vectors == one bound evaluation per row."""
+    import random
+    from qdc_b200.ansatz import dqv_cut_ansatz
+    from qdc_b200.circuit import Parameter
+    from qdc_b200.qsplit import qsplit_circuit_cutter as qcc
+    from qdc_b200.utils import graph_funcs
+    from qdc_b200.utils.cutting_funcs import simple_choose_nodes, sim_with_cutting
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4), (5, 6), (6, 7), (7, 4)])
+    partition = [[0, 1, 2], [3, 4, 5, 6, 7]]
+    random.seed(2); np.random.seed(2)
+    n = G.number_of_nodes()
+    subgraphs, cut_edges = graph_funcs.get_subgraphs(G, partition)
+    cut_nodes, hot_nodes = simple_choose_nodes(G, partition, cut_edges, 2)
+    order = [v for part in partition for v in part]
+    syms = [Parameter(f"var_{i}") for i in range(n + 1)]
+    circ, cuts = dqv_cut_ansatz.gen_dqva(G, partition, cut_nodes, hot_nodes, order, params=syms,
+                                         init_state="0" * n, fused=True)
+    frags, wpm = qcc.cut_circuit(circ, cuts)
+    used = circ.parameters
+    table = np.random.uniform(0, 2 * np.pi, size=(5, len(used)))
+    be = _be(cuda, graph=G, tile_bits=4)
+    dists = sim_with_cutting(frags, wpm, 1, be, mode="direct", params=table, param_order=used)
+    assert len(dists) == 5
+    N = circ.num_qubits
+    for row, dist in zip(table, dists):
+        bound = circ.bind_parameters(dict(zip(used, row)))
+        full = sv.probabilities(sv.simulate(N, bound.to_instructions()))
+        assert np.abs(dist.P.cpu().numpy() - full).max() < TOL
