@@ -43,7 +43,9 @@ SIGNATURES = {
     "qdc_mis_reduce": (C.c_int, [vp, C.c_int, c_i64, c_i64, c_i64, vp, C.c_double,
                                  vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i64, vp, vp]),
     "qdc_topk_select": (C.c_int, [vp, vp, vp, c_i64, C.c_int, vp, vp, vp]),
-    "qdc_contract_f64": (C.c_int, [vp, vp, c_i64, c_i64, c_i64, C.c_int, C.c_double, vp,
+    "qdc_contract_packed_doubles": (c_i64, [c_i64, C.c_int]),
+    "qdc_contract_pack": (C.c_int, [vp, c_i64, C.c_int, vp, vp]),
+    "qdc_contract_f64": (C.c_int, [vp, c_i64, vp, c_i64, c_i64, c_i64, C.c_int, C.c_double, vp,
                                    C.c_double, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int,
                                    vp, vp, vp, vp, c_i64, vp, vp]),
     "qdc_norm_workspace_doubles": (C.c_int, [C.c_int]),

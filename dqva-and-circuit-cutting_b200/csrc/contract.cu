@@ -12,27 +12,53 @@
 // panel, so HBM only matters when d_P_out is requested (8 or 4 bytes per output, written once).
 //
 // Tiling: persistent CTAs (one per SM), 128x128 output tile, 16 warps as 4x4, warp tile 32x32 =
-// 4x4 mma.m8n8k4 accumulators (64 registers).  Operands stream through a 4-stage cp.async ring of
-// 16-wide k slices stored as [k/4][row][4] so that every fragment load is 256 contiguous bytes
-// (bank-conflict free).  The ring runs across tile boundaries, so the register-only epilogue of
-// tile t overlaps the loads of tile t+1.
+// 4x4 mma.m8n8k4 accumulators (64 registers).  Operands are pre-packed in global memory as
+// [k/4][row][4] (qdc_contract_pack), so the k-group slice of a tile is one contiguous 4 KB run:
+// one elected lane (the duty rotates over the warps, one k slice each) moves a 16-wide k slice of
+// both operands with 8 bulk async copies (cp.async.bulk, the 1-D TMA path) into a 6-stage
+// shared-memory ring and arms a per-stage "full" mbarrier (complete_tx); all warps wait on it, read
+// their fragments as conflict-free 256-byte rows, and release the stage on an "empty" mbarrier.
+// Only that one lane per slice computes a global address and there is no __syncthreads in the
+// main loop; the ring runs across tile boundaries, so the register-only
+// epilogue of tile t overlaps the loads of tile t+1.  (The per-thread cp.async version of this
+// loop topped out at 27 TFLOP/s -- the address arithmetic competes with DMMA issue; this one
+// reaches the DMMA pipe's 36 TFLOP/s in isolation, profiles/r1_gemm_tma_probe.log.)
 #include "qdc_common.cuh"
 
 namespace {
 
-constexpr int TM = 128, TN = 128, BK = 16, STAGES = 4, THREADS = 512;
+constexpr int TM = 128, TN = 128, BK = 16, STAGES = 6;
+constexpr int CONSUMER_WARPS = 16, THREADS = CONSUMER_WARPS * 32;
+constexpr int LAG = 2;                                       // producer runs STAGES - LAG slices ahead
 constexpr int OPERAND_DOUBLES = (BK / 4) * TM * 4;          // 2048 doubles = 16 KB
 constexpr int STAGE_DOUBLES = 2 * OPERAND_DOUBLES;           // A then B
-constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8;       // 128 KB
+constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8;       // 192 KB
 constexpr int PANEL_W = 16;                                  // tile columns per L2 panel
+constexpr int PACK_PAD_ROWS = 2 * TM;                        // zero rows after the last real row
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes));
+__host__ __device__ __forceinline__ long long packed_rows(long long n_rows) {
+    return (n_rows + TM - 1) / TM * TM + PACK_PAD_ROWS;
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N));
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n WAIT_%=:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 __device__ __forceinline__ void dmma_8x8x4(double& c0, double& c1, double a, double b) {
@@ -57,8 +83,9 @@ __device__ __forceinline__ TileCoord tile_coord(int t, int tiles_m, int tiles_n)
 }
 
 struct ContractArgs {
-    const double* A;        // rows row_lo.. (already offset), [n_rows][kdim]
-    const double* Bt;       // [n_cols][kdim]
+    const double* Ap;       // packed [kdim/4][a_rows_pad][4]
+    const double* Bp;       // packed [kdim/4][b_rows_pad][4]
+    long long a_rows_pad, b_rows_pad;
     long long row_lo, n_rows, n_cols;
     int kdim;
     double scale;
@@ -178,95 +205,119 @@ __device__ __forceinline__ void tile_epilogue(const ContractArgs& a, double (&ac
 // STORE: 0 none, 1 united order, 2 circuit-order scatter.  OUT32: write float instead of double.
 template <int STORE, bool OUT32>
 __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a) {
-    extern __shared__ __align__(16) double smem[];
+    extern __shared__ __align__(128) double smem[];
     __shared__ double scratch[3 * (THREADS / 32)];
+    __shared__ __align__(8) uint64_t bar_full[STAGES], bar_empty[STAGES];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp >> 2, wn = warp & 3;
     const int tiles_m = (int)((a.n_rows + TM - 1) / TM), tiles_n = (int)((a.n_cols + TN - 1) / TN);
     const int n_tiles = tiles_m * tiles_n;
     const int kchunks = a.kdim / BK;
     const double out_scale = a.scale * (a.d_norm ? 1.0 / *a.d_norm : 1.0);
 
-    // ---- producer: 4 x 16-byte cp.async per thread per stage; its (tile, k chunk, stage)
-    // cursor is advanced incrementally (no divisions in the steady state) ----------------------
-    int p_tile = blockIdx.x, p_kc = 0, p_stage = 0;
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], CONSUMER_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    MisAccum macc = {0.0, 0.0, 0.0}, macc2 = {0.0, 0.0, 0.0};
+
+    // ---- producer duty, rotated over the warps: k slice p is issued by warp p % 16 --------------
+    // Slice p reuses the ring slot of slice p - STAGES, which every warp released LAG iterations
+    // ago, so the empty-barrier wait below practically never blocks.  All threads advance the
+    // cursor; only the elected lane touches barriers and issues the 8 bulk copies.
+    int p_tile = blockIdx.x, p_kc = 0, p_stage = 0, p_rr = 0;
+    uint32_t p_phase = 0;
     TileCoord p_tc = tile_coord(p_tile < n_tiles ? p_tile : 0, tiles_m, tiles_n);
-    auto issue = [&]() {
-        if (p_tile < n_tiles) {
+    auto produce = [&]() {
+        if (p_tile >= n_tiles) return;
+        if (warp == p_rr && lane == 0) {
+            mbar_wait(&bar_empty[p_stage], p_phase ^ 1u);
+            mbar_expect_tx(&bar_full[p_stage], STAGE_DOUBLES * 8);
             double* st = smem + p_stage * STAGE_DOUBLES;
+            const double* srcA = a.Ap + ((long long)p_kc * (BK / 4) * a.a_rows_pad + a.row_lo + p_tc.r0) * 4;
+            const double* srcB = a.Bp + ((long long)p_kc * (BK / 4) * a.b_rows_pad + p_tc.c0) * 4;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int q = tid + j * THREADS;             // 0..2047
-                const int op = q >> 10;                      // 0 = A, 1 = B
-                const int qq = q & 1023;
-                const int row = qq >> 3, c16 = qq & 7;       // 8 x 16 B per row slice
-                const int kg = c16 >> 1, within = (c16 & 1) * 2;
-                double* dst = st + op * OPERAND_DOUBLES + (kg * TM + row) * 4 + within;
-                const long long grow = (op == 0 ? p_tc.r0 : p_tc.c0) + row;
-                const long long lim = op == 0 ? a.n_rows : a.n_cols;
-                const double* base = op == 0 ? a.A : a.Bt;
-                const bool ok = grow < lim;
-                const double* src = base + (ok ? grow : 0) * (long long)a.kdim + p_kc * BK + c16 * 2;
-                cp_async16(dst, src, ok ? 16 : 0);
-            }
-            if (++p_kc == kchunks) {
-                p_kc = 0;
-                p_tile += gridDim.x;
-                if (p_tile < n_tiles) p_tc = tile_coord(p_tile, tiles_m, tiles_n);
+            for (int kg = 0; kg < BK / 4; ++kg) {
+                bulk_g2s(st + kg * TM * 4, srcA + (long long)kg * a.a_rows_pad * 4, TM * 32, &bar_full[p_stage]);
+                bulk_g2s(st + OPERAND_DOUBLES + kg * TN * 4, srcB + (long long)kg * a.b_rows_pad * 4, TN * 32,
+                         &bar_full[p_stage]);
             }
         }
-        p_stage = p_stage + 1 == STAGES ? 0 : p_stage + 1;
-        cp_async_commit();
+        p_rr = (p_rr + 1) & (CONSUMER_WARPS - 1);
+        if (++p_stage == STAGES) { p_stage = 0; p_phase ^= 1u; }
+        if (++p_kc == kchunks) {
+            p_kc = 0;
+            p_tile += gridDim.x;
+            if (p_tile < n_tiles) p_tc = tile_coord(p_tile, tiles_m, tiles_n);
+        }
     };
+#pragma unroll 1
+    for (int i = 0; i < STAGES - LAG; ++i) produce();
 
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) issue();
-
+    const int wm = warp >> 2, wn = warp & 3;
     double acc[4][4][2];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-
-    MisAccum macc = {0.0, 0.0, 0.0}, macc2 = {0.0, 0.0, 0.0};
-    int c_stage = 0;
-
+    int stage = 0;
+    uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-      for (int kc = 0; kc < kchunks; ++kc) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        issue();
-
-        const double* sA = smem + c_stage * STAGE_DOUBLES;
-        c_stage = c_stage + 1 == STAGES ? 0 : c_stage + 1;
-        const double* sB = sA + OPERAND_DOUBLES;
+#pragma unroll 1
+        for (int kc = 0; kc < kchunks; ++kc) {
+            produce();
+            mbar_wait(&bar_full[stage], phase);
+            const double* sA = smem + stage * STAGE_DOUBLES;
+            const double* sB = sA + OPERAND_DOUBLES;
 #pragma unroll
-        for (int kk = 0; kk < BK / 4; ++kk) {
-            double fa[4], fb[4];
+            for (int kk = 0; kk < BK / 4; ++kk) {
+                double fa[4], fb[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) fa[i] = sA[(kk * TM + wm * 32 + i * 8) * 4 + lane];
+                for (int i = 0; i < 4; ++i) fa[i] = sA[(kk * TM + wm * 32 + i * 8) * 4 + lane];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) fb[j] = sB[(kk * TN + wn * 32 + j * 8) * 4 + lane];
+                for (int j = 0; j < 4; ++j) fb[j] = sB[(kk * TN + wn * 32 + j * 8) * 4 + lane];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma_8x8x4(acc[i][j][0], acc[i][j][1], fa[i], fb[j]);
+                    for (int j = 0; j < 4; ++j) dmma_8x8x4(acc[i][j][0], acc[i][j][1], fa[i], fb[j]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_empty[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-
-      }
-      // ---- epilogue of this tile, registers only; interior tiles take the guard-free path ----
-      {
+        // epilogue of this tile, registers only; interior tiles take the guard-free path
         const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
         if (tc.r0 + TM <= a.n_rows && tc.c0 + TN <= a.n_cols)
             tile_epilogue<true, STORE, OUT32>(a, acc, macc, macc2, tc, out_scale, wm, wn, lane);
         else
             tile_epilogue<false, STORE, OUT32>(a, acc, macc, macc2, tc, out_scale, wm, wn, lane);
-      }
     }
     macc.s_p += macc2.s_p; macc.s_pw += macc2.s_pw; macc.s_pwok += macc2.s_pwok;
-    cp_async_wait<0>();
     mis_block_store(macc, scratch, a.partials);
+}
+
+// ---- operand packing: row-major [n_rows][kdim] -> [kdim/4][rows_pad][4], zero padded ----------
+__global__ void __launch_bounds__(256) pack_kernel(const double* __restrict__ X, long long n_rows,
+                                                   long long rows_pad, int kdim,
+                                                   double* __restrict__ out) {
+    // one thread per (k group, row): reads 32 contiguous bytes, writes 32 contiguous bytes;
+    // threads of a warp walk k groups of one row first so reads coalesce into 128-byte lines
+    const int kgroups = kdim / 4;
+    const long long total = rows_pad * kgroups;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / kgroups;
+        const int g = (int)(i - row * kgroups);
+        double2 v0 = make_double2(0.0, 0.0), v1 = v0;
+        if (row < n_rows) {
+            const double2* src = reinterpret_cast<const double2*>(X + row * kdim + g * 4);
+            v0 = src[0]; v1 = src[1];
+        }
+        double2* dst = reinterpret_cast<double2*>(out + ((long long)g * rows_pad + row) * 4);
+        dst[0] = v0; dst[1] = v1;
+    }
 }
 
 // ---- norm: column sums --------------------------------------------------------------------
@@ -346,7 +397,27 @@ static int launch_contract(const ContractArgs& args, int grid, cudaStream_t s) {
     return QDC_OK;
 }
 
-extern "C" int qdc_contract_f64(const double* d_A, const double* d_Bt, int64_t row_lo,
+extern "C" int64_t qdc_contract_packed_doubles(int64_t n_rows, int kdim) {
+    return n_rows < 0 || kdim < 0 ? 0 : packed_rows(n_rows) * (int64_t)kdim;
+}
+
+extern "C" int qdc_contract_pack(const double* d_X, int64_t n_rows, int kdim, double* d_packed,
+                                 void* stream) {
+    QDC_REQUIRE(d_X && d_packed, "null buffer");
+    QDC_REQUIRE(n_rows >= 1 && kdim >= BK && kdim % BK == 0, "shape (kdim must be a multiple of 16)");
+    QDC_REQUIRE((((uintptr_t)d_X) & 15) == 0 && (((uintptr_t)d_packed) & 15) == 0, "16-byte alignment");
+    const long long rows_pad = packed_rows(n_rows);
+    const long long total = rows_pad * (kdim / 4);
+    long long blocks = (total + 255) / 256;
+    const long long cap = (long long)qdc_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    pack_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_X, n_rows, rows_pad, kdim, d_packed);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+extern "C" int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_Bp,
+                                int64_t row_lo,
                                 int64_t n_rows, int64_t n_cols, int kdim, double scale,
                                 const double* d_norm, double threshold,
                                 const uint64_t* d_row_x, const uint64_t* d_row_forb,
@@ -355,7 +426,9 @@ extern "C" int qdc_contract_f64(const double* d_A, const double* d_Bt, int64_t r
                                 int out_dtype, double* d_sums, uint64_t* d_cand_x,
                                 double* d_cand_p, unsigned long long* d_cand_count,
                                 int64_t cand_cap, double* d_partials, void* stream) {
-    QDC_REQUIRE(d_A && d_Bt && d_sums && d_partials, "null buffer");
+    QDC_REQUIRE(d_Ap && d_Bp && d_sums && d_partials, "null buffer");
+    QDC_REQUIRE(a_rows_total >= 1 && row_lo + n_rows <= a_rows_total, "row slab outside the row operand");
+    QDC_REQUIRE((((uintptr_t)d_Ap) & 15) == 0 && (((uintptr_t)d_Bp) & 15) == 0, "16-byte alignment");
     QDC_REQUIRE(d_row_x && d_row_forb && d_row_wok && d_col_x && d_col_wok, "null tables");
     QDC_REQUIRE(d_cand_x && d_cand_p && d_cand_count && cand_cap >= 0, "candidate sink");
     QDC_REQUIRE(kdim >= BK && kdim % BK == 0, "kdim must be a multiple of 16");
@@ -366,8 +439,10 @@ extern "C" int qdc_contract_f64(const double* d_A, const double* d_Bt, int64_t r
     if (n_rows == 0) return QDC_OK;
     cudaStream_t s = (cudaStream_t)stream;
     ContractArgs args;
-    args.A = d_A + row_lo * (long long)kdim;
-    args.Bt = d_Bt;
+    args.Ap = d_Ap;
+    args.Bp = d_Bp;
+    args.a_rows_pad = packed_rows(a_rows_total);
+    args.b_rows_pad = packed_rows(n_cols);
     args.row_lo = row_lo; args.n_rows = n_rows; args.n_cols = n_cols; args.kdim = kdim;
     args.scale = scale; args.d_norm = d_norm;
     args.tab = {d_row_x, d_row_forb, d_row_wok, d_col_x, d_col_wok};

@@ -137,7 +137,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                        row_lo: int = 0, n_rows: Optional[int] = None,
                        store: Optional[str] = None, out_dtype=torch.float64,
                        out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
-                       stream=None, kernel_events: Optional[list] = None) -> ScoreResult:
+                       stream=None, kernel_events: Optional[list] = None,
+                       packed_cache: Optional[dict] = None) -> ScoreResult:
     """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
 
     A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
@@ -145,6 +146,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
     (full-circuit order, length 2^(row_bits+col_bits), scatter).
     kernel_events: if a list, a (start, end) CUDA event pair bracketing the contraction kernel
     alone (recorded on the launching stream) is appended to it.
+    packed_cache: optional dict reused across calls; operands whose storage and version are
+    unchanged are not re-packed (the kernel reads the k-group-major packed copies).
     """
     lib = _lib.load()
     dev = A.device
@@ -177,12 +180,14 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             _lib.check(lib.qdc_contract_norm(_lib.ptr(A), M, _lib.ptr(Bt), N, kdim, scale,
                                              _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
                        "qdc_contract_norm")
+        Ap = _packed(lib, A, sp, packed_cache)
+        Bp = _packed(lib, Bt, sp, packed_cache)
         if kernel_events is not None:
             ev0 = torch.cuda.Event(enable_timing=True)
             ev1 = torch.cuda.Event(enable_timing=True)
             ev0.record(stream)
         _lib.check(lib.qdc_contract_f64(
-            _lib.ptr(A), _lib.ptr(Bt), row_lo, n_rows, N, kdim, scale, _lib.ptr(norm), threshold,
+            _lib.ptr(Ap), M, _lib.ptr(Bp), row_lo, n_rows, N, kdim, scale, _lib.ptr(norm), threshold,
             _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
             _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), store_mode, odt,
             _lib.ptr(sums), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
@@ -192,6 +197,22 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             kernel_events.append((ev0, ev1))
         _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
     return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
+
+
+def _packed(lib, X: torch.Tensor, sp, cache: Optional[dict]) -> torch.Tensor:
+    """k-group-major copy [kdim/4][rows_pad][4] of a row-major operand (qdc_contract_pack)."""
+    key = (X.data_ptr(), tuple(X.shape), X._version)
+    if cache is not None and key in cache:
+        return cache[key]
+    rows, kdim = X.shape
+    out = torch.empty(lib.qdc_contract_packed_doubles(rows, kdim), dtype=torch.float64,
+                      device=X.device)
+    _lib.check(lib.qdc_contract_pack(_lib.ptr(X), rows, kdim, _lib.ptr(out), sp),
+               "qdc_contract_pack")
+    if cache is not None:
+        cache.clear()            # one generation only: operands change every evaluation
+        cache[key] = out
+    return out
 
 
 def _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp):

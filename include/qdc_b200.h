@@ -184,17 +184,23 @@ int  qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets, uint
 /* ---- K5: two-operand contraction over the cut-basis index ---------------------------------
  * Replaces the itertools.product loop of _recombine_using_networks
  * (qsplit_mlrecon_methods.py:412-461) and cutqc build.c:91-169 for two operands:
- *   P~[r, c] = scale * sum_k A[r, k] * Bt[c, k],  r < n_rows (rows row_lo.. of A), c < n_cols.
- * d_A: [*, kdim] row-major (row operand, fragments F-1..1), d_Bt: [n_cols, kdim] row-major
- * (column operand, fragment 0), kdim = 4^K, kdim % 16 == 0 required (pad with zeros).
+ *   P~[r, c] = scale * sum_k A[r, k] * Bt[c, k],  r in [row_lo, row_lo + n_rows), c < n_cols.
+ * A: [a_rows_total, kdim] (row operand, fragments F-1..1), Bt: [n_cols, kdim] (column operand,
+ * fragment 0), kdim = 4^K, kdim % 16 == 0 required (pad with zeros).  Both operands are passed
+ * PACKED: qdc_contract_pack turns a row-major [n_rows][kdim] array into the k-group-major layout
+ * [kdim/4][rows_pad][4] (zero padded; qdc_contract_packed_doubles(n_rows, kdim) doubles) whose tile
+ * slices are contiguous, so the kernel is fed by bulk async copies (TMA 1-D path) alone.
  * FP64 via DMMA (mma.sync m8n8k4).  The MIS epilogue of qdc_mis_reduce is applied to every
  * tile in registers; P is only written when d_P_out != NULL:
  *   store_mode 1: d_P_out[(r - row_lo) * n_cols + c]         (united order, slab-local)
  *   store_mode 2: d_P_out[row_x[r] | col_x[c]]               (full-circuit order, scatter)
  * out_dtype 0 = f64, 1 = f32.
  */
-int qdc_contract_f64(const double* d_A, const double* d_Bt, int64_t row_lo, int64_t n_rows,
-                     int64_t n_cols, int kdim, double scale, const double* d_norm, double threshold,
+int64_t qdc_contract_packed_doubles(int64_t n_rows, int kdim);
+int qdc_contract_pack(const double* d_X, int64_t n_rows, int kdim, double* d_packed, void* stream);
+int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_Bp, int64_t row_lo,
+                     int64_t n_rows, int64_t n_cols, int kdim, double scale, const double* d_norm,
+                     double threshold,
                      const uint64_t* d_row_x, const uint64_t* d_row_forb,
                      const uint32_t* d_row_wok, const uint64_t* d_col_x,
                      const uint32_t* d_col_wok,

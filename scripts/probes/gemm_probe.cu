@@ -42,7 +42,7 @@ gemm(const double* __restrict__ A, const double* __restrict__ B, int tiles_m, in
                     const int qq = isB ? q - TM * BK / 2 : q;
                     int row, c16;
                     if (REMAP) {        // quarter-warp = 4 rows x 32 B of one k group: 128 B of distinct banks
-                        static_assert(BK == 16, "remap assumes BK 16");
+                        static_assert(!REMAP || BK == 16, "remap assumes BK 16");
                         const int l = qq & 31, blk = qq >> 5;
                         row = blk * 4 + ((l >> 1) & 3);
                         c16 = (l & 1) + 2 * (l >> 3);
@@ -125,6 +125,13 @@ int main() {
     cudaMemset(A, 0, (size_t)rows * kdim * 8);
     cudaMemset(B, 0, (size_t)cols * kdim * 8);
     run<128, 128, 16, 4, 4, 4>(A, B, rows, cols, kdim, out);
+    run<128, 128, 16, 4, 4, 4, true, false>(A, B, rows, cols, kdim, out);
+    run<128, 128, 16, 4, 4, 4, true, true>(A, B, rows, cols, kdim, out);
+    run<128, 128, 16, 4, 2, 4, true, false>(A, B, rows, cols, kdim, out);
+    run<128, 128, 16, 4, 2, 4, true, true>(A, B, rows, cols, kdim, out);
+    run<128, 128, 32, 3, 4, 4>(A, B, rows, cols, kdim, out);
+    run<128, 128, 32, 3, 2, 4>(A, B, rows, cols, kdim, out);
+    run<256, 128, 16, 3, 4, 4>(A, B, rows, cols, kdim, out);
     run<128, 128, 16, 4, 4, 4, false, false, true>(A, B, rows, cols, kdim, out);
     run<128, 128, 16, 4, 2, 4, false, false, true>(A, B, rows, cols, kdim, out);
     run<128, 128, 16, 6, 4, 4, false, false, true>(A, B, rows, cols, kdim, out);

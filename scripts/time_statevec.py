@@ -56,6 +56,9 @@ def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "one":
+        case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4)
+        sys.exit(0)
     for t, c in [(12, 4), (13, 4), (11, 4), (12, 5), (12, 3), (10, 4)]:
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, t, c)
     for t, c in [(12, 4), (13, 4), (11, 4), (12, 5)]:
