@@ -230,6 +230,66 @@ def measure_dgemm_peak(torch, dev):
     return 2.0 * 8192 ** 3 / best / 1e12
 
 
+def variant_sims_leg(torch, dev):
+    """Second BASELINE metric, "fragment-variant sims/s": the statevector engine on the C4
+    fragment shapes (DQVA-structured fragments on seeded 3-regular graphs): prep side = 17 qubits
+    x 4^4 preparation variants, meas side = 21 qubits x 3^4 measurement variants (all obtained
+    from ONE simulated state), each followed by the Pauli-tensor kernel.  Device-timed, inputs
+    resident.  `ref_variants_per_s` counts variants the way the reference does (4^p * 3^m
+    circuits, qsplit_mlrecon_methods.py:689-691)."""
+    import networkx as nx
+    from qdc_b200.engine import B200Backend
+    from qdc_b200.circuit import Parameter
+
+    def fragment(n_nodes, seed):
+        G = nx.random_regular_graph(3, n_nodes, seed=seed)
+        rng = np.random.default_rng(seed)
+        pars = [Parameter(f"var_{i}") for i in range(n_nodes + 1)]
+        insts = [("zcrx", tuple(int(v) for v in G.neighbors(int(q))) + (int(q),), (2 * pars[int(q)],), None)
+                 for q in rng.permutation(n_nodes)]
+        insts += [("rz", (q,), (2 * pars[n_nodes],), None) for q in range(n_nodes)]
+        return n_nodes + 1, insts, pars
+
+    be = B200Backend(device=dev)
+    out, total_t, total_ref, total_states, group_bytes = {}, 0.0, 0, 0, 0.0
+    for name, n_nodes, prep, meas in (("prep_side", 16, [0, 5, 9, 13], []),
+                                      ("meas_side", 20, [], [3, 8, 12, 17])):
+        n, insts, pars = fragment(n_nodes, 7)
+        zero = ((1 << n) - 1) & ~sum(1 << q for q in prep)
+        prog, auto = be.compile_instructions(n, insts, pars, zero)
+        table = np.random.default_rng(1).uniform(0, 2 * np.pi, (1, len(pars)))
+        n_init = 4 ** len(prep)
+        states = torch.empty(n_init, 1 << n, dtype=torch.complex128, device=dev)
+        T = be.pauli_tensor(be.run(prog, auto, table, prep_qubits=prep, out=states), prog, 1,
+                            len(prep), meas)
+
+        def step():
+            be.run(prog, auto, table, prep_qubits=prep, out=states)
+            be.pauli_tensor(states, prog, 1, len(prep), meas, out=T)
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        a.record()
+        for _ in range(reps):
+            step()
+        b.record()
+        torch.cuda.synchronize()
+        t = a.elapsed_time(b) * 1e-3 / reps
+        ref = n_init * 3 ** len(meas)
+        out[name] = {"n_qubits": n, "prep": len(prep), "meas": len(meas), "states": n_init,
+                     "ref_variants": ref, "ms": t * 1e3, "groups": prog.n_groups, "ops": prog.n_ops}
+        total_t += t; total_ref += ref; total_states += n_init
+        group_bytes += prog.n_groups * 32.0 * (1 << n) * n_init
+    out.update({"value": total_ref / total_t, "unit": "ref-equivalent variants/s",
+                "states_per_s": total_states / total_t, "ms_total": total_t * 1e3,
+                "gate_traffic_gbs": group_bytes / total_t / 1e9,
+                "note": "337 reference variants of C4 per evaluation; launches: "
+                        "sv_matrix + sv_group x groups + sv_pauli_tensor per fragment"})
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -270,6 +330,7 @@ def run_b200(args):
     kernel_events = []
 
     def step_device():
+        # inputs resident in HBM (row-major); packing for the bulk-copy pipeline is part of the step
         res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
                                     row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events)
         return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
@@ -345,7 +406,7 @@ def run_b200(args):
         "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(A_pin.numel() * 8 + Bt_pin.numel() * 8),
                 "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
-        "gpu_launches": 6 * args.steps,
+        "gpu_launches": 8 * args.steps,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
                      "unit": "TFLOP/s", "frac": achieved / dgemm_peak, "traffic": None,
                      "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64 DMMA pipe; "
@@ -354,6 +415,11 @@ def run_b200(args):
                      "kernel": "contract_f64_kernel", "kernel_ms": t_kernel * 1e3},
         "result": {"sum_p": sum_p, "avg_cost": -cost, "top": top[:k]},
     }
+    if ws == 1:
+        try:
+            line["variant_sims"] = variant_sims_leg(torch, dev)
+        except Exception as exc:
+            line["variant_sims"] = {"value": None, "note": f"failed: {exc}"}
     if not args.no_cpu_baseline and ws == 1:
         try:
             line["cpu_baseline"] = cpu_reference_sample(args.cpu_sample_bits or 20)

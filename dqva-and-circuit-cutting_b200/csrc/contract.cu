@@ -227,17 +227,22 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
     // Slice p reuses the ring slot of slice p - STAGES, which every warp released LAG iterations
     // ago, so the empty-barrier wait below practically never blocks.  All threads advance the
     // cursor; only the elected lane touches barriers and issues the 8 bulk copies.
-    int p_tile = blockIdx.x, p_kc = 0, p_stage = 0, p_rr = 0;
-    uint32_t p_phase = 0;
-    TileCoord p_tc = tile_coord(p_tile < n_tiles ? p_tile : 0, tiles_m, tiles_n);
-    auto produce = [&]() {
+    // The producer cursor is (p_tile, p_kc); its ring slot and phase follow from the consumer's
+    // (it runs exactly STAGES - LAG slices ahead), the issuing warp is p_kc % 16.
+    int p_tile = blockIdx.x, p_kc = 0;
+    int p_r0 = 0, p_c0 = 0;                      // tile origin in units of rows (fits 32 bits: < 2^31 outputs per side)
+    {
+        const TileCoord t0 = tile_coord(p_tile < n_tiles ? p_tile : 0, tiles_m, tiles_n);
+        p_r0 = (int)t0.r0; p_c0 = (int)t0.c0;
+    }
+    auto produce = [&](int p_stage, uint32_t p_phase) {
         if (p_tile >= n_tiles) return;
-        if (warp == p_rr && lane == 0) {
+        if (warp == (p_kc & (CONSUMER_WARPS - 1)) && lane == 0) {
             mbar_wait(&bar_empty[p_stage], p_phase ^ 1u);
             mbar_expect_tx(&bar_full[p_stage], STAGE_DOUBLES * 8);
             double* st = smem + p_stage * STAGE_DOUBLES;
-            const double* srcA = a.Ap + ((long long)p_kc * (BK / 4) * a.a_rows_pad + a.row_lo + p_tc.r0) * 4;
-            const double* srcB = a.Bp + ((long long)p_kc * (BK / 4) * a.b_rows_pad + p_tc.c0) * 4;
+            const double* srcA = a.Ap + ((long long)p_kc * (BK / 4) * a.a_rows_pad + a.row_lo + p_r0) * 4;
+            const double* srcB = a.Bp + ((long long)p_kc * (BK / 4) * a.b_rows_pad + p_c0) * 4;
 #pragma unroll
             for (int kg = 0; kg < BK / 4; ++kg) {
                 bulk_g2s(st + kg * TM * 4, srcA + (long long)kg * a.a_rows_pad * 4, TM * 32, &bar_full[p_stage]);
@@ -245,16 +250,17 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
                          &bar_full[p_stage]);
             }
         }
-        p_rr = (p_rr + 1) & (CONSUMER_WARPS - 1);
-        if (++p_stage == STAGES) { p_stage = 0; p_phase ^= 1u; }
         if (++p_kc == kchunks) {
             p_kc = 0;
             p_tile += gridDim.x;
-            if (p_tile < n_tiles) p_tc = tile_coord(p_tile, tiles_m, tiles_n);
+            if (p_tile < n_tiles) {
+                const TileCoord t = tile_coord(p_tile, tiles_m, tiles_n);
+                p_r0 = (int)t.r0; p_c0 = (int)t.c0;
+            }
         }
     };
 #pragma unroll 1
-    for (int i = 0; i < STAGES - LAG; ++i) produce();
+    for (int i = 0; i < STAGES - LAG; ++i) produce(i, 0u);
 
     const int wm = warp >> 2, wn = warp & 3;
     double acc[4][4][2];
@@ -267,7 +273,11 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int kc = 0; kc < kchunks; ++kc) {
-            produce();
+            {
+                const int ps = stage + (STAGES - LAG);
+                const bool wrap = ps >= STAGES;
+                produce(wrap ? ps - STAGES : ps, wrap ? phase ^ 1u : phase);
+            }
             mbar_wait(&bar_full[stage], phase);
             const double* sA = smem + stage * STAGE_DOUBLES;
             const double* sB = sA + OPERAND_DOUBLES;
