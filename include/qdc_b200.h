@@ -218,6 +218,41 @@ int qdc_contract_norm(const double* d_A, int64_t n_rows_total, const double* d_B
                       int64_t n_cols, int kdim, double scale, double* d_colsums,
                       double* d_norm, void* stream);
 
+/* ---- CutQC-style stages (K3c, K4c, K6, K7) --------------------------------------------------
+ * In-memory equivalents of the reference's four C programs (which talk through %e text files;
+ * the CLI/file-compatible shims live in the Python package `qdc_b200.cutqc`).  Bit conventions:
+ * index bit q <-> subcircuit qubit q (measure.c decToBinary/combine_effective_O_state are
+ * big-endian arrays of the same integer).  All vectors are float64 on the device.
+ *
+ * measure (cutqc/measure.c:123-161): d_raw [n_inst][2^n_qubits] (dtype 0 f64, 1 f32);
+ *   out[i][e] = sum over the non-kept qubits of (-1)^popcount(x & sign_mask_i) * raw[i][x], where
+ *   keep_mask = qubits measured in "comp" (they form the effective index e, ascending) and
+ *   sign_mask_i = qubits of instance i whose measurement label is neither "I" nor "comp". */
+int qdc_cutqc_measure(const void* d_raw, int dtype, int n_qubits, int64_t n_inst,
+                      uint64_t keep_mask, const uint64_t* d_sign_masks, double* d_out,
+                      void* stream);
+/* vertical collapse (cutqc/vertical_collapse.c:27-104): CSR over kron terms,
+ *   out[t][j] = sum_{k in [term_ptr[t], term_ptr[t+1])} coeff[k] * measured[inst_idx[k]][j];
+ *   d_nonzero[t] = 1 iff some |out[t][j]| > 1e-16 (the early-termination test, :65-75). */
+int qdc_cutqc_collapse(const double* d_measured, int64_t len, int n_terms,
+                       const int32_t* d_term_ptr, const int32_t* d_inst_idx,
+                       const int32_t* d_coeff, double* d_out, int32_t* d_nonzero, void* stream);
+/* merge (cutqc/merge.c:28-122): d_in [n_vec][2^n_effective]; qubits in active_mask keep their
+ *   relative order in the output index, qubits in zoom_mask must equal zoom_val, all others are
+ *   summed out: d_out [n_vec][2^popcount(active_mask)]. */
+int qdc_cutqc_merge(const double* d_in, int64_t n_vec, int n_effective, uint64_t active_mask,
+                    uint64_t zoom_mask, uint64_t zoom_val, double* d_out, void* stream);
+/* build, step 1 (cutqc/build.c:97-160): operand of one subcircuit, A[i][t] = vecs[idx[t]][i] for
+ *   summation term t (idx[t] < 0: the kron file is missing, the term is zero, build.c:35-67),
+ *   zero for t in [n_terms, kdim).  d_vecs [*][len], d_A [len][kdim] row-major. */
+int qdc_cutqc_gather(const double* d_vecs, int64_t len, const int32_t* d_idx, int n_terms,
+                     int kdim, double* d_A, void* stream);
+/* build, step 2 for more than two subcircuits: W[(i, j)][t] = A0[i][t] * A1[j][t] (the growing
+ *   cblas_sger product of build.c:142, kept factored per term).  Step 3 is qdc_contract_f64 with
+ *   store_mode 1 and scale 0.5^num_cuts (build.c:169). */
+int qdc_khatri_rao(const double* d_A0, int64_t m0, const double* d_A1, int64_t m1, int kdim,
+                   double* d_W, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
