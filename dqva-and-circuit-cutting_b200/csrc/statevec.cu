@@ -15,6 +15,7 @@
 // are runs of 2^c * 16 B.  Fragments of <= t qubits run their whole circuit in ONE launch with
 // one CTA per batch element.  Bound: shared-memory bandwidth inside a group (32 B per amplitude
 // per non-diagonal gate), L2/HBM between groups (algorithmic bytes per group = 32 B * 2^n * batch).
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -42,7 +43,7 @@ struct __align__(16) SvOp {   // 64 bytes
     uint8_t diag_run;         // kind 1 without controls: consecutive such ops starting here
     uint8_t pad[2];
     uint8_t fixed[MAX_FIXED];
-    uint32_t pad2;
+    uint32_t fmask;           // OR of 1 << fixed[k]
 };
 static_assert(sizeof(SvOp) == 64, "SvOp layout");
 
@@ -65,7 +66,7 @@ struct GroupArgs {
     const double* mats;       // [n_sets][n_mats][8]
     long long n_tiles;        // tiles per state
     long long init_lo;
-    uint64_t prep_mask;
+    uint64_t prep_mask, hole_mask;
     int n, t, n_sets, n_mats, op_lo, op_hi, first, n_runs, n_prep, n_codes;
     uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
     uint8_t prep_q[MAX_PREP];
@@ -97,11 +98,16 @@ __device__ __forceinline__ uint32_t insert_fixed(uint32_t i, int n_fixed, const 
     return i;
 }
 
-__global__ void __launch_bounds__(1024) sv_group_kernel(const GroupArgs a) {
+constexpr int OPS_CHUNK = 32;          // ops staged in shared memory at a time
+constexpr int TAB_LO_BITS = 6;          // diagonal-run phase table over the low tile bits
+
+// Index walks use the carry trick: if x = expand(l) has zeros at the positions of mask M, then
+// expand(l + s) = ((x | M) + expand(s)) & ~M -- three integer ops per step instead of a loop.
+__global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
     extern __shared__ double2 tile[];
-    __shared__ double2 sh_d0[MAX_DIAG_RUN], sh_d1[MAX_DIAG_RUN];
-    __shared__ int sh_tb[MAX_DIAG_RUN];
-    __shared__ double2 sh_gfac;
+    __shared__ SvOp sh_ops[OPS_CHUNK];
+    __shared__ double sh_mats[OPS_CHUNK][8];
+    __shared__ double2 sh_tab[(1 << TAB_LO_BITS) + (1 << (13 - TAB_LO_BITS))];
 
     const long long blk = blockIdx.x;
     const long long batch = blk / a.n_tiles;
@@ -117,95 +123,133 @@ __global__ void __launch_bounds__(1024) sv_group_kernel(const GroupArgs a) {
     }
     double2* st = a.state + (batch << a.n);
     const uint32_t T = 1u << a.t;
-    const int nthr = blockDim.x, tid = threadIdx.x;
+    const uint32_t nthr = blockDim.x, tid = threadIdx.x;
+    const uint64_t hole = a.hole_mask;
+    const uint64_t x_first = expand_runs(tid, a.n_runs, a.run_pos, a.run_len);
+    const uint64_t x_step = expand_runs(nthr, a.n_runs, a.run_pos, a.run_len);
 
     if (a.first) {
         // initial product state: prep qubit j in code[digit_j], every other qubit in |0>
         long long v = a.init_lo + batch / a.n_sets;
         int digit[MAX_PREP];
-        for (int j = a.n_prep - 1; j >= 0; --j) { digit[j] = (int)(v % a.n_codes); v /= a.n_codes; }
-        for (uint32_t l = tid; l < T; l += nthr) {
-            const uint64_t x = expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base;
+#pragma unroll
+        for (int j = MAX_PREP - 1; j >= 0; --j)
+            if (j < a.n_prep) { digit[j] = (int)(v % a.n_codes); v /= a.n_codes; }
+        uint64_t x = x_first;
+        for (uint32_t l = tid; l < T; l += nthr, x = ((x | hole) + x_step) & ~hole) {
+            const uint64_t full = x | base;
             double2 amp = make_double2(0.0, 0.0);
-            if ((x & ~a.prep_mask) == 0ull) {
+            if ((full & ~a.prep_mask) == 0ull) {
                 amp = make_double2(1.0, 0.0);
-                for (int j = 0; j < a.n_prep; ++j) {
-                    const int bit = (int)((x >> a.prep_q[j]) & 1ull);
-                    amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
-                }
+#pragma unroll
+                for (int j = 0; j < MAX_PREP; ++j)
+                    if (j < a.n_prep) {
+                        const int bit = (int)((full >> a.prep_q[j]) & 1ull);
+                        amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
+                    }
             }
             tile[l] = amp;
         }
     } else {
-        for (uint32_t l = tid; l < T; l += nthr)
-            tile[l] = st[expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base];
+        // all loads of a batch are issued before the first one is consumed (8 in flight per thread)
+        constexpr int U = 8;
+        uint64_t x = x_first;
+        for (uint32_t l = tid; l < T; l += nthr * U) {
+            double2 v[U];
+            uint64_t xs = x;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (l + u * nthr < T) v[u] = __ldcs(st + (xs | base));
+                xs = ((xs | hole) + x_step) & ~hole;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (l + u * nthr < T) tile[l + u * nthr] = v[u];
+            x = xs;
+        }
     }
-    __syncthreads();
 
     const double* mats = a.mats + (size_t)(batch % a.n_sets) * a.n_mats * 8;
-    for (int i = a.op_lo; i < a.op_hi;) {
-        const SvOp op = a.ops[i];
-        if ((base & op.gmask) != op.gval) { ++i; continue; }          // uniform over the CTA
-        if (op.kind == 0) {
-            const double* m = mats + (size_t)op.mat * 8;
-            const double2 m00 = make_double2(m[0], m[1]), m01 = make_double2(m[2], m[3]);
-            const double2 m10 = make_double2(m[4], m[5]), m11 = make_double2(m[6], m[7]);
-            const uint32_t count = 1u << (a.t - op.n_fixed), tb = 1u << op.tbit;
-            for (uint32_t k = tid; k < count; k += nthr) {
-                const uint32_t l0 = insert_fixed(k, op.n_fixed, op.fixed) | op.lval;
-                const uint32_t l1 = l0 | tb;
-                const double2 a0 = tile[l0], a1 = tile[l1];
-                tile[l0] = cfma(m00, a0, cmul(m01, a1));
-                tile[l1] = cfma(m10, a0, cmul(m11, a1));
-            }
-            ++i;
-        } else if (op.diag_run >= 1) {
-            // joint pass over a run of uncontrolled diagonal gates
-            const int run = op.diag_run;
-            if (tid < run) {
-                const SvOp o = a.ops[i + tid];
-                const double* m = mats + (size_t)o.mat * 8;
-                sh_d0[tid] = make_double2(m[0], m[1]);
-                sh_d1[tid] = make_double2(m[6], m[7]);
-                sh_tb[tid] = o.tbit >= 0 ? o.tbit : -1 - o.gtarget;
-            }
-            __syncthreads();
-            if (tid == 0) {
-                double2 g = make_double2(1.0, 0.0);
-                for (int k = 0; k < run; ++k)
-                    if (sh_tb[k] < 0) g = cmul(g, ((base >> (-1 - sh_tb[k])) & 1ull) ? sh_d1[k] : sh_d0[k]);
-                sh_gfac = g;
-            }
-            __syncthreads();
-            const double2 g = sh_gfac;
-            for (uint32_t l = tid; l < T; l += nthr) {
-                double2 f = g;
-                for (int k = 0; k < run; ++k) {
-                    const int b = sh_tb[k];
-                    if (b >= 0) f = cmul(f, ((l >> b) & 1u) ? sh_d1[k] : sh_d0[k]);
-                }
-                tile[l] = cmul(tile[l], f);
-            }
-            i += run;
-        } else {
-            // controlled diagonal gate (or one too many for a run): fixed[] = local control bits
-            const double* m = mats + (size_t)op.mat * 8;
-            const double2 d0 = make_double2(m[0], m[1]), d1 = make_double2(m[6], m[7]);
-            const uint32_t count = 1u << (a.t - op.n_fixed);
-            const bool local = op.tbit >= 0;
-            const double2 dg = ((base >> op.gtarget) & 1ull) ? d1 : d0;
-            for (uint32_t k = tid; k < count; k += nthr) {
-                const uint32_t l = insert_fixed(k, op.n_fixed, op.fixed) | op.lval;
-                const double2 d = local ? (((l >> op.tbit) & 1u) ? d1 : d0) : dg;
-                tile[l] = cmul(tile[l], d);
-            }
-            ++i;
+    for (int cb = a.op_lo; cb < a.op_hi; cb += OPS_CHUNK) {
+        const int n_chunk = a.op_hi - cb < OPS_CHUNK ? a.op_hi - cb : OPS_CHUNK;
+        __syncthreads();                                   // tile ready / previous chunk consumed
+        {
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(a.ops + cb);
+            uint32_t* dst = reinterpret_cast<uint32_t*>(sh_ops);
+            for (uint32_t w = tid; w < (uint32_t)n_chunk * 16u; w += nthr) dst[w] = src[w];
+            const double* msrc = mats + (size_t)cb * 8;    // matrix slot == op index
+            double* mdst = &sh_mats[0][0];
+            for (uint32_t w = tid; w < (uint32_t)n_chunk * 8u; w += nthr) mdst[w] = msrc[w];
         }
         __syncthreads();
+        for (int i = 0; i < n_chunk;) {
+            const SvOp& op = sh_ops[i];
+            if ((base & op.gmask) != op.gval) { ++i; continue; }          // uniform over the CTA
+            const double* m = sh_mats[i];
+            if (op.kind == 0) {
+                const double2 m00 = make_double2(m[0], m[1]), m01 = make_double2(m[2], m[3]);
+                const double2 m10 = make_double2(m[4], m[5]), m11 = make_double2(m[6], m[7]);
+                const uint32_t count = 1u << (a.t - op.n_fixed), tb = 1u << op.tbit;
+                const uint32_t fm = op.fmask, lval = op.lval;
+                uint32_t e = insert_fixed(tid, op.n_fixed, op.fixed);
+                const uint32_t e_step = insert_fixed(nthr, op.n_fixed, op.fixed);
+                for (uint32_t k = tid; k < count; k += nthr, e = ((e | fm) + e_step) & ~fm) {
+                    const uint32_t l0 = e | lval, l1 = l0 | tb;
+                    const double2 a0 = tile[l0], a1 = tile[l1];
+                    tile[l0] = cfma(m00, a0, cmul(m01, a1));
+                    tile[l1] = cfma(m10, a0, cmul(m11, a1));
+                }
+                ++i;
+            } else if (op.diag_run >= 1) {
+                // joint pass over a run of uncontrolled diagonal gates: the phase of tile index l
+                // factors into a table over its low bits times a table over its high bits (the
+                // latter also carries the constant factor of the gates on non-local qubits)
+                const int run = op.diag_run;
+                const int h = a.t < TAB_LO_BITS ? a.t : TAB_LO_BITS;
+                const uint32_t n_lo = 1u << h, n_hi = 1u << (a.t - h);
+                for (uint32_t w = tid; w < n_lo + n_hi; w += nthr) {
+                    const bool hi = w >= n_lo;
+                    const uint32_t idx = hi ? w - n_lo : w;
+                    double2 f = make_double2(1.0, 0.0);
+                    for (int k = 0; k < run; ++k) {
+                        const SvOp& o = sh_ops[i + k];
+                        const double* mk = sh_mats[i + k];
+                        int bit = -1;
+                        if (o.tbit < 0) { if (hi) bit = (int)((base >> o.gtarget) & 1ull); }
+                        else if (!hi && o.tbit < h) bit = (idx >> o.tbit) & 1;
+                        else if (hi && o.tbit >= h) bit = (idx >> (o.tbit - h)) & 1;
+                        if (bit >= 0) f = cmul(f, bit ? make_double2(mk[6], mk[7]) : make_double2(mk[0], mk[1]));
+                    }
+                    sh_tab[w] = f;
+                }
+                __syncthreads();
+                for (uint32_t l = tid; l < T; l += nthr)
+                    tile[l] = cmul(tile[l], cmul(sh_tab[l & (n_lo - 1u)], sh_tab[n_lo + (l >> h)]));
+                i += run;
+            } else {
+                // controlled diagonal gate: fixed[] = local control bits
+                const double2 d0 = make_double2(m[0], m[1]), d1 = make_double2(m[6], m[7]);
+                const uint32_t count = 1u << (a.t - op.n_fixed);
+                const bool local = op.tbit >= 0;
+                const double2 dg = ((base >> op.gtarget) & 1ull) ? d1 : d0;
+                const uint32_t fm = op.fmask, lval = op.lval;
+                uint32_t e = insert_fixed(tid, op.n_fixed, op.fixed);
+                const uint32_t e_step = insert_fixed(nthr, op.n_fixed, op.fixed);
+                for (uint32_t k = tid; k < count; k += nthr, e = ((e | fm) + e_step) & ~fm) {
+                    const uint32_t l = e | lval;
+                    const double2 d = local ? (((l >> op.tbit) & 1u) ? d1 : d0) : dg;
+                    tile[l] = cmul(tile[l], d);
+                }
+                ++i;
+            }
+            __syncthreads();
+        }
     }
-
-    for (uint32_t l = tid; l < T; l += nthr)
-        st[expand_runs(l, a.n_runs, a.run_pos, a.run_len) | base] = tile[l];
+    __syncthreads();
+    {
+        uint64_t x = x_first;
+        for (uint32_t l = tid; l < T; l += nthr, x = ((x | hole) + x_step) & ~hole) st[x | base] = tile[l];
+    }
 }
 
 // one thread per (parameter set, matrix slot)
@@ -278,7 +322,8 @@ __global__ void __launch_bounds__(256) sv_pauli_tensor_kernel(const TensorArgs a
     const int n_s = 1 << (2 * p), n_mu = 1 << m, n_pm = 1 << (2 * m);
     const int n_kappa = n_s * n_pm;
     double2* amp = sh_raw;                                        // [bb][n_s][n_mu]
-    double* R = reinterpret_cast<double*>(sh_raw + (size_t)a.bb * n_s * n_mu);   // [bb][n_s][n_pm]
+    double2* C = sh_raw + (size_t)a.bb * n_s * n_mu;             // [bb][n_s][n_pm] complex work array (m > 0)
+    double* R = reinterpret_cast<double*>(C);                    // [bb][n_s][n_pm], aliases C
     const long long set = blockIdx.y;
     const long long b0 = (long long)blockIdx.x * a.bb;
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -298,29 +343,86 @@ __global__ void __launch_bounds__(256) sv_pauli_tensor_kernel(const TensorArgs a
     }
     __syncthreads();
 
-    // 2. Pauli expectation on the measured qubits: R[bl][s][pm] = <psi| P_pm |psi> restricted to b
-    for (int idx = tid; idx < a.bb * n_s * n_pm; idx += nthr) {
-        const int pm = idx % n_pm, rest = idx / n_pm;            // rest = bl * n_s + s
-        uint32_t xmask = 0, zmask = 0;
-        int n_y = 0;
-        for (int j = 0; j < m; ++j) {                             // axis j: digit j, most significant first
-            const int aj = (pm >> (2 * (m - 1 - j))) & 3;         // 0 I, 1 X, 2 Y, 3 Z
-            if (aj == 1 || aj == 2) xmask |= 1u << j;
-            if (aj == 2 || aj == 3) zmask |= 1u << j;
-            n_y += aj == 2;
+    if (m == 0) {
+        // no measured qubit in this fragment: the only "Pauli" is the identity, <I> = |amp|^2
+        for (int idx = tid; idx < a.bb * n_s; idx += nthr) {
+            const double2 v = amp[idx];
+            R[idx] = v.x * v.x + v.y * v.y;
         }
-        const double2* v = amp + (size_t)rest * n_mu;
-        double re = 0.0, im = 0.0;
-        for (int mu = 0; mu < n_mu; ++mu) {
-            const double2 ket = v[mu], bra = v[mu ^ xmask];      // conj(bra) * ket
-            double tr = bra.x * ket.x + bra.y * ket.y, ti = bra.x * ket.y - bra.y * ket.x;
-            if (__popc(mu & zmask) & 1) { tr = -tr; ti = -ti; }
-            re += tr; im += ti;
+        __syncthreads();
+    } else if (m <= 2) {
+        // few measured qubits: direct sums  R = Re <psi_b| P |psi_b>  (at most 4 terms each)
+        for (int idx = tid; idx < a.bb * n_s * n_pm; idx += nthr) {
+            const int pm = idx % n_pm, rest = idx / n_pm;            // rest = bl * n_s + s
+            uint32_t xmask = 0, zmask = 0;
+            int n_y = 0;
+            for (int j = 0; j < m; ++j) {                             // axis j: digit j, most significant first
+                const int aj = (pm >> (2 * (m - 1 - j))) & 3;         // 0 I, 1 X, 2 Y, 3 Z
+                if (aj == 1 || aj == 2) xmask |= 1u << j;
+                if (aj == 2 || aj == 3) zmask |= 1u << j;
+                n_y += aj == 2;
+            }
+            const double2* v = amp + (size_t)rest * n_mu;
+            double re = 0.0, im = 0.0;
+            for (int mu = 0; mu < n_mu; ++mu) {
+                const double2 ket = v[mu], bra = v[mu ^ xmask];      // conj(bra) * ket
+                double tr = bra.x * ket.x + bra.y * ket.y, ti = bra.x * ket.y - bra.y * ket.x;
+                if (__popc(mu & zmask) & 1) { tr = -tr; ti = -ti; }
+                re += tr; im += ti;
+            }
+            const int ny = n_y & 3;                                   // multiply by i^n_y, keep Re
+            R[idx] = ny == 0 ? re : ny == 1 ? -im : ny == 2 ? -re : im;
         }
-        const int ny = n_y & 3;                                   // multiply by i^n_y, keep Re
-        R[idx] = ny == 0 ? re : ny == 1 ? -im : ny == 2 ? -re : im;
+        __syncthreads();
+    } else {
+        // 2. Pauli coordinates of rho_b = |psi_b><psi_b| on the measured qubits: outer product in the
+        //    matrix-unit basis (digit j = 2 * row bit + column bit of measured qubit j), then one
+        //    4-point butterfly per qubit (e00, e01, e10, e11) -> (I, X, Y, Z):
+        //    I = r00 + r11, X = r01 + r10, Y = i (r01 - r10), Z = r00 - r11   (Tr(rho P))
+        for (int idx = tid; idx < a.bb * n_s * n_pm; idx += nthr) {
+            const int dgt = idx % n_pm, rest = idx / n_pm;            // rest = bl * n_s + s
+            uint32_t row = 0, col = 0;
+            for (int j = 0; j < m; ++j) {
+                const int aj = (dgt >> (2 * (m - 1 - j))) & 3;
+                row |= (uint32_t)(aj >> 1) << j;
+                col |= (uint32_t)(aj & 1) << j;
+            }
+            const double2 r = amp[(size_t)rest * n_mu + row], c = amp[(size_t)rest * n_mu + col];
+            C[idx] = make_double2(r.x * c.x + r.y * c.y, r.y * c.x - r.x * c.y);     // r * conj(c)
+        }
+        __syncthreads();
+        for (int j = 0; j < m; ++j) {
+            const int inner = 1 << (2 * (m - 1 - j));
+            const int n_vec = a.bb * n_s * n_pm / 4;
+            for (int idx = tid; idx < n_vec; idx += nthr) {
+                const int lo = idx % inner, hi = idx / inner;
+                double2* q = C + (size_t)hi * inner * 4 + lo;
+                const double2 r00 = q[0], r01 = q[inner], r10 = q[2 * inner], r11 = q[3 * inner];
+                q[0] = make_double2(r00.x + r11.x, r00.y + r11.y);
+                q[inner] = make_double2(r01.x + r10.x, r01.y + r10.y);
+                q[2 * inner] = make_double2(-(r01.y - r10.y), r01.x - r10.x);
+                q[3 * inner] = make_double2(r00.x - r11.x, r00.y - r11.y);
+            }
+            __syncthreads();
+        }
+        // keep the real parts, compacted in place through registers (R aliases C; a chunk only
+        // overwrites complex entries that this or an earlier chunk has already read)
+        for (int base_idx = 0; base_idx < a.bb * n_kappa; base_idx += 8 * nthr) {
+            double keep[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base_idx + tid + u * nthr;
+                keep[u] = idx < a.bb * n_kappa ? C[idx].x : 0.0;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base_idx + tid + u * nthr;
+                if (idx < a.bb * n_kappa) R[idx] = keep[u];
+            }
+            __syncthreads();
+        }
     }
-    __syncthreads();
 
     // 3. preparation frame inverse along each prep axis: out[a] = sum_s frame[a][s] in[s]
     for (int j = 0; j < p; ++j) {
@@ -524,7 +626,10 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
             std::sort(fixed.begin(), fixed.end());
             if ((int)fixed.size() > MAX_FIXED) { qdc_sv_free(prog); QDC_REQUIRE(false, "too many local controls"); }
             op.n_fixed = (uint8_t)fixed.size();
-            for (size_t k = 0; k < fixed.size(); ++k) op.fixed[k] = (uint8_t)fixed[k];
+            for (size_t k = 0; k < fixed.size(); ++k) {
+                op.fixed[k] = (uint8_t)fixed[k];
+                op.fmask |= 1u << fixed[k];
+            }
             prog->ops.push_back(op);
             MatDesc md;
             memset(&md, 0, sizeof(md));
@@ -544,8 +649,10 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
             SvOp& o = prog->ops[i];
             if (o.kind == 1 && o.lmask == 0 && o.gmask == 0) {
                 int e = i;
-                while (e < gr.first_op + gr.n_ops && e - i < MAX_DIAG_RUN && prog->ops[e].kind == 1 &&
-                       prog->ops[e].lmask == 0 && prog->ops[e].gmask == 0) ++e;
+                // a run must not straddle a staging chunk of the kernel (OPS_CHUNK ops from first_op)
+                const int chunk_end = gr.first_op + ((i - gr.first_op) / OPS_CHUNK + 1) * OPS_CHUNK;
+                while (e < gr.first_op + gr.n_ops && e < chunk_end && e - i < MAX_DIAG_RUN &&
+                       prog->ops[e].kind == 1 && prog->ops[e].lmask == 0 && prog->ops[e].gmask == 0) ++e;
                 o.diag_run = (uint8_t)(e - i);
                 i = e;
             } else {
@@ -653,14 +760,24 @@ extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t ini
     QDC_REQUIRE(grid < (1ll << 31), "batch * tiles exceeds one grid: split the batch");
     const size_t smem = (size_t)16 << prog->t;
     QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // measured on B200 (profiles/r1_time_statevec_threads.log): several small CTAs per SM overlap
+    // their load / gate / store phases better than one or two large ones
+    const int max_threads = prog->t >= 13 ? 512 : prog->t == 12 ? 256 : 128;
     int threads = 1 << (prog->t > 1 ? prog->t - 1 : 0);
-    if (threads > 512) threads = 512;
+    if (threads > max_threads) threads = max_threads;
     if (threads < 32) threads = 32;
+    if (const char* env = getenv("QDC_SV_THREADS")) {       // tuning knob (power of two, 32..512)
+        const int v = atoi(env);
+        if (v >= 32 && v <= 512 && (v & (v - 1)) == 0) threads = v;
+    }
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_group_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
     for (size_t g = 0; g < prog->groups.size(); ++g) {
         const Group& gr = prog->groups[g];
         a.op_lo = gr.first_op; a.op_hi = gr.first_op + gr.n_ops;
         a.first = g == 0;
         a.n_runs = gr.n_runs;
+        a.hole_mask = ~gr.local_mask;                      // bits above n never receive a carry-out that matters
         for (int r = 0; r < gr.n_runs; ++r) { a.run_pos[r] = gr.run_pos[r]; a.run_len[r] = gr.run_len[r]; }
         sv_group_kernel<<<(unsigned)grid, threads, smem, s>>>(a);
         QDC_CHECK_LAUNCH();
@@ -728,7 +845,7 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
     if (bb > a.n_b) bb = (int)a.n_b;
     a.bb = bb;
     const size_t n_s = (size_t)1 << (2 * n_prep), n_mu = (size_t)1 << n_meas;
-    const size_t smem = (size_t)bb * n_s * n_mu * 16 + (size_t)bb * n_kappa * 8;
+    const size_t smem = (size_t)bb * n_s * n_mu * 16 + (size_t)bb * n_kappa * (n_meas >= 3 ? 16 : 8);
     QDC_REQUIRE(smem <= 200 * 1024, "shared memory");
     QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_pauli_tensor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long gx = (a.n_b + bb - 1) / bb;
