@@ -1,0 +1,146 @@
+"""GPU parity at the shapes BASELINE.json names: C1 = N18_com2_pin80_pout2/G1, 2
+fragments, 1 cut; C2 = N26_com2_pin20_pout10/G1, 2 fragments, 2-3 cuts, batch of parameter
+vectors; C3 = N33_com3_pin80_pout2/G1, 3 fragments.  The cut path (gate-faithful fragments ->
+engine -> Pauli tensors -> contraction + MIS scoring) is compared with the UNCUT circuit: numpy
+oracle statevector where it fits (C1), the engine's own uncut simulation beyond that (C2; the
+engine is pinned to the oracle at <= 16 qubits in test_gpu_statevec.py), and size-independent
+properties where nothing else fits (C3: total probability, non-negativity of the top entry)."""
+import os
+import random
+
+import networkx as nx
+import numpy as np
+import pytest
+import torch
+
+from oracle import mis_oracle as mo
+from oracle import statevector as sv
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _graph(golden_dir, name):
+    from qdc_b200.utils import graph_funcs
+    return graph_funcs.graph_from_file(os.path.join(golden_dir, "graphs", name + ".txt"))
+
+
+def _cut_circuit(G, partition, max_cuts, seed, fused, symbolic=False):
+    from qdc_b200.ansatz import dqv_cut_ansatz
+    from qdc_b200.circuit import Parameter
+    from qdc_b200.qsplit import qsplit_circuit_cutter as qcc
+    from qdc_b200.utils import graph_funcs
+    from qdc_b200.utils.cutting_funcs import simple_choose_nodes
+    random.seed(seed)
+    np.random.seed(seed)
+    n = G.number_of_nodes()
+    _, cut_edges = graph_funcs.get_subgraphs(G, partition)
+    cut_nodes, hot_nodes = simple_choose_nodes(G, partition, cut_edges, max_cuts)
+    order = [int(v) for part in partition for v in np.random.permutation(part)]
+    params = ([Parameter(f"var_{i}") for i in range(n + 1)] if symbolic
+              else list(np.random.uniform(0, 2 * np.pi, n + 1)))
+    circ, cuts = dqv_cut_ansatz.gen_dqva(G, partition, cut_nodes, hot_nodes, order, params=params,
+                                         init_state="0" * n, fused=fused)
+    frags, wpm = qcc.cut_circuit(circ, cuts)
+    return circ, cuts, frags, wpm, (cut_nodes, hot_nodes, order, params)
+
+
+def _kl_partition(G, max_cuts):
+    """Kernighan-Lin bisection (the reference's default partition_alg, mis.py:145-149); the first
+    seed whose cut admits a hot-node set within max_cuts is used and recorded."""
+    from qdc_b200.utils import graph_funcs
+    from qdc_b200.utils.cutting_funcs import simple_choose_nodes
+    for seed in range(20):
+        parts = [sorted(p) for p in nx.algorithms.community.kernighan_lin_bisection(G, seed=seed)]
+        _, cut_edges = graph_funcs.get_subgraphs(G, parts)
+        try:
+            random.seed(0)
+            simple_choose_nodes(G, parts, cut_edges, max_cuts)
+            return parts, seed
+        except IndexError:
+            continue
+    pytest.skip("no feasible hot-node set for this graph / max_cuts")
+
+
+def test_c1_n18_one_cut_matches_uncut_oracle(cuda, golden_dir):
+    from qdc_b200.engine import B200Backend
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = _graph(golden_dir, "N18_com2_pin80_pout2_G1")
+    partition, kl_seed = _kl_partition(G, 1)
+    circ, cuts, frags, wpm, meta = _cut_circuit(G, partition, 1, 0, fused=False)
+    assert len(frags) == 2 and len(cuts) == 1
+    be = B200Backend(device=cuda, graph=G)
+    dist = sim_with_cutting(frags, wpm, 1000, be, mode="likely", topk=3)
+    # uncut reference: numpy oracle on the fused form of the same circuit (same unitary)
+    from qdc_b200.ansatz import dqv_cut_ansatz
+    cut_nodes, hot_nodes, order, params = meta
+    fused_circ, _ = dqv_cut_ansatz.gen_dqva(G, partition, cut_nodes, hot_nodes, order, params=params,
+                                            init_state="0" * 18, fused=True)
+    want = sv.probabilities(sv.simulate(fused_circ.num_qubits, fused_circ.to_instructions()))
+    got = dist.P.cpu().numpy()
+    assert got.shape == want.shape == (1 << 20,)
+    assert np.abs(got - want).max() < TOL
+    s_p, s_pwok = mo.score_array(want, 18, 2, mo.adjacency_masks(G, 18))
+    out = dist.score.get()
+    assert abs(out["sum_p"] - 1) < TOL and abs(out["sum_pw_indset"] - s_pwok) < TOL
+    idx = np.nonzero(want > 1e-5)[0]
+    order_ = idx[np.lexsort((idx, -want[idx]))][:3]
+    assert [x for x, _ in out["top"]] == [int(i) for i in order_]
+
+
+@pytest.mark.parametrize("max_cuts", [2, 3])
+def test_c2_n26_parameter_batch_matches_uncut_engine(cuda, golden_dir, max_cuts):
+    from qdc_b200 import recombine as rc
+    from qdc_b200.engine import B200Backend
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = _graph(golden_dir, "N26_com2_pin20_pout10_G1")
+    partition, kl_seed = _kl_partition(G, max_cuts)
+    circ, cuts, frags, wpm, meta = _cut_circuit(G, partition, max_cuts, 1, fused=False, symbolic=True)
+    assert len(frags) == 2 and 1 <= len(cuts) <= max_cuts
+    used = circ.parameters
+    n_sets = 3
+    table = np.random.default_rng(1).uniform(0, 2 * np.pi, (n_sets, len(used)))
+    be = B200Backend(device=cuda, graph=G)
+    dists = sim_with_cutting(frags, wpm, 1, be, mode="direct", params=table, param_order=used,
+                             store=True)
+    if n_sets == 1:
+        dists = [dists]
+    N = circ.num_qubits                                   # 26 + 2 ancillas
+    prog, auto = be.compile(circ, param_order=used)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(26)] + [0, 0]
+    for s in range(n_sets):
+        state = be.run(prog, auto, table[s:s + 1])
+        want = be.probabilities(state, prog)[0]
+        got = dists[s].P
+        assert float((got - want).abs().max()) < TOL
+        tabs = rc.build_tables(N - 14, 14, list(range(N)), adj, (1 << 26) - 1, device=cuda,
+                               index_flip=prog.flip_mask)
+        ref = rc.reduce_and_score(torch.view_as_real(state[0]).reshape(-1), tabs, amplitudes=True).get()
+        out = dists[s].score.get()
+        assert abs(out["sum_p"] - 1) < 1e-9
+        assert abs(out["sum_pw_indset"] - ref["sum_pw_indset"]) < 1e-9
+        assert abs(out["sum_pw"] - ref["sum_pw"]) < 1e-9
+        del state, want
+
+
+def test_c3_n33_three_fragments_properties(cuda, golden_dir):
+    """2^36 outputs reduced on the fly (nothing stored): total probability and sanity of top-1."""
+    from qdc_b200.engine import B200Backend
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = _graph(golden_dir, "N33_com3_pin80_pout2_G1")
+    partition = [list(range(0, 11)), list(range(11, 22)), list(range(22, 33))]   # planted split
+    for max_cuts in (2, 3, 4):
+        try:
+            circ, cuts, frags, wpm, meta = _cut_circuit(G, partition, max_cuts, 2, fused=False)
+            break
+        except IndexError:
+            continue
+    else:
+        pytest.skip("no feasible hot-node set")
+    assert len(frags) == 3
+    be = B200Backend(device=cuda, graph=G)
+    dist = sim_with_cutting(frags, wpm, 1, be, mode="direct", store=False, threshold=1e-3, topk=2)
+    out = dist.score.get()
+    assert abs(out["sum_p"] - 1) < 1e-9
+    assert 0 <= out["sum_pw_indset"] <= out["sum_pw"] + 1e-12 <= 33
+    assert all(0 < p <= 1 for _, p in out["top"])
