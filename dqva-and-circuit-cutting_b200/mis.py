@@ -1,0 +1,95 @@
+"""Cost functions of the reference's variational solvers (mis.py), evaluated on the B200.
+
+Only the per-evaluation hot path lives here; the outer optimisation loops of
+`solve_mis_cut_dqva` / `solve_mis_dqva` (scipy COBYLA, partition rounds) are unchanged host
+Python in the reference and call these where they call their closures.
+
+* `cut_cost`   -- `avg_cost` of solve_mis_cut_dqva (mis.py:117-134): sim_with_cutting, strip the
+                  ancillas, sum p(x) |x| [x independent set]; batched over parameter vectors.
+* `uncut_cost` -- `f(params)` of solve_mis_dqva / solve_mis_qaoa (mis.py:639-665): full
+                  statevector, strip the ancilla, sum p(x) |x| (no independent-set mask there).
+                  The score is taken straight from the amplitudes (no probability vector is
+                  written).  The reference rounds probabilities to 5 decimals in its statevector
+                  branch (:652); this evaluates the exact sum.
+* `top_strings`-- top_probs / better_strs (mis.py:232-242).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import recombine as _rc
+from .engine import B200Backend
+from .utils.cutting_funcs import sim_with_cutting
+
+__all__ = ["cut_cost", "uncut_cost", "top_strings"]
+
+
+def _adjacency(graph, n_wires):
+    n = graph.number_of_nodes()
+    return [sum(1 << int(v) for v in graph.neighbors(i)) for i in range(n)] + [0] * (n_wires - n)
+
+
+def cut_cost(fragments, wire_path_map, frag_shots, backend: B200Backend, graph=None,
+             params=None, param_order=None, mode="likely") -> np.ndarray:
+    """-avg_cost for every parameter vector (a length-1 array for bound fragments)."""
+    if graph is not None:
+        backend.graph = graph
+    dists = sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode=mode,
+                             params=params, param_order=param_order)
+    if not isinstance(dists, list):
+        dists = [dists]
+    return np.array([-d.score.get()["sum_pw_indset"] for d in dists])
+
+
+def uncut_cost(circuit, backend: B200Backend, graph, params=None, param_order=None,
+               masked: bool = False, max_states: Optional[int] = None) -> np.ndarray:
+    """-sum_x p(x) |x| of the uncut circuit for every parameter vector (masked=True adds the
+    independent-set indicator).  Wires beyond graph.number_of_nodes() are ancillas."""
+    if param_order is None:
+        param_order = list(circuit.parameters)
+    prog, auto = backend.compile(circuit, param_order=param_order)
+    n = prog.n_qubits
+    table = np.zeros((1, 0)) if params is None else np.asarray(params, dtype=np.float64)
+    if table.ndim == 1:
+        table = table.reshape(1, -1)
+    n_sets = table.shape[0]
+    col_bits = min(n, 14)
+    tabs = _rc.build_tables(n - col_bits, col_bits, list(range(n)), _adjacency(graph, n),
+                            (1 << graph.number_of_nodes()) - 1, device=backend.device,
+                            index_flip=prog.flip_mask)
+    state_bytes = 16 << n
+    if max_states is None:
+        max_states = max(1, backend.max_state_bytes // state_bytes)
+    chunk = min(n_sets, max_states)
+    states = torch.empty(chunk, 1 << n, dtype=torch.complex128, device=backend.device)
+    out = np.empty(n_sets)
+    for lo in range(0, n_sets, chunk):
+        hi = min(lo + chunk, n_sets)
+        backend.run(prog, auto, table[lo:hi], out=states[:hi - lo])
+        results = [_rc.reduce_and_score(torch.view_as_real(states[s]).reshape(-1), tabs,
+                                        threshold=2.0, k=1, cand_cap=1, amplitudes=True)
+                   for s in range(hi - lo)]
+        for s, res in enumerate(results):
+            sums = res.sums.cpu().numpy()
+            out[lo + s] = -(sums[1] if masked else sums[2])
+    return out
+
+
+def top_strings(dist, graph, cutoff=1, threshold=1e-5, best_weight=0, num_anc=None):
+    """Bitstrings among the `cutoff` most probable (p > threshold) that are independent sets
+    heavier than `best_weight` (mis.py:232-242), from the fused on-device top-k when present."""
+    from .utils.graph_funcs import is_indset
+    from .utils.helper_funcs import hamming_weight
+    n = graph.number_of_nodes()
+    if getattr(dist, "score", None) is not None and len(dist.score.top_x) >= cutoff:
+        top = [(format(x & ((1 << n) - 1), f"0{n}b"), p) for x, p in dist.score.get()["top"]]
+    else:
+        from .utils.helper_funcs import strip_ancillas
+        probs = strip_ancillas(dict(dist), num_anc if num_anc is not None else dist.n_wires - n)
+        top = sorted([(k, v) for k, v in probs.items() if v > threshold], key=lambda t: -t[1])
+    top = top[:cutoff]
+    return [(s, hamming_weight(s)) for s, _ in top if is_indset(s, graph)
+            and hamming_weight(s) > best_weight]

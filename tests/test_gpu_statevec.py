@@ -153,3 +153,41 @@ def test_amplitude_scoring_matches_oracle(cuda):
     assert abs(res["sum_pw"] - s_pw) < TOL
     order = np.lexsort((np.arange(p.size), -p))[:3]
     assert [x for x, _ in res["top"]] == [int(i) for i in order if p[i] > 1e-5]
+
+
+def test_uncut_cost_batch_matches_oracle(cuda):
+    """mis.uncut_cost == the reference's f(params) (mis.py:639-665) per parameter vector."""
+    import networkx as nx
+    from oracle import mis_oracle as mo
+    from qdc_b200 import mis
+    from qdc_b200.ansatz import dqv_ansatz
+    from qdc_b200.circuit import Parameter
+    n = 10
+    G = nx.random_regular_graph(3, n, seed=5)
+    syms = [Parameter(f"var_{i}") for i in range(n + 1)]
+    init = "0001000000"
+    circ = dqv_ansatz.gen_dqva(G, P=1, params=syms, init_state=init, mixer_order=list(range(n)))
+    used = circ.parameters
+    table = np.random.default_rng(2).uniform(0, 2 * np.pi, (5, len(used)))
+    be = _backend(cuda, tile_bits=6)
+    got = mis.uncut_cost(circ, be, G, params=table, param_order=used, max_states=2)
+    got_masked = mis.uncut_cost(circ, be, G, params=table, param_order=used, masked=True)
+    adj = mo.adjacency_masks(G, n)
+    for s in range(5):
+        bound = circ.bind_parameters(dict(zip(used, table[s])))
+        p = sv.probabilities(sv.simulate(n + 1, bound.to_instructions()))
+        _, s_pw = mo.score_array(p, n, 1, adj, masked=False)
+        _, s_pwok = mo.score_array(p, n, 1, adj, masked=True)
+        assert abs(got[s] + s_pw) < TOL and abs(got_masked[s] + s_pwok) < TOL
+
+
+def test_qaoa_plus_circuit_on_engine(cuda):
+    import networkx as nx
+    from qdc_b200.ansatz import qaoa_plus
+    G = nx.random_regular_graph(3, 12, seed=1)
+    circ = qaoa_plus.construct_qaoa_plus(2, G, [0.4, 0.9, 1.3, 0.25])
+    be = _backend(cuda, tile_bits=7)
+    prog, auto = be.compile(circ)
+    got = be.probabilities(be.run(prog, auto), prog).cpu().numpy()[0]
+    want = sv.probabilities(sv.simulate(12, circ.to_instructions()))
+    assert np.abs(got - want).max() < TOL
