@@ -5,6 +5,8 @@
 // filtered/sorted by top_probs (mis.py:232-233).
 //
 // Algorithmic bytes: sizeof(T) per output read once; nothing written but 3 doubles per CTA.
+#include <stdlib.h>
+
 #include "qdc_common.cuh"
 
 // ------------------------------------------------------------------------------------------
@@ -114,46 +116,99 @@ template <> __device__ __forceinline__ void unpack<float>(const float4& v, doubl
     o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
 }
 
-// One CTA walks whole 16-byte vectors; n_cols is a power of two >= Vec<T>::N so a vector never
-// straddles a row.  UNROLL independent 16-byte loads are issued before any is consumed.
+// A thread owns VN adjacent columns for its whole life: their table entries (col_x, col_wok) sit in
+// registers, so the steady state reads nothing but the distribution itself (16 bytes per thread
+// per row, UNROLL rows in flight) plus three warp-uniform row-table words per row.  A CTA covers
+// a strip of up to 256 * VN columns; when the table is narrower, the spare threads take
+// neighbouring rows.  n_cols is a power of two >= VN.
 template <typename T, int UNROLL>
-__global__ void __launch_bounds__(256) mis_reduce_kernel(
+__global__ void __launch_bounds__(256, 4) mis_reduce_kernel(
     const T* __restrict__ P, long long row_lo, long long n_rows, int col_shift,
     const double* __restrict__ d_norm, MisTables tab, CandSink sink, double* __restrict__ partials) {
     constexpr int VN = Vec<T>::N;
     using V = typename Vec<T>::type;
     __shared__ double scratch[3 * 8];
     const double inv_norm = d_norm ? 1.0 / *d_norm : 1.0;
-    const long long n_vec = (n_rows << col_shift) / VN;
-    const long long col_mask = (1ll << col_shift) - 1;
+    const long long n_cols = 1ll << col_shift;
+    const long long strip_cols = n_cols < 256ll * VN ? n_cols : 256ll * VN;
+    const int rows_per_pass = (int)(256ll * VN / strip_cols);
+    const long long e0 = (long long)threadIdx.x * VN;
+    const long long c = (long long)blockIdx.x * strip_cols + e0 % strip_cols;
+    const int rsub = (int)(e0 / strip_cols);
+    // per-column constants in registers: bits, weight as a double (no I2F per output), and the
+    // independence test folded into one AND (flag bits 62 / 63 carry "column / row is not itself
+    // independent", as in the contraction epilogue)
+    constexpr uint64_t FLAG_ROW_BAD = 1ull << 63, FLAG_COL_BAD = 1ull << 62;
+    uint64_t cx[VN], cf[VN];
+    double cwd[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+        cx[j] = __ldg(tab.col_x + c + j);
+        const uint32_t cw = __ldg(tab.col_wok + c + j);
+        cf[j] = cx[j] | FLAG_ROW_BAD | ((cw >> 8) & 1u ? 0ull : FLAG_COL_BAD);
+        cwd[j] = (double)(cw & 0xffu);
+    }
+    const double thr = sink.threshold;
     MisAccum acc = {0.0, 0.0, 0.0};
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    for (; v0 < n_vec; v0 += stride * UNROLL) {
-        V vals[UNROLL];
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-            const long long vi = v0 + u * stride;
-            if (vi < n_vec) vals[u] = ld_stream<T>(P + vi * VN);
+    // Rows are taken in batches of RB per CTA pass; the first RB * rows_per_pass threads fold each
+    // row's table words (flags, weight as a double) into shared memory once, so the streaming loop
+    // pays two LDS per row instead of three global loads and an int->double conversion per thread.
+    constexpr int RB = 32;
+    __shared__ uint64_t sh_rfl[RB * 4];
+    __shared__ double sh_rwd[RB * 4];
+    const long long r_step = (long long)gridDim.y * rows_per_pass;       // rows between passes
+    const int rpp = rows_per_pass > 4 ? 4 : rows_per_pass;               // (host guarantees <= 4 here)
+    for (long long rb0 = (long long)blockIdx.y * rows_per_pass; rb0 < n_rows; rb0 += r_step * RB) {
+        __syncthreads();
+        if (threadIdx.x < RB * rpp) {
+            const int k = threadIdx.x / rpp, sub = threadIdx.x % rpp;
+            const long long r = rb0 + (long long)k * r_step + sub;
+            uint64_t fl = 0; double wd = 0.0;
+            if (r < n_rows) {
+                const uint32_t rw = __ldg(tab.row_wok + row_lo + r);
+                fl = __ldg(tab.row_forb + row_lo + r) | FLAG_COL_BAD | ((rw >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
+                wd = (double)(rw & 0xffu);
+            }
+            sh_rfl[threadIdx.x] = fl; sh_rwd[threadIdx.x] = wd;
         }
+        __syncthreads();
+        for (int k0 = 0; k0 < RB; k0 += UNROLL) {
+            V vals[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-            const long long vi = v0 + u * stride;
-            if (vi >= n_vec) break;
-            const long long e = vi * VN;
-            const long long r = row_lo + (e >> col_shift);
-            const long long c = e & col_mask;
-            const uint64_t rx = __ldg(tab.row_x + r), rf = __ldg(tab.row_forb + r);
-            const uint32_t rw = __ldg(tab.row_wok + r);
-            double p[VN];
-            unpack<T>(vals[u], p);
+            for (int u = 0; u < UNROLL; ++u) {
+                const long long r = rb0 + (long long)(k0 + u) * r_step + rsub;
+                if (r < n_rows) vals[u] = ld_stream<T>(P + ((r << col_shift) + c));
+            }
 #pragma unroll
-            for (int j = 0; j < VN; ++j)
-                mis_accumulate(acc, p[j] * inv_norm, rx, rf, rw, __ldg(tab.col_x + c + j),
-                               __ldg(tab.col_wok + c + j), sink);
+            for (int u = 0; u < UNROLL; ++u) {
+                const long long r = rb0 + (long long)(k0 + u) * r_step + rsub;
+                if (r >= n_rows) break;
+                const uint64_t rfl = sh_rfl[(k0 + u) * rpp + rsub];
+                const double rwd = sh_rwd[(k0 + u) * rpp + rsub];
+                double p[VN];
+                unpack<T>(vals[u], p);
+#pragma unroll
+                for (int j = 0; j < VN; ++j) {
+                    const double pj = p[j] * inv_norm, w = rwd + cwd[j];
+                    acc.s_p += pj;
+                    acc.s_pw = fma(pj, w, acc.s_pw);
+                    if ((cf[j] & rfl) == 0ull) acc.s_pwok = fma(pj, w, acc.s_pwok);
+                    if (pj > thr) cand_emit(sink, __ldg(tab.row_x + row_lo + r) | cx[j], pj);
+                }
+            }
         }
     }
-    mis_block_store(acc, scratch, partials);
+    // one partial triple per CTA, linear CTA index
+    const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double a0 = warp_sum(acc.s_p), a1 = warp_sum(acc.s_pwok), a2 = warp_sum(acc.s_pw);
+    if (lane == 0) { scratch[warp] = a0; scratch[8 + warp] = a1; scratch[16 + warp] = a2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double x = 0, y = 0, z = 0;
+        for (int w = 0; w < 8; ++w) { x += scratch[w]; y += scratch[8 + w]; z += scratch[16 + w]; }
+        partials[3 * cta] = x; partials[3 * cta + 1] = y; partials[3 * cta + 2] = z;
+    }
 }
 
 // scalar fallback for tiny tables (n_cols < vector width)
@@ -221,21 +276,30 @@ extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_
     const int vn = dtype == 0 ? 2 : dtype == 1 ? 4 : 1;
     int blocks;
     QDC_REQUIRE(dtype != 2 || (((uintptr_t)d_P) & 15) == 0, "complex128 input must be 16-byte aligned");
-    if (n_cols >= vn && (((uintptr_t)d_P) & 15) == 0) {
+    if (n_cols >= vn && n_cols * 4 >= 256ll * vn && (((uintptr_t)d_P) & 15) == 0) {
         constexpr int UNROLL = 4;
-        const long long per_pass = 256ll * UNROLL * vn;
-        long long want = (total + per_pass - 1) / per_pass;
-        const long long cap = (long long)qdc_sm_count() * 8;      // 8 x 256 threads per SM
-        blocks = (int)(want < cap ? want : cap);
-        if (blocks < 1) blocks = 1;
+        const long long strip_cols = n_cols < 256ll * vn ? n_cols : 256ll * vn;
+        const long long gx = n_cols / strip_cols;
+        const int rows_per_pass = (int)(256ll * vn / strip_cols);
+        QDC_REQUIRE(gx <= QDC_MAX_PARTIALS, "table too wide for one launch");
+        // one resident wave (4 CTAs of 256 threads per SM): no tail, every CTA streams rows
+        long long gy = ((long long)qdc_sm_count() * 4) / gx * (dtype == 1 ? 3 : 2);   // measured best, profiles/r1_k8_tuning.log
+        if (const char* env = getenv("QDC_K8_WAVES")) gy = ((long long)qdc_sm_count() * 4) / gx * atoi(env);
+        const long long gy_need = (n_rows + (long long)rows_per_pass * UNROLL - 1) / ((long long)rows_per_pass * UNROLL);
+        if (gy > gy_need) gy = gy_need;
+        if (gy * gx > QDC_MAX_PARTIALS) gy = QDC_MAX_PARTIALS / gx;
+        if (gy < 1) gy = 1;
+        if (gy > 65535) gy = 65535;
+        blocks = (int)(gx * gy);
+        const dim3 grid((unsigned)gx, (unsigned)gy);
         if (dtype == 0)
-            mis_reduce_kernel<double, UNROLL><<<blocks, 256, 0, s>>>(
+            mis_reduce_kernel<double, UNROLL><<<grid, 256, 0, s>>>(
                 (const double*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
         else if (dtype == 2)
-            mis_reduce_kernel<Amp, UNROLL><<<blocks, 256, 0, s>>>(
+            mis_reduce_kernel<Amp, UNROLL><<<grid, 256, 0, s>>>(
                 (const Amp*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
         else
-            mis_reduce_kernel<float, UNROLL><<<blocks, 256, 0, s>>>(
+            mis_reduce_kernel<float, UNROLL><<<grid, 256, 0, s>>>(
                 (const float*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
     } else {
         blocks = (int)((total + 255) / 256);
