@@ -124,3 +124,59 @@ def time_build_sample(active0, active1, num_cuts, num_ranks, workdir, seed=0):
     vec, t_ranks, t_total = run_build(data, dest, active0 + active1, 2, terms, num_cuts,
                                       num_ranks)
     return float(1 << (active0 + active1)) / t_total, t_total, vec, (V0, V1)
+
+
+# ---------------------------------------------------------------------------------------------
+# the whole post-simulation pipeline through the reference's C programs
+# ---------------------------------------------------------------------------------------------
+def write_raw(eval_folder, subcircuit_idx, index, counter, inits, meas, probs):
+    """raw_%d_%d.txt as cutqc/evaluator.py:134-153 writes it."""
+    with open(os.path.join(eval_folder, f"raw_{subcircuit_idx}_{index}.txt"), "w") as f:
+        f.write("d=%d effective=%d\n" % (counter[subcircuit_idx]["d"], counter[subcircuit_idx]["effective"]))
+        f.write("".join("%s " % x for x in inits) + "\n")
+        f.write("".join("%s " % x for x in meas) + "\n")
+        f.write("".join("%e " % x for x in probs))
+
+
+def write_kron_terms_file(path, kronecker_terms, counter):
+    """subcircuit_kron_terms_%d.txt for one rank holding every term (cutqc/main.py:335-349)."""
+    with open(path, "w") as f:
+        f.write("%d subcircuits\n" % len(kronecker_terms))
+        for s in kronecker_terms:
+            f.write("subcircuit %d kron_terms %d num_effective %d\n"
+                    % (s, len(kronecker_terms[s]), counter[s]["effective"]))
+            for term, k in kronecker_terms[s].items():
+                f.write("subcircuit_kron_index=%d kron_term_len=%d\n" % (k, len(term)))
+                f.write("".join("%d,%d " % (c, i) for c, i in term) + "\n")
+
+
+def run_pipeline(workdir, full_circ_size, counter, raw_instances, kronecker_terms, write_layer_files,
+                 early_termination=0):
+    """raw_instances[s] = {mutated index: (inits, meas, probabilities)}.  Runs measure ->
+    vertical_collapse -> merge -> build exactly as cutqc/main.py:270-457 launches them (one
+    rank) and returns the reconstructed vector.  `write_layer_files(vc_folder, dd_folder)` must
+    write merge_0.txt / build_0.txt (cutqc/distributor.py:143-187)."""
+    ev = os.path.join(workdir, "eval")
+    vc = os.path.join(workdir, "vc")
+    dd = os.path.join(workdir, "dd")
+    for d in (ev, vc, dd):
+        os.makedirs(d, exist_ok=True)
+    for s, insts in raw_instances.items():
+        for idx, (inits, meas, probs) in insts.items():
+            write_raw(ev, s, idx, counter, inits, meas, probs)
+        run_measure(ev, full_circ_size, s, sorted(insts))
+    terms_file = os.path.join(ev, "subcircuit_kron_terms_0.txt")
+    write_kron_terms_file(terms_file, kronecker_terms, counter)
+    run_vertical_collapse(full_circ_size, terms_file, ev, vc, early_termination)
+    write_layer_files(vc, dd)
+    run_merge(os.path.join(dd, "merge_0.txt"), vc, dd)
+    with open(os.path.join(dd, "rank_0_summary.txt")) as f:
+        lines = f.readlines()
+    assert lines[-2].split(" = ")[0] == "Total merge time" and lines[-1] == "DONE"   # main.py:410
+    subprocess.run([os.path.join(REF_DIR, "build"), os.path.join(dd, "build_0.txt"), dd, dd, "0", "0"],
+                   check=True)
+    with open(os.path.join(dd, "rank_0_summary.txt")) as f:
+        lines = f.readlines()
+    assert lines[-2].split(" = ")[0] == "Total build time" and lines[-1] == "DONE"   # main.py:436
+    with open(os.path.join(dd, "reconstructed_prob_0.txt")) as f:
+        return np.array(f.readline().split(), dtype=np.float64)

@@ -1,0 +1,89 @@
+"""GPU parity of the CutQC path end to end (rows a13-a16): engine-simulated instances ->
+measure -> vertical_collapse -> merge -> build -> reorder, against the cutqc oracle stage by
+stage and against the uncut statevector.  float64 on the device: 1e-10."""
+import networkx as nx
+import numpy as np
+import pytest
+import torch
+
+from oracle import cutqc_oracle as co
+from oracle import mis_oracle as mo
+from oracle import statevector as sv
+import cutqc_cases as cc
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _be(cuda, **kw):
+    from qdc_b200.engine import B200Backend
+    return B200Backend(device=cuda, **kw)
+
+
+@pytest.mark.parametrize("name", list(cc.CASES))
+def test_stages_match_oracle_and_uncut(cuda, name):
+    from qdc_b200.cutqc.main import CutQC
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    counter, kron_o, terms_o, K, inter = co.evaluate(frags, cpm, early_termination=1)
+    job = CutQC.from_fragments(circ, frags, wpm, _be(cuda, tile_bits=3)).evaluate(early_termination=(0, 1))
+    assert job.counter == counter and job.num_cuts == K
+    for s in range(len(frags)):
+        measured = job.measured[s].cpu().numpy()
+        assert measured.shape[0] == len(inter["measured"][s])
+        for idx, want in inter["measured"][s].items():
+            assert np.abs(measured[idx] - want).max() < TOL
+        kron = job.kron[1][s].cpu().numpy()
+        present = job.kron_present[1][s].cpu().numpy()
+        assert bool(job.kron_present[0][s].all())
+        # "all zero" (vertical_collapse.c:64-72, |x| <= 1e-16) is decided on rounding noise for
+        # terms that vanish analytically: a term the oracle keeps must be kept; one it drops
+        # may survive here only as noise
+        for k in range(kron.shape[0]):
+            if k in kron_o[s]:
+                assert np.abs(kron[k] - kron_o[s][k]).max() < TOL
+                assert present[k] or np.abs(kron_o[s][k]).max() < 1e-12
+            else:
+                assert np.abs(kron[k]).max() < 1e-12
+    n = circ.num_qubits
+    full = sv.probabilities(sv.simulate(n, circ.to_instructions()))
+    for et in (0, 1):
+        layer, = job.post_process(early_termination=et)
+        assert np.abs(layer.dense().cpu().numpy() - full).max() < TOL
+        got = layer.to_dict()
+        assert set(got) == {format(x, f"0{n}b") for x in range(1 << n) if full[x] > 1e-10}
+
+
+@pytest.mark.parametrize("name,limit", [("chain3", 4), ("dqva6_fused", 3), ("there_and_back", 2)])
+def test_dynamic_definition_layers_match_oracle(cuda, name, limit):
+    from qdc_b200.cutqc.main import CutQC
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    counter, kron_o, terms_o, K, _ = co.evaluate(frags, cpm)
+    want = co.post_process(list(circ.qubits), frags, cpm, counter, kron_o, terms_o, K,
+                           qubit_limit=limit, recursion_depth=4)
+    job = CutQC.from_fragments(circ, frags, wpm, _be(cuda)).evaluate()
+    got = job.post_process(qubit_limit=limit, recursion_depth=4)
+    assert len(got) == len(want)
+    for layer, (schedule, vec, dist) in zip(got, want):
+        assert layer.schedule == schedule
+        assert np.abs(layer.prob.cpu().numpy() - vec).max() < TOL
+        d = layer.to_dict()
+        assert d.keys() == dist.keys() and all(abs(d[k] - dist[k]) < TOL for k in dist)
+
+
+def test_float32_output_and_fused_mis_score(cuda):
+    from qdc_b200.cutqc.main import CutQC
+    circ, frags, wpm, G = cc.dqva6(2, 5, True)
+    job = CutQC.from_fragments(circ, frags, wpm, _be(cuda)).evaluate()
+    layer, = job.post_process()
+    n = circ.num_qubits
+    full = sv.probabilities(sv.simulate(n, circ.to_instructions()))
+    num_anc = n - G.number_of_nodes()
+    res = layer.score(G, k=3, num_anc=num_anc).get()
+    probs = {format(x, f"0{n}b"): full[x] for x in range(1 << n)}
+    assert abs(res["sum_p"] - 1) < TOL
+    assert abs(-res["sum_pw_indset"] - mo.avg_cost(mo.strip_ancillas(probs, num_anc), G)) < TOL
+    layer32, = job.post_process(out_dtype=torch.float32)
+    assert layer32.prob.dtype == torch.float32
+    assert np.abs(layer32.dense().cpu().numpy() - full).max() < 2e-6
