@@ -408,7 +408,8 @@ def run_b200(args):
                 "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
         "gpu_launches": 8 * args.steps,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
-                     "unit": "TFLOP/s", "frac": achieved / dgemm_peak, "traffic": None,
+                     "unit": "TFLOP/s", "frac": achieved / dgemm_peak,
+                     "traffic": ncu_traffic(rb, cb, KDIM, ws),
                      "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64 DMMA pipe; "
                                     "MEASURED_PEAKS.json has no FP64 entry; nominal 37 TFLOP/s)",
                      "algorithmic_flops_per_launch": flops / ws,
@@ -435,6 +436,20 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     if ws > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic(rb, cb, kdim, ws):
+    """dram read + write bytes per launch of the contraction kernel from the committed
+    `ncu --set full` capture of this exact configuration (profiles/contract_traffic.json);
+    None when the configuration differs."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "contract_traffic.json")) as f:
+            rec = json.load(f)
+        if (rec["row_bits"], rec["col_bits"], rec["kdim"], rec["n_gpus"]) == (rb, cb, kdim, ws):
+            return rec["dram_bytes_read"] + rec["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        pass
+    return None
 
 
 def main():
