@@ -24,7 +24,7 @@ from . import recombine as _rc
 from .engine import B200Backend
 from .utils.cutting_funcs import sim_with_cutting
 
-__all__ = ["cut_cost", "uncut_cost", "top_strings"]
+__all__ = ["cut_cost", "uncut_cost", "qaoa_plus_cost", "top_strings"]
 
 
 def _adjacency(graph, n_wires):
@@ -75,6 +75,37 @@ def uncut_cost(circuit, backend: B200Backend, graph, params=None, param_order=No
         for s, res in enumerate(results):
             sums = res.sums.cpu().numpy()
             out[lo + s] = -(sums[1] if masked else sums[2])
+    return out
+
+
+def qaoa_plus_cost(circuit, backend: B200Backend, graph, Lambda: float, params=None,
+                   param_order=None, max_states: Optional[int] = None) -> np.ndarray:
+    """The QAOA+ cost closure f(params) = -expectation_value(counts, G, Lambda)
+    (ansatz/qaoa_plus.py:40-53, 60-70) in the exact limit, for every parameter vector:
+    -(sum_x p(x) |x| - Lambda sum_x p(x) #{edges inside x}), reduced on the device from the
+    amplitudes."""
+    if param_order is None:
+        param_order = list(circuit.parameters)
+    prog, auto = backend.compile(circuit, param_order=param_order)
+    n = prog.n_qubits
+    table = np.zeros((1, 0)) if params is None else np.asarray(params, dtype=np.float64)
+    if table.ndim == 1:
+        table = table.reshape(1, -1)
+    n_sets = table.shape[0]
+    adj = _adjacency(graph, n)
+    node_mask = (1 << graph.number_of_nodes()) - 1
+    if max_states is None:
+        max_states = max(1, backend.max_state_bytes // (16 << n))
+    chunk = min(n_sets, max_states)
+    states = torch.empty(chunk, 1 << n, dtype=torch.complex128, device=backend.device)
+    out = np.empty(n_sets)
+    for lo in range(0, n_sets, chunk):
+        hi = min(lo + chunk, n_sets)
+        backend.run(prog, auto, table[lo:hi], out=states[:hi - lo])
+        sums = [_rc.penalty_reduce(torch.view_as_real(states[s]).reshape(-1), n, adj, node_mask,
+                                   index_flip=prog.flip_mask, amplitudes=True) for s in range(hi - lo)]
+        for s, v in enumerate(torch.stack(sums).cpu().numpy()):
+            out[lo + s] = -(v[2] - Lambda * v[1])
     return out
 
 

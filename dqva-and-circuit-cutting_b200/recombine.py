@@ -258,3 +258,25 @@ def reduce_and_score(P: torch.Tensor, tables: MisTables, threshold: float = 1e-5
             _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp), "qdc_mis_reduce")
         _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
     return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, P, norm)
+
+
+def penalty_reduce(P: torch.Tensor, n_bits: int, adj: Sequence[int], node_mask: int,
+                   index_flip: int = 0, amplitudes: bool = False, stream=None) -> torch.Tensor:
+    """[sum p, sum p * #edges(x), sum p * |x|] over 2^n_bits entries (device float64[3]); the
+    QAOA+ objective of ansatz/qaoa_plus.py:40-53 is sums[2] - Lambda * sums[1].  `P`: float64 /
+    float32 probabilities, or with amplitudes=True a float64 view of complex128 amplitudes."""
+    lib = _lib.load()
+    dev = P.device
+    assert P.is_contiguous() and P.dtype in (torch.float64, torch.float32)
+    assert P.numel() == (2 if amplitudes else 1) << n_bits
+    ws = torch.empty(lib.qdc_penalty_workspace_bytes(), dtype=torch.uint8, device=dev)
+    partials = torch.empty(3 * lib.qdc_reduce_partials(), dtype=torch.float64, device=dev)
+    sums = torch.zeros(3, dtype=torch.float64, device=dev)
+    h_adj = (C.c_uint64 * max(len(adj), 1))(*[int(a) for a in adj])
+    with torch.cuda.device(dev):
+        _lib.check(lib.qdc_penalty_reduce(_lib.ptr(P), 2 if amplitudes else (0 if P.dtype == torch.float64 else 1),
+                                          n_bits, C.c_uint64(index_flip), h_adj, len(adj),
+                                          C.c_uint64(node_mask), _lib.ptr(ws), _lib.ptr(sums),
+                                          _lib.ptr(partials), _lib.stream_ptr(stream)),
+                   "qdc_penalty_reduce")
+    return sums

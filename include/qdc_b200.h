@@ -76,6 +76,18 @@ int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_t n_rows, i
                    unsigned long long* d_cand_count, int64_t cand_cap,
                    double* d_partials, void* stream);
 
+/* Penalised objective of QAOA+ (ansatz/qaoa_plus.py:40-53: expectation_value = sum_x p(x) (|x| -
+ * Lambda * #edges of the graph with both ends 1 in x)) over 2^n_bits entries, entry i holding
+ * basis state i ^ index_flip, bit b of the state = wire b.  dtype as qdc_mis_reduce (2: complex128
+ * amplitudes, p = |amp|^2).  h_adj[w] = neighbour mask of wire w, node_mask = wires that count.
+ * d_sums (3 doubles, accumulated into: zero them first) = [sum p, sum p * #edges, sum p * |x|];
+ * d_workspace: qdc_penalty_workspace_bytes() bytes; d_partials as qdc_mis_reduce.  One pass,
+ * sizeof(entry) bytes read per output, deterministic summation order. */
+int qdc_penalty_workspace_bytes(void);
+int qdc_penalty_reduce(const void* d_P, int dtype, int n_bits, uint64_t index_flip,
+                       const uint64_t* h_adj, int n_wires, uint64_t node_mask,
+                       void* d_workspace, double* d_sums, double* d_partials, void* stream);
+
 /* Top-k of the first min(*d_cand_count, cand_cap) candidates by (p descending, x ascending) --
  * sorted(...)[:cutoff] of mis.py:232-233 with a deterministic tie-break.  k <= 1024; unused
  * output slots get x = ~0, p = -inf.  Destroys d_cand_p.  The count is read on the device, so

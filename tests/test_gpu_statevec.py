@@ -191,3 +191,58 @@ def test_qaoa_plus_circuit_on_engine(cuda):
     got = be.probabilities(be.run(prog, auto), prog).cpu().numpy()[0]
     want = sv.probabilities(sv.simulate(12, circ.to_instructions()))
     assert np.abs(got - want).max() < TOL
+
+
+@pytest.mark.parametrize("n_bits,dtype", [(5, "f64"), (13, "f64"), (16, "f32"), (15, "amp")])
+def test_penalty_reduce_matches_direct_sums(cuda, n_bits, dtype):
+    """qdc_penalty_reduce: [sum p, sum p #edges, sum p |x|] with a flip frame and a non-node wire."""
+    import networkx as nx
+    import torch
+    from qdc_b200 import recombine as rc
+    rng = np.random.default_rng(n_bits)
+    n_nodes = n_bits - 1                                    # top wire is an ancilla
+    G = nx.gnm_random_graph(n_nodes, 2 * n_nodes, seed=3)
+    adj = [0] * n_bits
+    for a, b in G.edges():
+        adj[a] |= 1 << b
+        adj[b] |= 1 << a
+    flip = int(rng.integers(0, 1 << n_bits))
+    N = 1 << n_bits
+    if dtype == "amp":
+        amps = rng.normal(size=N) + 1j * rng.normal(size=N)
+        p = np.abs(amps) ** 2
+        dev = torch.view_as_real(torch.as_tensor(amps, device=cuda)).reshape(-1)
+    else:
+        p = rng.random(N).astype(np.float32 if dtype == "f32" else np.float64)
+        dev = torch.as_tensor(p, device=cuda)
+        p = p.astype(np.float64)
+    got = rc.penalty_reduce(dev, n_bits, adj, (1 << n_nodes) - 1, index_flip=flip,
+                            amplitudes=dtype == "amp").cpu().numpy()
+    x = (np.arange(N) ^ flip) & ((1 << n_nodes) - 1)
+    w = np.array([bin(v).count("1") for v in x])
+    e = np.zeros(N)
+    for a, b in G.edges():
+        e += ((x >> a) & (x >> b) & 1)
+    want = np.array([p.sum(), (p * e).sum(), (p * w).sum()])
+    assert np.abs(got - want).max() < 1e-9 * max(1.0, want.max())
+
+
+def test_qaoa_plus_cost_batch_matches_oracle(cuda):
+    """mis.qaoa_plus_cost == -expectation_value(counts, G, Lambda) (ansatz/qaoa_plus.py:40-53)."""
+    import networkx as nx
+    from oracle import mis_oracle as mo
+    from qdc_b200 import mis
+    from qdc_b200.ansatz import qaoa_plus
+    from qdc_b200.circuit import Parameter
+    n, P, Lambda = 10, 2, 1.5
+    G = nx.random_regular_graph(3, n, seed=7)
+    syms = [Parameter(f"var_{i}") for i in range(2 * P)]
+    circ = qaoa_plus.construct_qaoa_plus(P, G, syms)
+    table = np.random.default_rng(4).uniform(0, 2 * np.pi, (4, 2 * P))
+    got = mis.qaoa_plus_cost(circ, _backend(cuda, tile_bits=6), G, Lambda, params=table,
+                             param_order=syms, max_states=3)
+    for s in range(4):
+        bound = circ.bind_parameters(dict(zip(syms, table[s])))
+        p = sv.probabilities(sv.simulate(n, bound.to_instructions()))
+        counts = {format(x, f"0{n}b"): p[x] for x in range(1 << n)}
+        assert abs(got[s] + mo.qaoa_plus_expectation(counts, G, Lambda)) < TOL
