@@ -453,6 +453,269 @@ __global__ void __launch_bounds__(256) sv_pauli_tensor_kernel(const TensorArgs a
     }
 }
 
+// ---- fragment tensor, specialised layouts ------------------------------------------------------
+// (a) preparation-only fragment (m == 0, p <= 4): T[b][kappa] = sum_s F[kappa][s] |amp_s(b)|^2.
+//     A CTA owns 32 consecutive b: a warp reads 512 contiguous bytes of one state, probabilities
+//     go to R[s][bl] with a row pitch of 33 doubles, so the frame butterflies (lanes = bl) and
+//     the kappa-contiguous write (lanes = kappa) are both bank-conflict free.
+__device__ __forceinline__ void pauli4(double2& r00, double2& r01, double2& r10, double2& r11) {
+    const double2 i_ = make_double2(r00.x + r11.x, r00.y + r11.y);
+    const double2 x_ = make_double2(r01.x + r10.x, r01.y + r10.y);
+    const double2 y_ = make_double2(-(r01.y - r10.y), r01.x - r10.x);
+    const double2 z_ = make_double2(r00.x - r11.x, r00.y - r11.y);
+    r00 = i_; r01 = x_; r10 = y_; r11 = z_;
+}
+
+template <int N>   // N = number of axes (1 or 2) held in registers: v[4^N], digit 0 most significant
+__device__ __forceinline__ void pauli_axes(double2* v) {
+    if (N == 1) {
+        pauli4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) pauli4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) pauli4(v[e], v[4 + e], v[8 + e], v[12 + e]);
+    }
+}
+
+constexpr int PT_BB = 32, PT_PITCH = 33, PT_UNROLL = 8;
+
+__device__ __forceinline__ void frame4(const double* f, double& v0, double& v1, double& v2, double& v3) {
+    const double a0 = f[0] * v0 + f[1] * v1 + f[2] * v2 + f[3] * v3;
+    const double a1 = f[4] * v0 + f[5] * v1 + f[6] * v2 + f[7] * v3;
+    const double a2 = f[8] * v0 + f[9] * v1 + f[10] * v2 + f[11] * v3;
+    const double a3 = f[12] * v0 + f[13] * v1 + f[14] * v2 + f[15] * v3;
+    v0 = a0; v1 = a1; v2 = a2; v3 = a3;
+}
+
+template <int M>      // M = measured (exit) qubits of the fragment, 0..2
+__global__ void __launch_bounds__(256, 3) sv_prep_tensor_kernel(const TensorArgs a) {
+    extern __shared__ double R[];                                  // [n_kappa][PT_PITCH]
+    __shared__ double fr[16];
+    constexpr int N_PM = 1 << (2 * M), N_MU = 1 << M;
+    const int p = a.n_prep, n_s = 1 << (2 * p), n_kappa = n_s * N_PM;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long set = blockIdx.y, b0 = (long long)blockIdx.x * PT_BB;
+    if (tid < 16) fr[tid] = a.frame[tid];
+    const long long b = b0 + lane;
+    const bool live = b < a.n_b;
+    if (M == 0) {
+        // 1. |amp|^2, PT_UNROLL independent loads in flight per thread
+        const long long off = (long long)((uint64_t)b ^ a.flip);
+        for (int s0 = warp; s0 < n_s; s0 += 8 * PT_UNROLL) {
+            double2 v[PT_UNROLL];
+#pragma unroll
+            for (int u = 0; u < PT_UNROLL; ++u) {
+                const int s = s0 + 8 * u;
+                v[u] = (live && s < n_s) ? __ldcs(a.state + ((((long long)s * a.n_sets + set) << a.n) | off))
+                                         : make_double2(0.0, 0.0);
+            }
+#pragma unroll
+            for (int u = 0; u < PT_UNROLL; ++u) {
+                const int s = s0 + 8 * u;
+                if (s < n_s) R[s * PT_PITCH + lane] = v[u].x * v[u].x + v[u].y * v[u].y;
+            }
+        }
+    } else {
+        // 1. per (state, b): the 2^M amplitudes -> 4^M Pauli coordinates of the measured qubits
+        const uint64_t xb = expand_runs((uint64_t)(live ? b : 0), a.n_runs, a.run_pos, a.run_len);
+        constexpr int U = M == 1 ? 4 : 2;                          // states per thread per round
+        for (int s0 = warp; s0 < n_s; s0 += 8 * U) {
+            double2 am[U][N_MU];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int s = s0 + 8 * u;
+#pragma unroll
+                for (int mu = 0; mu < N_MU; ++mu) {
+                    uint64_t x = xb;
+#pragma unroll
+                    for (int j = 0; j < M; ++j) x |= (uint64_t)((mu >> j) & 1) << a.meas_q[j];
+                    am[u][mu] = (live && s < n_s)
+                        ? __ldcs(a.state + ((((long long)s * a.n_sets + set) << a.n) | (long long)(x ^ a.flip)))
+                        : make_double2(0.0, 0.0);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int s = s0 + 8 * u;
+                if (s >= n_s) continue;
+                double2 v[N_PM];
+#pragma unroll
+                for (int e = 0; e < N_PM; ++e) {
+                    int row = 0, col = 0;
+#pragma unroll
+                    for (int j = 0; j < M; ++j) {
+                        const int d = (e >> (2 * (M - 1 - j))) & 3;
+                        row |= (d >> 1) << j; col |= (d & 1) << j;
+                    }
+                    const double2 r = am[u][row], c = am[u][col];
+                    v[e] = make_double2(r.x * c.x + r.y * c.y, r.y * c.x - r.x * c.y);
+                }
+                pauli_axes<M == 0 ? 1 : M>(v);
+#pragma unroll
+                for (int e = 0; e < N_PM; ++e) R[(s * N_PM + e) * PT_PITCH + lane] = v[e].x;
+            }
+        }
+    }
+    __syncthreads();
+    // 2. frame inverse along every axis; two axes per pass while at least two remain
+    int j = 0;
+    for (; j + 1 < p; j += 2) {
+        const int inner = N_PM << (2 * (p - 2 - j));               // stride of digit j + 1
+        const int n_item = (n_kappa >> 4) * PT_BB;
+        for (int idx = tid; idx < n_item; idx += 256) {
+            const int bl = idx & 31, vec = idx >> 5;
+            const int lo = vec % inner, hi = vec / inner;
+            double* q = R + (size_t)(hi * 16 * inner + lo) * PT_PITCH + bl;
+            const int st = inner * PT_PITCH;
+            double v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = q[e * st];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) frame4(fr, v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);   // digit j + 1
+#pragma unroll
+            for (int e = 0; e < 4; ++e) frame4(fr, v[e], v[4 + e], v[8 + e], v[12 + e]);                   // digit j
+#pragma unroll
+            for (int e = 0; e < 16; ++e) q[e * st] = v[e];
+        }
+        __syncthreads();
+    }
+    if (j < p) {                                                   // odd p: the last prep axis (stride 4^M)
+        const int n_item = (n_kappa >> 2) * PT_BB;
+        for (int idx = tid; idx < n_item; idx += 256) {
+            const int bl = idx & 31, vec = idx >> 5;
+            const int lo = vec % N_PM, hi = vec / N_PM;
+            double* q = R + (size_t)(hi * 4 * N_PM + lo) * PT_PITCH + bl;
+            constexpr int st = N_PM * PT_PITCH;
+            double v0 = q[0], v1 = q[st], v2 = q[2 * st], v3 = q[3 * st];
+            frame4(fr, v0, v1, v2, v3);
+            q[0] = v0; q[st] = v1; q[2 * st] = v2; q[3 * st] = v3;
+        }
+        __syncthreads();
+    }
+    // 3. T[set][b][kappa_out], lanes along kappa
+    for (int idx = tid; idx < PT_BB * n_kappa; idx += 256) {
+        const int kap = idx % n_kappa, bl = idx / n_kappa;
+        if (b0 + bl >= a.n_b) break;
+        long long ko = 0;
+        for (int ax = 0; ax < p + M; ++ax) ko += (long long)((kap >> (2 * (p + M - 1 - ax))) & 3) * a.stride[ax];
+        __stcs(a.T + (set * a.n_b + b0 + bl) * a.ld + ko, R[kap * PT_PITCH + bl]);
+    }
+}
+
+// (b) measurement-only fragment (p == 0, m = M_HI + M_LO <= 4): per b the 2^m amplitudes give
+//     4^m real Pauli coordinates.  Pass 1: a thread forms the matrix-unit products for the low
+//     M_LO measured axes in registers and applies their (e00,e01,e10,e11)->(I,X,Y,Z) butterflies;
+//     pass 2 (after one exchange through shared memory, pitch 4^M_LO + 1 complex) does the same for
+//     the high axes and stores the real parts straight to T, 4^M_LO consecutive doubles per lane group.
+template <int M_HI, int M_LO>
+__global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a) {
+    constexpr int M = M_HI + M_LO, N_MU = 1 << M, N_LO = 1 << (2 * M_LO), N_HI = 1 << (2 * M_HI);
+    constexpr int PITCH = N_LO + 1;
+    extern __shared__ double2 sh_raw[];
+    double2* amp = sh_raw;                                         // [bb][N_MU]
+    double2* C = sh_raw + (size_t)a.bb * N_MU;                     // [bb][N_HI][PITCH]
+    const int tid = threadIdx.x;
+    const long long set = blockIdx.y, b0 = (long long)blockIdx.x * a.bb;
+    for (int idx = tid; idx < a.bb * N_MU; idx += 256) {
+        const int bl = idx % a.bb, mu = idx / a.bb;
+        const long long b = b0 + bl;
+        double2 v = make_double2(0.0, 0.0);
+        if (b < a.n_b) {
+            uint64_t x = expand_runs((uint64_t)b, a.n_runs, a.run_pos, a.run_len);
+#pragma unroll
+            for (int j = 0; j < M; ++j) x |= (uint64_t)((mu >> j) & 1) << a.meas_q[j];
+            v = __ldcs(a.state + ((set << a.n) | (long long)(x ^ a.flip)));
+        }
+        amp[bl * N_MU + mu] = v;
+    }
+    __syncthreads();
+    // axis j (most significant digit first) <-> measured qubit j <-> bit j of mu.
+    // high axes = 0 .. M_HI-1, low axes = M_HI .. M-1.
+    if (M_HI == 0) {
+        for (int idx = tid; idx < a.bb; idx += 256) {
+            const double2* am = amp + idx * N_MU;
+            double2 v[N_LO];
+#pragma unroll
+            for (int e = 0; e < N_LO; ++e) {
+                int row = 0, col = 0;
+#pragma unroll
+                for (int j = 0; j < M_LO; ++j) {
+                    const int d = (e >> (2 * (M_LO - 1 - j))) & 3;
+                    row |= (d >> 1) << j; col |= (d & 1) << j;
+                }
+                const double2 r = am[row], c = am[col];
+                v[e] = make_double2(r.x * c.x + r.y * c.y, r.y * c.x - r.x * c.y);
+            }
+            pauli_axes<M_LO>(v);
+            const long long b = b0 + idx;
+            if (b < a.n_b) {
+#pragma unroll
+                for (int e = 0; e < N_LO; ++e) {
+                    long long ko = 0;
+#pragma unroll
+                    for (int j = 0; j < M_LO; ++j) ko += (long long)((e >> (2 * (M_LO - 1 - j))) & 3) * a.stride[j];
+                    a.T[(set * a.n_b + b) * a.ld + ko] = v[e].x;
+                }
+            }
+        }
+        return;
+    }
+    // pass 1: item = (bl, hi digits); products over the low axes, low butterflies
+    for (int idx = tid; idx < a.bb * N_HI; idx += 256) {
+        const int h = idx % N_HI, bl = idx / N_HI;
+        int row_h = 0, col_h = 0;
+#pragma unroll
+        for (int j = 0; j < M_HI; ++j) {
+            const int d = (h >> (2 * (M_HI - 1 - j))) & 3;
+            row_h |= (d >> 1) << j; col_h |= (d & 1) << j;
+        }
+        const double2* am = amp + bl * N_MU;
+        double2 v[N_LO];
+#pragma unroll
+        for (int e = 0; e < N_LO; ++e) {
+            int row = row_h, col = col_h;
+#pragma unroll
+            for (int j = 0; j < M_LO; ++j) {
+                const int d = (e >> (2 * (M_LO - 1 - j))) & 3;
+                row |= (d >> 1) << (M_HI + j); col |= (d & 1) << (M_HI + j);
+            }
+            const double2 r = am[row], c = am[col];
+            v[e] = make_double2(r.x * c.x + r.y * c.y, r.y * c.x - r.x * c.y);
+        }
+        pauli_axes<M_LO>(v);
+        // exchange layout C[bl][lo digits][hi digits] with pitch N_HI + 1 would serve pass 2's
+        // reads; we use [bl][e][h] so that this write has lanes (h fastest) on consecutive words
+        double2* dst = C + (size_t)bl * N_LO * (N_HI + 1) + h;
+#pragma unroll
+        for (int e = 0; e < N_LO; ++e) dst[e * (N_HI + 1)] = v[e];
+    }
+    __syncthreads();
+    // pass 2: item = (bl, lo digits); high butterflies, real parts to T
+    for (int idx = tid; idx < a.bb * N_LO; idx += 256) {
+        const int e = idx % N_LO, bl = idx / N_LO;
+        const double2* src = C + (size_t)bl * N_LO * (N_HI + 1) + e * (N_HI + 1);
+        double2 v[N_HI];
+#pragma unroll
+        for (int h = 0; h < N_HI; ++h) v[h] = src[h];
+        pauli_axes<M_HI>(v);
+        const long long b = b0 + bl;
+        if (b >= a.n_b) continue;
+        long long ko_lo = 0;
+#pragma unroll
+        for (int j = 0; j < M_LO; ++j) ko_lo += (long long)((e >> (2 * (M_LO - 1 - j))) & 3) * a.stride[M_HI + j];
+        double* out = a.T + (set * a.n_b + b) * a.ld + ko_lo;
+#pragma unroll
+        for (int h = 0; h < N_HI; ++h) {
+            long long ko = 0;
+#pragma unroll
+            for (int j = 0; j < M_HI; ++j) ko += (long long)((h >> (2 * (M_HI - 1 - j))) & 3) * a.stride[j];
+            __stcs(out + ko, v[h].x);
+        }
+    }
+    (void)PITCH;
+}
+
 // ---- host: compiler ---------------------------------------------------------------------------
 struct LGate {                 // lowered gate (after the X frame)
     int src, kind, target, conj;
@@ -840,6 +1103,51 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
         QDC_REQUIRE(a.stride[ax] >= 0 && 3 * a.stride[ax] < ld, "axis stride");
     }
     if (n_prep) for (int k = 0; k < 16; ++k) a.frame[k] = h_frame[k];
+    a.ld = ld;
+    if (n_prep >= 1 && n_meas <= 2 && n_prep + n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC")) {
+        const size_t smem = (size_t)n_kappa * PT_PITCH * sizeof(double);
+        const long long gx = (a.n_b + PT_BB - 1) / PT_BB;
+        QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
+        const dim3 grid((unsigned)gx, (unsigned)n_sets);
+        cudaStream_t st = (cudaStream_t)stream;
+#define QDC_PREP_CASE(MM)                                                                                   \
+        {                                                                                                   \
+            QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_prep_tensor_kernel<MM>,                                  \
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
+            sv_prep_tensor_kernel<MM><<<grid, 256, smem, st>>>(a);                                          \
+        }
+        if (n_meas == 0) QDC_PREP_CASE(0)
+        else if (n_meas == 1) QDC_PREP_CASE(1)
+        else QDC_PREP_CASE(2)
+#undef QDC_PREP_CASE
+        QDC_CHECK_LAUNCH();
+        return QDC_OK;
+    }
+    if (n_prep == 0 && n_meas >= 1 && n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC")) {
+        const int m_lo = n_meas < 2 ? n_meas : 2, m_hi = n_meas - m_lo;
+        const int n_lo = 1 << (2 * m_lo), n_hi = 1 << (2 * m_hi);
+        int bb = n_meas <= 2 ? 256 : (n_meas == 3 ? 64 : 16);
+        if (bb > a.n_b) bb = (int)a.n_b;
+        a.bb = bb;
+        const size_t smem = (size_t)bb * ((size_t)(1 << n_meas) + (m_hi ? (size_t)n_lo * (n_hi + 1) : 0)) * 16;
+        const long long gx = (a.n_b + bb - 1) / bb;
+        QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
+        const dim3 grid((unsigned)gx, (unsigned)n_sets);
+        cudaStream_t st = (cudaStream_t)stream;
+#define QDC_MEAS_CASE(HI, LO)                                                                               \
+        {                                                                                                   \
+            QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_meas_tensor_kernel<HI, LO>,                              \
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
+            sv_meas_tensor_kernel<HI, LO><<<grid, 256, smem, st>>>(a);                                      \
+        }
+        if (n_meas == 1) QDC_MEAS_CASE(0, 1)
+        else if (n_meas == 2) QDC_MEAS_CASE(0, 2)
+        else if (n_meas == 3) QDC_MEAS_CASE(1, 2)
+        else QDC_MEAS_CASE(2, 2)
+#undef QDC_MEAS_CASE
+        QDC_CHECK_LAUNCH();
+        return QDC_OK;
+    }
     int bb = (int)(2048 / n_kappa);
     if (bb < 1) bb = 1;
     if (bb > a.n_b) bb = (int)a.n_b;

@@ -58,6 +58,10 @@ def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce):
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "one":
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4)
+        case("C4 meas side", 20, [], [3, 8, 12, 17], 1, 12, 4)
+        case("C2 like", 14, [2, 9], [5], 64, 12, 4)
+        case("C2 prep", 14, [2, 9, 11], [], 64, 12, 4)
+        case("C2 meas", 14, [], [5, 8, 12], 64, 12, 4)
         sys.exit(0)
     for t, c in [(12, 4), (13, 4), (11, 4), (12, 5), (12, 3), (10, 4)]:
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, t, c)
