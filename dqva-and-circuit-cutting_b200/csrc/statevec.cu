@@ -90,6 +90,16 @@ __device__ __forceinline__ uint64_t expand_runs(uint64_t l, int n_runs, const ui
     return l;
 }
 
+// deposit the bits of i into the zero positions of fm (ascending); registers only
+__device__ __forceinline__ uint32_t deposit_bits(uint32_t i, uint32_t fm) {
+    while (fm) {
+        const uint32_t below = (fm & (0u - fm)) - 1u;          // bits under the lowest fixed position
+        i = ((i & ~below) << 1) | (i & below);
+        fm &= fm - 1u;
+    }
+    return i;
+}
+
 __device__ __forceinline__ uint32_t insert_fixed(uint32_t i, int n_fixed, const uint8_t* fixed) {
     for (int f = 0; f < n_fixed; ++f) {
         const int p = fixed[f];
@@ -139,14 +149,13 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
         for (uint32_t l = tid; l < T; l += nthr, x = ((x | hole) + x_step) & ~hole) {
             const uint64_t full = x | base;
             double2 amp = make_double2(0.0, 0.0);
-            if ((full & ~a.prep_mask) == 0ull) {
+            if ((full & ~a.prep_mask) == 0ull) {                   // rare: 2^n_prep basis states per state
                 amp = make_double2(1.0, 0.0);
-#pragma unroll
-                for (int j = 0; j < MAX_PREP; ++j)
-                    if (j < a.n_prep) {
-                        const int bit = (int)((full >> a.prep_q[j]) & 1ull);
-                        amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
-                    }
+#pragma unroll 1
+                for (int j = 0; j < a.n_prep; ++j) {
+                    const int bit = (int)((full >> a.prep_q[j]) & 1ull);
+                    amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
+                }
             }
             tile[l] = amp;
         }
@@ -191,13 +200,22 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
                 const double2 m10 = make_double2(m[4], m[5]), m11 = make_double2(m[6], m[7]);
                 const uint32_t count = 1u << (a.t - op.n_fixed), tb = 1u << op.tbit;
                 const uint32_t fm = op.fmask, lval = op.lval;
-                uint32_t e = insert_fixed(tid, op.n_fixed, op.fixed);
-                const uint32_t e_step = insert_fixed(nthr, op.n_fixed, op.fixed);
-                for (uint32_t k = tid; k < count; k += nthr, e = ((e | fm) + e_step) & ~fm) {
-                    const uint32_t l0 = e | lval, l1 = l0 | tb;
-                    const double2 a0 = tile[l0], a1 = tile[l1];
-                    tile[l0] = cfma(m00, a0, cmul(m01, a1));
-                    tile[l1] = cfma(m10, a0, cmul(m11, a1));
+                uint32_t e = deposit_bits(tid, fm);
+                if (count <= nthr) {                               // controlled gates: at most one pair per thread
+                    if (tid < count) {
+                        const uint32_t l0 = e | lval, l1 = l0 | tb;
+                        const double2 a0 = tile[l0], a1 = tile[l1];
+                        tile[l0] = cfma(m00, a0, cmul(m01, a1));
+                        tile[l1] = cfma(m10, a0, cmul(m11, a1));
+                    }
+                } else {
+                    const uint32_t e_step = deposit_bits(nthr, fm);
+                    for (uint32_t k = tid; k < count; k += nthr, e = ((e | fm) + e_step) & ~fm) {
+                        const uint32_t l0 = e | lval, l1 = l0 | tb;
+                        const double2 a0 = tile[l0], a1 = tile[l1];
+                        tile[l0] = cfma(m00, a0, cmul(m01, a1));
+                        tile[l1] = cfma(m10, a0, cmul(m11, a1));
+                    }
                 }
                 ++i;
             } else if (op.diag_run >= 1) {
@@ -233,8 +251,8 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
                 const bool local = op.tbit >= 0;
                 const double2 dg = ((base >> op.gtarget) & 1ull) ? d1 : d0;
                 const uint32_t fm = op.fmask, lval = op.lval;
-                uint32_t e = insert_fixed(tid, op.n_fixed, op.fixed);
-                const uint32_t e_step = insert_fixed(nthr, op.n_fixed, op.fixed);
+                uint32_t e = deposit_bits(tid, fm);
+                const uint32_t e_step = count > nthr ? deposit_bits(nthr, fm) : 0u;
                 for (uint32_t k = tid; k < count; k += nthr, e = ((e | fm) + e_step) & ~fm) {
                     const uint32_t l = e | lval;
                     const double2 d = local ? (((l >> op.tbit) & 1u) ? d1 : d0) : dg;
@@ -309,6 +327,7 @@ struct TensorArgs {
     long long n_sets, n_b, ld;
     uint64_t flip;
     int n, n_prep, n_meas, bb;      // bb = final-bit values per CTA
+    int n_basis;                    // basis-input mode: leading axes that select one of 2^n_basis states
     int n_runs;                     // runs of measured-qubit positions (holes of the b deposit)
     uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
     uint8_t meas_q[8];
@@ -622,10 +641,17 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
         const long long b = b0 + bl;
         double2 v = make_double2(0.0, 0.0);
         if (b < a.n_b) {
+            // axis j <-> bit j of mu: the first n_basis axes pick the basis-input state (first
+            // prep qubit = most significant digit of the state number), the rest a measured qubit
             uint64_t x = expand_runs((uint64_t)b, a.n_runs, a.run_pos, a.run_len);
+            long long init = 0;
 #pragma unroll
-            for (int j = 0; j < M; ++j) x |= (uint64_t)((mu >> j) & 1) << a.meas_q[j];
-            v = __ldcs(a.state + ((set << a.n) | (long long)(x ^ a.flip)));
+            for (int j = 0; j < M; ++j) {
+                const uint64_t bit = (uint64_t)((mu >> j) & 1);
+                if (j < a.n_basis) init |= (long long)bit << (a.n_basis - 1 - j);
+                else x |= bit << a.meas_q[j - a.n_basis];
+            }
+            v = __ldcs(a.state + (((init * a.n_sets + set) << a.n) | (long long)(x ^ a.flip)));
         }
         amp[bl * N_MU + mu] = v;
     }
@@ -653,9 +679,14 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
 #pragma unroll
                 for (int e = 0; e < N_LO; ++e) {
                     long long ko = 0;
+                    bool neg = false;                 // Tr(P^T N) on input axes: Y^T = -Y
 #pragma unroll
-                    for (int j = 0; j < M_LO; ++j) ko += (long long)((e >> (2 * (M_LO - 1 - j))) & 3) * a.stride[j];
-                    a.T[(set * a.n_b + b) * a.ld + ko] = v[e].x;
+                    for (int j = 0; j < M_LO; ++j) {
+                        const int d = (e >> (2 * (M_LO - 1 - j))) & 3;
+                        ko += (long long)d * a.stride[j];
+                        neg ^= (j < a.n_basis) && d == 2;
+                    }
+                    a.T[(set * a.n_b + b) * a.ld + ko] = neg ? -v[e].x : v[e].x;
                 }
             }
         }
@@ -702,15 +733,25 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
         const long long b = b0 + bl;
         if (b >= a.n_b) continue;
         long long ko_lo = 0;
+        bool neg_lo = false;
 #pragma unroll
-        for (int j = 0; j < M_LO; ++j) ko_lo += (long long)((e >> (2 * (M_LO - 1 - j))) & 3) * a.stride[M_HI + j];
+        for (int j = 0; j < M_LO; ++j) {
+            const int d = (e >> (2 * (M_LO - 1 - j))) & 3;
+            ko_lo += (long long)d * a.stride[M_HI + j];
+            neg_lo ^= (M_HI + j < a.n_basis) && d == 2;
+        }
         double* out = a.T + (set * a.n_b + b) * a.ld + ko_lo;
 #pragma unroll
         for (int h = 0; h < N_HI; ++h) {
             long long ko = 0;
+            bool neg = neg_lo;
 #pragma unroll
-            for (int j = 0; j < M_HI; ++j) ko += (long long)((h >> (2 * (M_HI - 1 - j))) & 3) * a.stride[j];
-            __stcs(out + ko, v[h].x);
+            for (int j = 0; j < M_HI; ++j) {
+                const int d = (h >> (2 * (M_HI - 1 - j))) & 3;
+                ko += (long long)d * a.stride[j];
+                neg ^= (j < a.n_basis) && d == 2;
+            }
+            __stcs(out + ko, neg ? -v[h].x : v[h].x);
         }
     }
     (void)PITCH;
@@ -1071,7 +1112,9 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
     QDC_REQUIRE(n_qubits >= 1 && n_qubits <= 40 && n_sets >= 1, "shape");
     QDC_REQUIRE(n_prep >= 0 && n_meas >= 0 && n_meas <= 6 && n_prep + n_meas <= 6, "at most 6 cut axes per fragment");
     QDC_REQUIRE(n_meas <= n_qubits, "n_meas");
-    QDC_REQUIRE(n_prep == 0 || (n_codes == 4 && h_frame != nullptr), "4 preparation states and their frame required");
+    QDC_REQUIRE(n_prep == 0 || n_codes == 2 || (n_codes == 4 && h_frame != nullptr),
+                "n_codes 4 (preparation states + frame) or 2 (basis inputs)");
+    QDC_REQUIRE(n_prep == 0 || n_codes != 2 || n_prep + n_meas <= 4, "basis-input mode handles at most 4 cut axes");
     QDC_REQUIRE(n_meas == 0 || h_meas_qubits != nullptr, "meas qubits");
     QDC_REQUIRE((flip_mask >> n_qubits) == 0, "flip_mask");
     TensorArgs a;
@@ -1102,9 +1145,11 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
         a.stride[ax] = h_axis_stride ? h_axis_stride[ax] : nat;
         QDC_REQUIRE(a.stride[ax] >= 0 && 3 * a.stride[ax] < ld, "axis stride");
     }
-    if (n_prep) for (int k = 0; k < 16; ++k) a.frame[k] = h_frame[k];
+    if (n_prep && n_codes == 4) for (int k = 0; k < 16; ++k) a.frame[k] = h_frame[k];
+    const bool basis = n_prep > 0 && n_codes == 2;
+    a.n_basis = basis ? n_prep : 0;
     a.ld = ld;
-    if (n_prep >= 1 && n_meas <= 2 && n_prep + n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC")) {
+    if (!basis && n_prep >= 1 && n_meas <= 2 && n_prep + n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC")) {
         const size_t smem = (size_t)n_kappa * PT_PITCH * sizeof(double);
         const long long gx = (a.n_b + PT_BB - 1) / PT_BB;
         QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
@@ -1123,26 +1168,28 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
         QDC_CHECK_LAUNCH();
         return QDC_OK;
     }
-    if (n_prep == 0 && n_meas >= 1 && n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC")) {
-        const int m_lo = n_meas < 2 ? n_meas : 2, m_hi = n_meas - m_lo;
+    if (basis || (n_prep == 0 && n_meas >= 1 && n_meas <= 4 && !getenv("QDC_SV_TENSOR_GENERIC"))) {
+        const int n_ax = basis ? n_prep + n_meas : n_meas;        // amplitude-index axes
+        const int m_lo = n_ax < 2 ? n_ax : 2, m_hi = n_ax - m_lo;
         const int n_lo = 1 << (2 * m_lo), n_hi = 1 << (2 * m_hi);
-        int bb = n_meas <= 2 ? 256 : (n_meas == 3 ? 64 : 16);
+        int bb = n_ax <= 2 ? 256 : (n_ax == 3 ? 64 : 16);
         if (bb > a.n_b) bb = (int)a.n_b;
         a.bb = bb;
-        const size_t smem = (size_t)bb * ((size_t)(1 << n_meas) + (m_hi ? (size_t)n_lo * (n_hi + 1) : 0)) * 16;
+        const size_t smem = (size_t)bb * ((size_t)(1 << n_ax) + (m_hi ? (size_t)n_lo * (n_hi + 1) : 0)) * 16;
         const long long gx = (a.n_b + bb - 1) / bb;
         QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
         const dim3 grid((unsigned)gx, (unsigned)n_sets);
         cudaStream_t st = (cudaStream_t)stream;
+        const int n_meas_axes = n_ax;
 #define QDC_MEAS_CASE(HI, LO)                                                                               \
         {                                                                                                   \
             QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_meas_tensor_kernel<HI, LO>,                              \
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
             sv_meas_tensor_kernel<HI, LO><<<grid, 256, smem, st>>>(a);                                      \
         }
-        if (n_meas == 1) QDC_MEAS_CASE(0, 1)
-        else if (n_meas == 2) QDC_MEAS_CASE(0, 2)
-        else if (n_meas == 3) QDC_MEAS_CASE(1, 2)
+        if (n_meas_axes == 1) QDC_MEAS_CASE(0, 1)
+        else if (n_meas_axes == 2) QDC_MEAS_CASE(0, 2)
+        else if (n_meas_axes == 3) QDC_MEAS_CASE(1, 2)
         else QDC_MEAS_CASE(2, 2)
 #undef QDC_MEAS_CASE
         QDC_CHECK_LAUNCH();

@@ -25,7 +25,7 @@ from . import _lib
 from .circuit import ParameterExpression
 
 __all__ = ["B200Backend", "CompiledCircuit", "QdcGate", "lower_instructions", "SIC_KETS",
-           "SIC_FRAME", "CUTQC_KETS", "CUTQC_FRAME"]
+           "SIC_FRAME", "CUTQC_KETS", "CUTQC_FRAME", "BASIS_KETS"]
 
 # gate kinds of include/qdc_b200.h
 G_ID, G_X, G_Y, G_Z, G_H, G_S, G_SDG, G_T, G_TDG, G_RX, G_RY, G_RZ, G_U1, G_U2 = range(14)
@@ -75,6 +75,9 @@ SIC_FRAME = _frame(SIC_KETS)
 CUTQC_KETS = np.array([[1, 0], [0, 1], [1 / math.sqrt(2), 1 / math.sqrt(2)],
                        [1 / math.sqrt(2), 1j / math.sqrt(2)]], dtype=complex)
 CUTQC_FRAME = _frame(CUTQC_KETS)
+# computational-basis inputs |0>, |1>: by linearity the 2^p basis evolutions carry everything the
+# 4^p preparation variants do (see B200Backend.pauli_tensor, basis_inputs=True)
+BASIS_KETS = np.array([[1, 0], [0, 1]], dtype=complex)
 
 
 def _code_table(kets) -> np.ndarray:
@@ -316,8 +319,15 @@ class B200Backend:
     def pauli_tensor(self, states: torch.Tensor, prog: CompiledCircuit, n_sets: int, n_prep: int,
                      meas_qubits: Sequence[int], frame=None, axis_strides=None,
                      ld: Optional[int] = None, out: Optional[torch.Tensor] = None,
-                     stream=None) -> torch.Tensor:
-        """T[set, b, kappa]: the fragment's Choi blocks in the Pauli basis (float64)."""
+                     stream=None, basis_inputs: bool = False) -> torch.Tensor:
+        """T[set, b, kappa]: the fragment's Choi blocks in the Pauli basis (float64).
+
+        basis_inputs=False: `states` are the 4^p preparation variants (`run(..., kets=SIC_KETS)`
+        or CUTQC_KETS) and `frame` their dual frame.  basis_inputs=True: `states` are the 2^p
+        evolutions of the computational-basis inputs (`run(..., kets=BASIS_KETS)`); since every
+        preparation is a linear combination of them, T[b, a] = Tr(P_a M_b) with (M_b)_{x'x} =
+        conj(psi_x'(b)) psi_x(b) -- the same numbers from 2^p instead of 4^p simulations
+        (p + m <= 4)."""
         lib = _lib.load()
         n, m = prog.n_qubits, len(meas_qubits)
         n_axes = n_prep + m
@@ -337,7 +347,8 @@ class B200Backend:
             st = (C.c_int64 * max(n_axes, 1))(*[int(s) for s in axis_strides])
         with torch.cuda.device(states.device):
             _lib.check(lib.qdc_sv_pauli_tensor(
-                _lib.ptr(states), n, n_sets, C.c_uint64(prog.flip_mask), n_prep, 4,
+                _lib.ptr(states), n, n_sets, C.c_uint64(prog.flip_mask), n_prep,
+                2 if basis_inputs else 4,
                 fr.ctypes.data_as(C.POINTER(C.c_double)), mq, m, st, _lib.ptr(out), ld,
                 _lib.stream_ptr(stream)), "qdc_sv_pauli_tensor")
         return out

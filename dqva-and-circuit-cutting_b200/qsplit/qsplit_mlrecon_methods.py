@@ -34,7 +34,7 @@ import torch
 
 from .. import _lib
 from .. import recombine as _rc
-from ..engine import B200Backend, SIC_FRAME, SIC_KETS
+from ..engine import B200Backend, BASIS_KETS, SIC_FRAME, SIC_KETS
 
 __all__ = ["get_frag_num", "identify_stitches", "identify_frag_targets", "fragment_cuts",
            "fragment_variants", "united_axis_permutation", "united_bit_wires",
@@ -229,7 +229,9 @@ _MEAS_SUFFIX = {"Z": (), "X": ("h",), "Y": ("sdg", "h")}          # ignis measur
 
 class FragmentData(Mapping):
     """Tomography data of ONE fragment: the final states of its 4^p preparation variants
-    (x n_sets parameter vectors), resident on the device.
+    (x n_sets parameter vectors), resident on the device -- or, when the fragment has at most 4
+    cut ends, of the 2^p computational-basis inputs those variants are linear combinations of
+    (`basis_inputs`): the exact-limit Choi blocks are the same, from 2^p simulations.
 
     As a Mapping it is the reference's `organize_tomography_data` layout (:169-213),
     `{final_bits: {(prep_label, meas_state): counts}}` for parameter set 0, with
@@ -237,13 +239,15 @@ class FragmentData(Mapping):
     too, so it is meant for fragments small enough for a Python dict."""
 
     def __init__(self, backend, fragment, prep_qubits, meas_qubits, states, prog, auto,
-                 n_sets, shots, cut_labels, params, param_order, prep_basis="SIC"):
+                 n_sets, shots, cut_labels, params, param_order, prep_basis="SIC",
+                 basis_inputs=False):
         self.backend, self.fragment = backend, fragment
         self.prep_qubits, self.meas_qubits = tuple(prep_qubits), tuple(meas_qubits)
         self.states, self.prog, self.auto = states, prog, auto
         self.n_sets, self.shots = n_sets, shots
         self.cut_labels = cut_labels          # {"prep": [stitch numbers], "meas": [...]}
         self.params, self.param_order, self.prep_basis = params, param_order, prep_basis
+        self.basis_inputs = basis_inputs      # states = 2^p basis-input evolutions, not 4^p SIC variants
         self._dict = None
 
     @property
@@ -305,12 +309,15 @@ class FragmentData(Mapping):
 
 
 def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=None,
-                          prep_basis="SIC", monitor_jobs=False, params=None, param_order=None):
+                          prep_basis="SIC", monitor_jobs=False, params=None, param_order=None,
+                          linear_inputs=True):
     """Simulate every preparation variant of every fragment (:216-232).
 
     `tomography_backend` must be a `B200Backend` (there is no other simulator here and no CPU
     fallback).  Extensions: `params` [n_sets, n_params] + `param_order` evaluate a batch of
-    parameter vectors of unbound fragments at once."""
+    parameter vectors of unbound fragments at once; `linear_inputs` (default) simulates the 2^p
+    basis inputs instead of the 4^p SIC preparations when a fragment has at most 4 cut ends
+    (same Choi blocks by linearity; the dict view still simulates every variant)."""
     if not isinstance(tomography_backend, B200Backend):
         raise _lib.QdcError("collect_fragment_data needs a qdc_b200.engine.B200Backend as "
                             "tomography_backend; there is no CPU simulator in this package")
@@ -338,10 +345,11 @@ def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=
                            for k, (exit_, _) in enumerate(stitches) if exit_ == (idx, q)]}
         zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in prep)
         prog, auto = be.compile_instructions(n, insts, param_order, zero_mask)
-        states = be.run(prog, auto, params, prep_qubits=prep)
-        n_sets = states.shape[0] // (4 ** len(prep))
+        basis = bool(prep) and len(prep) + len(meas) <= 4 and linear_inputs
+        states = be.run(prog, auto, params, prep_qubits=prep, kets=BASIS_KETS if basis else SIC_KETS)
+        n_sets = states.shape[0] // ((2 if basis else 4) ** len(prep))
         data.append(FragmentData(be, fragment, prep, meas, states, prog, auto, n_sets, shots,
-                                 labels, params, param_order, prep_basis))
+                                 labels, params, param_order, prep_basis, basis))
     return data
 
 
@@ -419,7 +427,7 @@ def direct_fragment_model(tomography_data, discard_poor_data=False, rank_cutoff=
     if isinstance(tomography_data, FragmentData):
         d = tomography_data
         T = d.backend.pauli_tensor(d.states, d.prog, d.n_sets, len(d.prep_qubits), d.meas_qubits,
-                                   frame=SIC_FRAME)
+                                   frame=SIC_FRAME, basis_inputs=d.basis_inputs)
         return FragmentModel(T, len(d.prep_qubits), len(d.meas_qubits), d.cut_labels, d.shots)
     if not torch.cuda.is_available():
         raise _lib.QdcError("direct_fragment_model needs a CUDA device; there is no CPU fallback")

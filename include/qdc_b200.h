@@ -187,6 +187,11 @@ int  qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t f
  * (h_meas_qubits); kappa = sum_axis a_axis * h_axis_stride[axis].  h_frame[a * n_codes + s] are the
  * expansion coefficients of Pauli a in the preparation projectors.  d_state holds
  * n_codes^n_prep * n_sets states laid out as by qdc_sv_run (init_lo = 0).
+ * n_codes = 2 selects the BASIS-INPUT form: d_state holds the 2^n_prep evolutions of the
+ * computational-basis inputs (qdc_sv_run with the code table {|0>, |1>}); every preparation is a
+ * linear combination of them, so T[set][b][a] = Tr(P_a M_b), (M_b)_{x'x} = conj(psi_x'(b))
+ * psi_x(b), gives the same numbers from 2^p instead of 4^p simulations (h_frame unused;
+ * n_prep + n_meas <= 4).
  * d_T: [n_sets][2^(n_qubits - n_meas)][ld] float64, ld >= 4^(n_prep + n_meas). */
 int  qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets, uint64_t flip_mask,
                          int n_prep, int n_codes, const double* h_frame,

@@ -33,20 +33,25 @@ def ev_time(fn, reps=5, warm=2):
     return min(ts)
 
 
-def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce):
+def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce, basis=None):
+    from qdc_b200.engine import BASIS_KETS, SIC_KETS
+    if basis is None:
+        basis = bool(prep) and len(prep) + len(meas) <= 4
     dev = torch.device("cuda:0")
     be = B200Backend(device=dev, tile_bits=tile_bits, coalesce_bits=coalesce)
     n, insts, pars = dqva_fragment(n_nodes, 7)
     zero = ((1 << n) - 1) & ~sum(1 << q for q in prep)
     prog, auto = be.compile_instructions(n, insts, pars, zero)
     table = np.random.default_rng(1).uniform(0, 2 * np.pi, (n_sets, len(pars)))
-    n_init = 4 ** len(prep)
+    n_init = (2 if basis else 4) ** len(prep)
+    kets = BASIS_KETS if basis else SIC_KETS
     states = torch.empty(n_init * n_sets, 1 << n, dtype=torch.complex128, device=dev)
-    t_run = ev_time(lambda: be.run(prog, auto, table, prep_qubits=prep, out=states))
-    T = be.pauli_tensor(states, prog, n_sets, len(prep), meas)
-    t_ten = ev_time(lambda: be.pauli_tensor(states, prog, n_sets, len(prep), meas, out=T))
+    t_run = ev_time(lambda: be.run(prog, auto, table, prep_qubits=prep, kets=kets, out=states))
+    T = be.pauli_tensor(states, prog, n_sets, len(prep), meas, basis_inputs=basis)
+    t_ten = ev_time(lambda: be.pauli_tensor(states, prog, n_sets, len(prep), meas, out=T, basis_inputs=basis))
     sims = n_init * n_sets
-    ref_variants = sims * 3 ** len(meas)
+    ref_variants = 4 ** len(prep) * n_sets * 3 ** len(meas)
+    name = name + (" [basis inputs]" if basis else "")
     gbytes = prog.n_groups * 32.0 * (1 << n) * sims / 1e9
     print(f"{name}: n={n} p={len(prep)} m={len(meas)} sets={n_sets} t={prog.tile_bits} c={coalesce} "
           f"groups={prog.n_groups} ops={prog.n_ops} | run {t_run*1e3:.3f} ms ({sims/t_run:.3e} states/s, "
@@ -57,6 +62,7 @@ def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce):
 
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "one":
+        case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4, basis=False)
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4)
         case("C4 meas side", 20, [], [3, 8, 12, 17], 1, 12, 4)
         case("C2 like", 14, [2, 9], [5], 64, 12, 4)

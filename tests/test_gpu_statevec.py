@@ -111,6 +111,13 @@ def test_pauli_tensor_matches_oracle(cuda, n, prep, meas, tile_bits, seed):
     R = qo.fragment_pauli_tensor((n, insts), prep, meas)
     assert T.shape == (1 << (n - len(meas)), 4 ** (len(prep) + len(meas)))
     assert np.abs(T - R.reshape(T.shape)).max() < TOL
+    if prep and len(prep) + len(meas) <= 4:
+        # linearity: the 2^p basis-input evolutions give the same tensor as the 4^p SIC variants
+        from qdc_b200.engine import BASIS_KETS
+        basis = be.run(prog, auto, prep_qubits=prep, kets=BASIS_KETS)
+        assert basis.shape[0] == 2 ** len(prep)
+        Tb = be.pauli_tensor(basis, prog, 1, len(prep), meas, basis_inputs=True).cpu().numpy()[0]
+        assert np.abs(Tb - R.reshape(T.shape)).max() < TOL
 
 
 def test_pauli_tensor_strides_and_sets(cuda):
@@ -127,6 +134,10 @@ def test_pauli_tensor_strides_and_sets(cuda):
     for a0, a1, a2 in itertools.product(range(4), repeat=3):
         want[:, a0 * 1 + a1 * 16 + a2 * 4] = R[:, a0, a1, a2]
     assert np.abs(T[0] - want).max() < TOL and np.abs(T[1] - want).max() < TOL
+    from qdc_b200.engine import BASIS_KETS
+    basis = be.run(prog, auto, params=np.zeros((2, 0)), prep_qubits=prep, kets=BASIS_KETS)
+    Tb = be.pauli_tensor(basis, prog, 2, 1, meas, axis_strides=strides, ld=64, basis_inputs=True).cpu().numpy()
+    assert np.abs(Tb[0] - want).max() < TOL and np.abs(Tb[1] - want).max() < TOL
 
 
 def test_amplitude_scoring_matches_oracle(cuda):
