@@ -195,6 +195,18 @@ def generate_subcircuit_instances(subcircuits, complete_path_map):
 _MEAS_ANGLES = ((0.0, 0.0), (math.pi, math.pi / 2), (math.pi / 2, math.pi / 2))
 
 
+def _param_order_of(subcircuits, param_order=None):
+    if param_order is not None:
+        return list(param_order)
+    seen = []
+    for sub in subcircuits:
+        for prm in getattr(sub, "parameters", []):
+            if prm not in seen:
+                seen.append(prm)
+    from ..circuit import _param_sort_key
+    return sorted(seen, key=_param_sort_key)
+
+
 def simulate_subcircuits(backend: B200Backend, subcircuits, complete_path_map, params=None,
                          param_order=None):
     """All instances of every subcircuit on the device.
@@ -205,14 +217,7 @@ def simulate_subcircuits(backend: B200Backend, subcircuits, complete_path_map, p
     if not isinstance(backend, B200Backend):
         raise _lib.QdcError("simulate_subcircuits needs a qdc_b200.engine.B200Backend; there is "
                             "no CPU simulator in this package")
-    if param_order is None:
-        seen = []
-        for sub in subcircuits:
-            for prm in getattr(sub, "parameters", []):
-                if prm not in seen:
-                    seen.append(prm)
-        from ..circuit import _param_sort_key
-        param_order = sorted(seen, key=_param_sort_key)
+    param_order = _param_order_of(subcircuits, param_order)
     user = np.zeros((1, len(param_order))) if params is None else \
         np.atleast_2d(np.asarray(params, dtype=np.float64))
     n_user = user.shape[0]

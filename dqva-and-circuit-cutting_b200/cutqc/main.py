@@ -145,7 +145,16 @@ class CutQC:
                    backend, verbose)
 
     # ---- evaluate (main.py:72-84) -----------------------------------------------------------
-    def evaluate(self, early_termination: Sequence[int] = (0,), params=None, param_order=None):
+    def evaluate(self, early_termination: Sequence[int] = (0,), params=None, param_order=None,
+                 fused: bool = False):
+        """fused=False: the reference's stages (all 4^rho 3^O instances -> measure ->
+        vertical_collapse).  fused=True: the kron vectors straight from the amplitudes of the
+        2^rho basis-input evolutions (`qdc_sv_pauli_tensor`, basis-input form): the init
+        expansion of post_process.py:20-30 is Tr(P_a .) on the rho axes and the signed marginal of
+        measure.c is Tr(. P_a) on the O axes, so no instance is simulated or stored
+        (subcircuits with at most 4 cut ends; others fall back to the staged path)."""
+        if fused:
+            return self._evaluate_fused(early_termination, params, param_order)
         sims = simulate_subcircuits(self.backend, self.subcircuits, self.complete_path_map,
                                     params, param_order)
         self.measured = []
@@ -163,6 +172,43 @@ class CutQC:
                 vecs, flags = kernels.vertical_collapse(measured, self.terms.kron_terms[s])
                 self.kron[et].append(vecs)
                 self.kron_present[et].append(flags.bool() if et == 1 else torch.ones_like(flags).bool())
+        return self
+
+    def _evaluate_fused(self, early_termination, params, param_order):
+        from ..engine import BASIS_KETS
+        from .evaluator import _param_order_of
+        order = _param_order_of(self.subcircuits, param_order)
+        table = None if params is None else np.atleast_2d(np.asarray(params, dtype=np.float64))
+        if table is not None and table.shape[0] != 1:
+            raise _lib.QdcError("CutQC.evaluate takes one parameter vector at a time")
+        kron = []
+        staged = None
+        for s, sub in enumerate(self.subcircuits):
+            tab, mine = self.terms.tables[s], self.terms.pairs_of[s]
+            if len(tab.rho) + len(tab.O) > 4:
+                if staged is None:                       # rare: wide cut, use the reference's stages
+                    staged = CutQC({"circuit": self.circuit, "subcircuits": self.subcircuits,
+                                    "complete_path_map": self.complete_path_map}, self.backend)
+                    staged.evaluate((0,), params, param_order)
+                kron.append(staged.kron[0][s])
+                continue
+            rank = {k: len(mine) - 1 - i for i, k in enumerate(mine)}        # base-4 digit of pair k
+            rho_pair = [k for k in mine if self.terms.pairs[k][1]["subcircuit_idx"] == s]
+            O_pair = [k for k in mine if self.terms.pairs[k][0]["subcircuit_idx"] == s]
+            strides = [4 ** rank[k] for k in rho_pair + O_pair]
+            zero_mask = ((1 << tab.d) - 1) & ~sum(1 << q for q in tab.rho)
+            prog, auto = self.backend.compile_instructions(tab.d, list(sub.to_instructions()), order, zero_mask)
+            states = self.backend.run(prog, auto, table, prep_qubits=tab.rho, kets=BASIS_KETS)
+            T = self.backend.pauli_tensor(states, prog, 1, len(tab.rho), tab.O,
+                                          axis_strides=strides if mine else None,
+                                          basis_inputs=bool(tab.rho))
+            kron.append(T[0].t().contiguous())                               # [kron index][2^effective]
+        self.measured = []
+        for et in early_termination:
+            self.kron[et] = kron
+            self.kron_present[et] = [(v.abs().amax(dim=1) > 1e-16) if et == 1
+                                     else torch.ones(v.shape[0], dtype=torch.bool, device=v.device)
+                                     for v in kron]
         return self
 
     # ---- post_process (main.py:86-139, 391-457) ---------------------------------------------

@@ -87,3 +87,24 @@ def test_float32_output_and_fused_mis_score(cuda):
     layer32, = job.post_process(out_dtype=torch.float32)
     assert layer32.prob.dtype == torch.float32
     assert np.abs(layer32.dense().cpu().numpy() - full).max() < 2e-6
+
+
+@pytest.mark.parametrize("name", list(cc.CASES))
+def test_fused_evaluate_matches_oracle_kron_vectors(cuda, name):
+    """fused=True: kron vectors straight from the basis-input amplitudes == vertical_collapse of
+    the measured instances (oracle), and the reconstruction == uncut."""
+    from qdc_b200.cutqc.main import CutQC
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    _, kron_o, _, _, _ = co.evaluate(frags, cpm, early_termination=0)
+    job = CutQC.from_fragments(circ, frags, wpm, _be(cuda)).evaluate(early_termination=(0, 1), fused=True)
+    for s in range(len(frags)):
+        kron = job.kron[0][s].cpu().numpy()
+        assert kron.shape[0] == len(kron_o[s])
+        for k, want in kron_o[s].items():
+            assert np.abs(kron[k] - want).max() < TOL
+    n = circ.num_qubits
+    full = sv.probabilities(sv.simulate(n, circ.to_instructions()))
+    for et in (0, 1):
+        layer, = job.post_process(early_termination=et)
+        assert np.abs(layer.dense().cpu().numpy() - full).max() < TOL
