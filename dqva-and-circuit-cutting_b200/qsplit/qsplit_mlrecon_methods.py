@@ -538,13 +538,15 @@ def _row_operand(models, sorted_T, sorted_labels, col_labels, s):
 
 
 def recombine_fragment_models(frag_models, wire_path_map, method="network", backend=None,
-                              graph=None, threshold=1e-5, topk=1, store=None):
+                              graph=None, threshold=1e-5, topk=1, store=None, compact="auto"):
     """Full-circuit distribution from fragment models (:463-472): sum over the 4^K cut-basis
     index of the product of fragment tensors, bits permuted to circuit order, normalised.
 
     Returns one `DeviceDistribution` (a list of them for a batch of parameter sets).
     Extensions: `graph` (or `backend.graph`) fuses the MIS objective and top-k into the
-    contraction; `store=False` never materialises the 2^N array (required beyond ~2^31 outputs)."""
+    contraction; `store=False` never materialises the 2^N array (required beyond ~2^31 outputs);
+    `compact` ("auto": from 2^24 outputs on) restricts the contraction to the fragment outcomes
+    that occur at all (all-zero tensor rows are dropped, exactly; see recombine.compact_operands)."""
     if method not in ("network", "insertion"):
         raise ValueError("recombination method {method} not recognized")     # :469 (sic)
     if not all(isinstance(m, FragmentModel) and m.cut_labels is not None for m in frag_models):
@@ -580,7 +582,10 @@ def recombine_fragment_models(frag_models, wire_path_map, method="network", back
         else:
             A = _row_operand(frag_models, sorted_T, sorted_labels, col_labels, s)
         A, Bt = _rc.pad_kdim(A), _rc.pad_kdim(Bt)
-        res = _rc.contract_and_score(A, Bt, tables, scale=0.5 ** K, threshold=threshold, k=topk,
+        tabs = tables
+        if compact is True or (compact == "auto" and N >= 24):
+            A, Bt, tabs, _ = _rc.compact_operands(A, Bt, tables)
+        res = _rc.contract_and_score(A, Bt, tabs, scale=0.5 ** K, threshold=threshold, k=topk,
                                      store="circuit" if store else None)
         results.append(DeviceDistribution(n_wires, res.P, res, res.norm))
     return results[0] if n_sets == 1 else results

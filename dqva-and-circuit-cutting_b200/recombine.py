@@ -18,6 +18,7 @@ import torch
 from . import _lib
 
 __all__ = ["MisTables", "ScoreResult", "build_tables", "contract_and_score", "reduce_and_score",
+           "compact_operands",
            "pad_kdim"]
 
 
@@ -155,7 +156,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
         and Bt.is_contiguous()
     M, kdim = A.shape
     N = Bt.shape[0]
-    assert Bt.shape[1] == kdim and M == 1 << tables.row_bits and N == 1 << tables.col_bits
+    assert Bt.shape[1] == kdim and M == tables.row_x.numel() and N == tables.col_x.numel()
+    assert store != "united" or (M == 1 << tables.row_bits and N == 1 << tables.col_bits)
     if n_rows is None:
         n_rows = M - row_lo
     if cand_cap is None:
@@ -173,7 +175,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
         if store_mode == 1:
             out = torch.empty(n_rows, N, dtype=out_dtype, device=dev)
         else:
-            out = torch.zeros(M * N, dtype=out_dtype, device=dev)
+            out = torch.zeros(1 << (tables.row_bits + tables.col_bits), dtype=out_dtype, device=dev)
     sp = _lib.stream_ptr(stream)
     with torch.cuda.device(dev):
         if normalize:
@@ -197,6 +199,32 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             kernel_events.append((ev0, ev1))
         _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
     return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
+
+
+def compact_operands(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables):
+    """Drop the rows of A and of Bt that are identically zero, together with their table entries.
+
+    A fragment outcome that never occurs has an all-zero tensor row (for the DQVA ansatz: every
+    assignment of the fragment's nodes that is not an independent set of its subgraph), and every
+    output that involves it has probability exactly 0, so the contraction only has to visit the
+    product of the two supports.  Exact: nothing is thresholded.  Returns (A', Bt', tables',
+    kept_fraction); costs one host synchronisation (the support sizes)."""
+    rows = torch.nonzero(A.abs().amax(dim=1) > 0).reshape(-1)
+    cols = torch.nonzero(Bt.abs().amax(dim=1) > 0).reshape(-1)
+    M, N = A.shape[0], Bt.shape[0]
+    frac = (rows.numel() * cols.numel()) / float(M * N)
+    if rows.numel() == 0 or cols.numel() == 0:
+        rows, cols = rows.new_zeros(1), cols.new_zeros(1)          # keep one (zero) row: sums stay 0
+    if cols.numel() > 1 and cols.numel() % 2 == 1:
+        # the kernel's epilogue walks columns in pairs: keep one of the all-zero columns as well
+        spare = torch.ones(N, dtype=torch.bool, device=cols.device)
+        spare[cols] = False
+        cols = torch.sort(torch.cat([cols, torch.nonzero(spare).reshape(-1)[:1]])).values
+    tabs = MisTables(tables.row_bits, tables.col_bits, tables.row_x[rows].contiguous(),
+                     tables.row_forb[rows].contiguous(), tables.row_wok[rows].contiguous(),
+                     tables.col_x[cols].contiguous(), tables.col_wok[cols].contiguous(),
+                     tables.bitpos, tables.node_mask)
+    return A[rows].contiguous(), Bt[cols].contiguous(), tabs, frac
 
 
 def _packed(lib, X: torch.Tensor, sp, cache: Optional[dict]) -> torch.Tensor:

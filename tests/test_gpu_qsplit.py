@@ -140,3 +140,25 @@ def test_parameter_batch(cuda):
         bound = circ.bind_parameters(dict(zip(used, row)))
         full = sv.probabilities(sv.simulate(N, bound.to_instructions()))
         assert np.abs(dist.P.cpu().numpy() - full).max() < TOL
+
+
+def test_support_compaction_is_exact(cuda):
+    """recombine(..., compact=True) drops the all-zero tensor rows (fragment outcomes that never
+    occur): same distribution, same fused scores and top-k as the full contraction."""
+    from qdc_b200 import recombine as rc
+    from qdc_b200.qsplit import qsplit_mlrecon_methods as qmm
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4), (5, 6), (6, 7), (7, 4)])
+    _, _, frags, wpm = _cut_dqva(G, [[0, 1, 2, 3], [4, 5, 6, 7]], 2, 3, True)
+    be = _be(cuda)
+    models = qmm.direct_fragment_model(qmm.collect_fragment_data(frags, wpm, 1, be))
+    full = qmm.recombine_fragment_models(models, wpm, graph=G, topk=3, store=True, compact=False)
+    comp = qmm.recombine_fragment_models(models, wpm, graph=G, topk=3, store=True, compact=True)
+    assert torch.equal(full.P, comp.P)
+    a, b = full.score.get(), comp.score.get()
+    assert a["top"] == b["top"]
+    for key in ("sum_p", "sum_pw", "sum_pw_indset"):
+        assert abs(a[key] - b[key]) < 1e-13
+    # the support really is a strict subset here (non-independent sets of a fragment have amplitude 0)
+    T = models[0].T[0]
+    assert int((T.abs().amax(dim=1) > 0).sum()) < T.shape[0]
