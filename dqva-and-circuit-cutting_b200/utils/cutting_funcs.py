@@ -64,7 +64,7 @@ def simple_choose_nodes(graph: nx.Graph, partition: List[List[int]],
 
 def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely",
                      verbose=0, params=None, param_order=None, threshold=1e-5, topk=1,
-                     store=None):
+                     store=None, compact="auto"):
     """Simulate a fragmented circuit and recombine (utils/cutting_funcs.py:167-205).
 
     Returns the recombined distribution as a Mapping `{bitstring: probability}` that keeps the
@@ -72,7 +72,8 @@ def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely
     `backend` must be a `qdc_b200.engine.B200Backend`; `frag_shots` only scales the dict views
     (the engine evaluates the infinite-shot limit).  Extensions: `params`
     [n_sets, n_params] + `param_order` evaluate a batch of parameter vectors of unbound fragments
-    in one pass and return a list of distributions."""
+    in one pass and return a list of distributions; `compact` as in
+    `recombine_fragment_models` (contract only over fragment outcomes that occur)."""
     from ..qsplit import qsplit_mlrecon_methods as qmm
 
     t0 = time.time()
@@ -90,7 +91,8 @@ def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely
 
     t1 = time.time()
     recombined_dist = qmm.recombine_fragment_models(models, wire_path_map, backend=backend,
-                                                    threshold=threshold, topk=topk, store=store)
+                                                    threshold=threshold, topk=topk, store=store,
+                                                    compact=compact)
     recombine_time = time.time() - t1
     if verbose:
         print(f"\tModel time: {model_time:.3f}, Recombine time: {recombine_time:.3f}")
