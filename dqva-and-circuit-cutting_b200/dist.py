@@ -14,7 +14,8 @@ from typing import List, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-__all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "merge_topk"]
+__all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "merge_topk",
+           "sharded_over_parameter_sets"]
 
 
 def init_from_env(backend: str | None = None) -> Tuple[int, int, int]:
@@ -82,3 +83,32 @@ def finish(sums: torch.Tensor, top_x: torch.Tensor, top_p: torch.Tensor, k: int)
         xs = host[r, 3 + k:3 + 2 * k].tolist()
         cands += [(int(x), p) for x, p in zip(xs, ps) if x >= 0]
     return total, merge_topk(cands, k)
+
+
+def sharded_over_parameter_sets(fn, table, device=None):
+    """Evaluate `fn(rows) -> float array[len(rows)]` for every row of the parameter table with
+    the rows dealt round-robin over the ranks (parameter sets are independent: SURVEY.md 8e, the
+    C2 batch and the C5 sweep), then all-gather the scalars so that every rank returns the full
+    vector in table order.  The only exchange is `ceil(n_sets / world_size)` doubles per rank."""
+    import numpy as np
+    table = np.atleast_2d(np.asarray(table, dtype=np.float64))
+    n_sets = table.shape[0]
+    rank, ws = world()
+    if ws == 1:
+        return np.asarray(fn(table), dtype=np.float64)
+    mine = round_robin(n_sets, rank, ws)
+    local = np.asarray(fn(table[mine]), dtype=np.float64) if mine else np.zeros(0)
+    per = (n_sets + ws - 1) // ws
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device()) \
+            if dist.get_backend() == "nccl" else torch.device("cpu")
+    buf = torch.zeros(per, dtype=torch.float64, device=device)
+    buf[:len(mine)] = torch.as_tensor(local, dtype=torch.float64)
+    gathered = torch.empty(ws * per, dtype=torch.float64, device=device)
+    dist.all_gather_into_tensor(gathered, buf)
+    g = gathered.view(ws, per).cpu().numpy()
+    out = np.empty(n_sets)
+    for r in range(ws):
+        idx = round_robin(n_sets, r, ws)
+        out[idx] = g[r, :len(idx)]
+    return out

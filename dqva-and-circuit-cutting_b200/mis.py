@@ -33,21 +33,38 @@ def _adjacency(graph, n_wires):
 
 
 def cut_cost(fragments, wire_path_map, frag_shots, backend: B200Backend, graph=None,
-             params=None, param_order=None, mode="likely") -> np.ndarray:
-    """-avg_cost for every parameter vector (a length-1 array for bound fragments)."""
+             params=None, param_order=None, mode="likely", shard: bool = False) -> np.ndarray:
+    """-avg_cost for every parameter vector (a length-1 array for bound fragments).
+    shard=True under torchrun: the parameter sets are dealt over the ranks and the costs
+    all-gathered (`dist.sharded_over_parameter_sets`); every rank returns the full vector."""
     if graph is not None:
         backend.graph = graph
-    dists = sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode=mode,
-                             params=params, param_order=param_order)
-    if not isinstance(dists, list):
-        dists = [dists]
-    return np.array([-d.score.get()["sum_pw_indset"] for d in dists])
+
+    def local(rows):
+        dists = sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode=mode,
+                                 params=rows, param_order=param_order, store=False)
+        if not isinstance(dists, list):
+            dists = [dists]
+        return np.array([-d.score.get()["sum_pw_indset"] for d in dists])
+
+    if shard and params is not None:
+        from . import dist as _dist
+        return _dist.sharded_over_parameter_sets(local, params)
+    return local(params)
 
 
 def uncut_cost(circuit, backend: B200Backend, graph, params=None, param_order=None,
-               masked: bool = False, max_states: Optional[int] = None) -> np.ndarray:
+               masked: bool = False, max_states: Optional[int] = None,
+               shard: bool = False) -> np.ndarray:
     """-sum_x p(x) |x| of the uncut circuit for every parameter vector (masked=True adds the
-    independent-set indicator).  Wires beyond graph.number_of_nodes() are ancillas."""
+    independent-set indicator).  Wires beyond graph.number_of_nodes() are ancillas.
+    shard=True under torchrun: parameter sets dealt over the ranks ("replicas only": a state
+    fits one GPU), costs all-gathered."""
+    if shard and params is not None:
+        from . import dist as _dist
+        return _dist.sharded_over_parameter_sets(
+            lambda rows: uncut_cost(circuit, backend, graph, rows, param_order, masked, max_states),
+            params)
     if param_order is None:
         param_order = list(circuit.parameters)
     prog, auto = backend.compile(circuit, param_order=param_order)

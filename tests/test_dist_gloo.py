@@ -53,3 +53,34 @@ def test_sharding_helpers():
     items = sorted(i for r in range(3) for i in qdist.round_robin(10, r, 3))
     assert items == list(range(10))
     assert qdist.merge_topk([(5, 0.2), (3, 0.2), (9, 0.7)], 2) == [(9, 0.7), (3, 0.2)]
+
+
+def _worker_sets(rank, ws, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
+    import importlib, sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import dist as qd
+    qd.init_from_env(backend="gloo")
+    table = np.arange(7 * 3, dtype=float).reshape(7, 3)
+    seen = []
+
+    def fn(rows):
+        seen.append(len(rows))
+        return rows.sum(axis=1) * 2.0
+    res = qd.sharded_over_parameter_sets(fn, table)
+    out[rank] = (res.tolist(), seen)
+    dist.destroy_process_group()
+
+
+def test_parameter_sets_sharded_world_size_2():
+    """7 parameter sets over 2 ranks: 4 + 3 evaluated locally, every rank ends with all 7."""
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_sets, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    want = [2.0 * sum(range(3 * i, 3 * i + 3)) for i in range(7)]
+    assert out[0][0] == want and out[1][0] == want
+    assert out[0][1] == [4] and out[1][1] == [3]
