@@ -310,14 +310,16 @@ class FragmentData(Mapping):
 
 def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=None,
                           prep_basis="SIC", monitor_jobs=False, params=None, param_order=None,
-                          linear_inputs=True):
+                          linear_inputs=True, sample=False, seed=None):
     """Simulate every preparation variant of every fragment (:216-232).
 
     `tomography_backend` must be a `B200Backend` (there is no other simulator here and no CPU
     fallback).  Extensions: `params` [n_sets, n_params] + `param_order` evaluate a batch of
     parameter vectors of unbound fragments at once; `linear_inputs` (default) simulates the 2^p
     basis inputs instead of the 4^p SIC preparations when a fragment has at most 4 cut ends
-    (same Choi blocks by linearity; the dict view still simulates every variant)."""
+    (same Choi blocks by linearity; the dict view still simulates every variant); `sample=True`
+    draws `shots` outcomes per variant circuit on the device instead of taking the infinite-shot
+    limit (one parameter vector), `seed` makes the draws reproducible."""
     if not isinstance(tomography_backend, B200Backend):
         raise _lib.QdcError("collect_fragment_data needs a qdc_b200.engine.B200Backend as "
                             "tomography_backend; there is no CPU simulator in this package")
@@ -345,6 +347,13 @@ def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=
                            for k, (exit_, _) in enumerate(stitches) if exit_ == (idx, q)]}
         zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in prep)
         prog, auto = be.compile_instructions(n, insts, param_order, zero_mask)
+        if sample:
+            if params is not None and np.atleast_2d(np.asarray(params)).shape[0] != 1:
+                raise _lib.QdcError("sample=True evaluates one parameter vector at a time")
+            data.append(SampledFragmentData(be, fragment, prep, meas, None, prog, auto, 1, shots,
+                                            labels, params, param_order, prep_basis,
+                                            seed=None if seed is None else seed + idx))
+            continue
         basis = bool(prep) and len(prep) + len(meas) <= 4 and linear_inputs
         states = be.run(prog, auto, params, prep_qubits=prep, kets=BASIS_KETS if basis else SIC_KETS)
         n_sets = states.shape[0] // ((2 if basis else 4) ** len(prep))
@@ -397,20 +406,36 @@ class FragmentModel(Mapping):
         return len(self._materialise())
 
 
+_FIT_CACHE: Dict = {}
+
+
+def _fit_matrix(n_prep, n_meas, rank_cutoff=1e-8, prep_basis="SIC"):
+    """(labels, W): `scipy.linalg.lstsq(state_matrix.conj(), counts, cond)` (:301-312) has the same
+    design matrix for every bitstring (labels zero-filled to the full set, :204-211), so the fit
+    is counts @ W^T with W = pinv(design) folded with the trace row."""
+    key = (n_prep, n_meas, rank_cutoff, prep_basis)
+    if key not in _FIT_CACHE:
+        prep_labels = list(itertools.product(prep_state_keys[prep_basis], repeat=n_prep))
+        meas_states = list(itertools.product(meas_state_keys["Pauli"], repeat=n_meas))
+        labels = list(itertools.product(prep_labels, meas_states))
+        q = n_prep + n_meas
+        design = np.array([target_labels_to_matrix(lab).flatten() for lab in labels]
+                          + [np.eye(2 ** q).flatten()]).conj()
+        pinv = np.linalg.pinv(design, rcond=rank_cutoff)             # [4^q, n_labels + 1]
+        # trace row = sum(counts) / (2^p 3^m)  (:306-309)
+        W = pinv[:, :-1] + pinv[:, -1:] / (2 ** n_prep * 3 ** n_meas)
+        _FIT_CACHE[key] = (labels, W)
+    return _FIT_CACHE[key]
+
+
 def _model_from_counts(data: Mapping, device, rank_cutoff) -> FragmentModel:
-    """Reference-layout counts dict -> model.  `scipy.linalg.lstsq(state_matrix.conj(), counts,
-    cond)` (:301-312) has the same design matrix for every bitstring (labels zero-filled to the
-    full set, :204-211), so the fit is counts @ W^T with W = pinv(design) folded with the trace
-    row: one GEMM on the device for all bitstrings."""
+    """Reference-layout counts dict -> model: one GEMM on the device for all bitstrings."""
     keys = list(data.keys())
-    labels = list(next(iter(data.values())).keys())
-    n_prep, n_meas = len(labels[0][0]), len(labels[0][1])
+    first = list(next(iter(data.values())).keys())
+    n_prep, n_meas = len(first[0][0]), len(first[0][1])
     q = n_prep + n_meas
-    design = np.array([target_labels_to_matrix(lab).flatten() for lab in labels]
-                      + [np.eye(2 ** q).flatten()]).conj()
-    pinv = np.linalg.pinv(design, rcond=rank_cutoff)                 # [4^q, n_labels + 1]
-    W = pinv[:, :-1] + pinv[:, -1:] / (2 ** n_prep * 3 ** n_meas)    # trace row = sum(counts)/(2^p 3^m)
-    counts = np.array([[data[k][lab] for lab in labels] for k in keys], dtype=float)
+    labels, W = _fit_matrix(n_prep, n_meas, rank_cutoff)
+    counts = np.array([[data[k].get(lab, 0) for lab in labels] for k in keys], dtype=float)
     width = len(keys[0])
     C_d = torch.zeros(1 << width, len(labels), dtype=torch.complex128, device=device)
     idx = torch.as_tensor([int(k, 2) if width else 0 for k in keys], device=device)
@@ -420,10 +445,82 @@ def _model_from_counts(data: Mapping, device, rank_cutoff) -> FragmentModel:
     return FragmentModel(T.unsqueeze(0), n_prep, n_meas, None)
 
 
+class SampledFragmentData(FragmentData):
+    """Finite-shot tomography data: every one of the 4^p 3^m variant circuits is simulated and
+    `shots` outcomes are drawn from its distribution on the device (what the reference's
+    qasm_simulator run produces, qsplit_mlrecon_methods.py:20-42, 216-232).  `counts` is the
+    organised table [final bits b][label] (:169-213) as a device tensor; the Mapping view is the
+    reference's dict."""
+
+    def __init__(self, *args, seed=None, **kwargs):
+        super().__init__(*args, **kwargs)
+        n, m = self.n_qubits, len(self.meas_qubits)
+        p = len(self.prep_qubits)
+        dev = self.backend.device
+        gen = torch.Generator(device=dev)
+        if seed is not None:
+            gen.manual_seed(int(seed))
+        labels, _ = _fit_matrix(p, m)
+        col = {lab: i for i, lab in enumerate(labels)}
+        prep_labels = list(itertools.product(prep_state_keys["SIC"], repeat=p))
+        x = torch.arange(1 << n, device=dev)
+        keep = [q for q in range(n) if q not in self.meas_qubits]
+        b = torch.zeros_like(x)
+        for j, q in enumerate(keep):
+            b |= ((x >> q) & 1) << j
+        mid = torch.zeros_like(x)
+        for j, q in enumerate(self.meas_qubits):
+            mid |= ((x >> q) & 1) << j
+        counts = torch.zeros(1 << (n - m), len(labels), dtype=torch.float64, device=dev)
+        for (prep_label, meas_label), probs in self._variant_probabilities_device().items():
+            draws = torch.multinomial(probs.clamp_min(0), int(self.shots), replacement=True, generator=gen)
+            hist = torch.bincount(draws, minlength=1 << n).to(torch.float64)
+            # column of (prep_label, outcome state) for every value of the measured bits
+            cols = torch.empty(1 << m, dtype=torch.long, device=dev)
+            for mv in range(1 << m):
+                state = tuple(basis + ("p" if not (mv >> j) & 1 else "m") for j, basis in enumerate(meas_label))
+                cols[mv] = col[(prep_label, state)]
+            counts.index_put_((b, cols[mid]), hist, accumulate=True)
+        self.counts = counts
+        self.labels = labels
+
+    def _variant_probabilities_device(self):
+        n, insts = _frag_insts(self.fragment)
+        p, m = len(self.prep_qubits), len(self.meas_qubits)
+        prep_labels = list(itertools.product(prep_state_keys["SIC"], repeat=p))
+        zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in self.prep_qubits)
+        out = {}
+        for meas_label in itertools.product(["Z", "X", "Y"], repeat=m):
+            suffix = [(g, (q,), (), None) for q, lab in zip(self.meas_qubits, meas_label)
+                      for g in _MEAS_SUFFIX[lab]]
+            prog, auto = self.backend.compile_instructions(n, insts + suffix, self.param_order, zero_mask)
+            states = self.backend.run(prog, auto, self.params, prep_qubits=self.prep_qubits)
+            probs = self.backend.probabilities(states, prog).reshape(len(prep_labels), -1, 1 << n)[:, 0]
+            for i, prep_label in enumerate(prep_labels):
+                out[(prep_label, meas_label)] = probs[i]
+        return out
+
+    def _materialise(self):
+        if self._dict is None:
+            n, m = self.n_qubits, len(self.meas_qubits)
+            host = self.counts.cpu().numpy()
+            seen = np.nonzero(host.sum(axis=1) > 0)[0]
+            self._dict = {_bits(int(b), n - m): {lab: float(host[b, i]) for i, lab in enumerate(self.labels)}
+                          for b in seen}
+        return self._dict
+
+
 def direct_fragment_model(tomography_data, discard_poor_data=False, rank_cutoff=1e-8):
     """Choi blocks by linear inversion (:273-317)."""
     if type(tomography_data) is list:
         return [direct_fragment_model(d, discard_poor_data, rank_cutoff) for d in tomography_data]
+    if isinstance(tomography_data, SampledFragmentData):
+        d = tomography_data
+        p, m = len(d.prep_qubits), len(d.meas_qubits)
+        _, W = _fit_matrix(p, m, rank_cutoff)
+        blocks = (d.counts.to(torch.complex128) @ torch.as_tensor(W, device=d.counts.device).T)
+        T = _tensor_from_choi(blocks.reshape(-1, 2 ** (p + m), 2 ** (p + m)), p, m) / d.shots
+        return FragmentModel(T.unsqueeze(0), p, m, d.cut_labels, d.shots)
     if isinstance(tomography_data, FragmentData):
         d = tomography_data
         T = d.backend.pauli_tensor(d.states, d.prog, d.n_sets, len(d.prep_qubits), d.meas_qubits,

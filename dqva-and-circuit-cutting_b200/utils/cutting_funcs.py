@@ -64,7 +64,7 @@ def simple_choose_nodes(graph: nx.Graph, partition: List[List[int]],
 
 def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely",
                      verbose=0, params=None, param_order=None, threshold=1e-5, topk=1,
-                     store=None, compact="auto"):
+                     store=None, compact="auto", sample=False, seed=None):
     """Simulate a fragmented circuit and recombine (utils/cutting_funcs.py:167-205).
 
     Returns the recombined distribution as a Mapping `{bitstring: probability}` that keeps the
@@ -73,13 +73,15 @@ def sim_with_cutting(fragments, wire_path_map, frag_shots, backend, mode="likely
     (the engine evaluates the infinite-shot limit).  Extensions: `params`
     [n_sets, n_params] + `param_order` evaluate a batch of parameter vectors of unbound fragments
     in one pass and return a list of distributions; `compact` as in
-    `recombine_fragment_models` (contract only over fragment outcomes that occur)."""
+    `recombine_fragment_models` (contract only over fragment outcomes that occur);
+    `sample=True` draws `frag_shots` outcomes per variant circuit on the device (the reference's
+    finite-shot behaviour) instead of the exact limit."""
     from ..qsplit import qsplit_mlrecon_methods as qmm
 
     t0 = time.time()
     frag_data = qmm.collect_fragment_data(fragments, wire_path_map, shots=frag_shots,
                                           tomography_backend=backend, params=params,
-                                          param_order=param_order)
+                                          param_order=param_order, sample=sample, seed=seed)
     direct_models = qmm.direct_fragment_model(frag_data)
     if mode == "direct":
         models = direct_models

@@ -162,3 +162,31 @@ def test_support_compaction_is_exact(cuda):
     # the support really is a strict subset here (non-independent sets of a fragment have amplitude 0)
     T = models[0].T[0]
     assert int((T.abs().amax(dim=1) > 0).sum()) < T.shape[0]
+
+
+def test_finite_shot_mode_converges_to_exact(cuda):
+    """sample=True: counts drawn per variant circuit, least-squares model from the
+    counts table, ML projection, recombination.  Statistical test: the error shrinks like
+    1/sqrt(shots), the draws are reproducible, the dict view has the reference's layout."""
+    from qdc_b200.qsplit import qsplit_mlrecon_methods as qmm
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = nx.Graph()
+    G.add_edges_from([(0, 1), (1, 2), (2, 0), (2, 3), (3, 4), (4, 5), (5, 3), (1, 4)])
+    circ, _, frags, wpm = _cut_dqva(G, [[0, 1, 2], [3, 4, 5]], 2, 5, True)
+    be = _be(cuda)
+    exact = sim_with_cutting(frags, wpm, 1, be, mode="direct", store=True).P.cpu().numpy()
+    errs = []
+    for shots in (2000, 200000):
+        a = sim_with_cutting(frags, wpm, shots, be, mode="likely", store=True, sample=True, seed=7)
+        b = sim_with_cutting(frags, wpm, shots, be, mode="likely", store=True, sample=True, seed=7)
+        assert torch.equal(a.P, b.P)
+        got = a.P.cpu().numpy()
+        assert abs(got.sum() - 1) < 1e-9
+        errs.append(np.abs(got - exact).max())
+    assert errs[1] < 0.01 and errs[1] < errs[0]
+    data = qmm.collect_fragment_data(frags, wpm, shots=500, tomography_backend=be, sample=True, seed=1)
+    for d in data:
+        p, m = len(d.prep_qubits), len(d.meas_qubits)
+        assert abs(float(d.counts.sum()) - 500 * 4 ** p * 3 ** m) < 1e-6      # every draw lands in one cell
+        row = next(iter(d.values()))
+        assert len(row) == 4 ** p * 6 ** m
