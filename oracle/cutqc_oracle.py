@@ -384,3 +384,62 @@ def post_process(full_qubits, subcircuits, complete_path_map, counter, kron, sum
     return [(layers[l], outputs[l]["reconstructed_prob"],
              reorder(full_qubits, outputs[l]["reconstructed_prob"], complete_path_map, subcircuits, layers[l]))
             for l in range(len(layers))]
+
+
+# ---------------------------------------------------------------------------------------------
+# the CKT numpy twin (circuit-knitting-toolbox/.../wire_cutting*.py), float64
+# ---------------------------------------------------------------------------------------------
+def ckt_attribute_shots(subcircuit_entries, subcircuit_instance_probs):        # wire_cutting.py:252-310
+    out = {}
+    for s in subcircuit_entries:
+        out[s] = {}
+        for label in subcircuit_entries[s]:
+            entry_idx, kronecker_term = subcircuit_entries[s][label]
+            prob = None
+            for coefficient, inst in kronecker_term:
+                term = coefficient * subcircuit_instance_probs[s][inst]
+                prob = term if prob is None else prob + term
+            out[s][entry_idx] = prob
+    return out
+
+
+def ckt_build(summation_terms, subcircuit_entry_probs, num_cuts):   # wire_cutting_post_processing.py:340-443
+    smart_order = sorted(subcircuit_entry_probs.keys(), key=lambda s: len(subcircuit_entry_probs[s][0]))
+    overhead = {"additions": 0, "multiplications": 0}
+    total = None
+    for term in summation_terms:
+        vec = None
+        for s in smart_order:
+            entry = subcircuit_entry_probs[s][term[s]]
+            if vec is None:
+                vec = entry
+            else:
+                vec = np.kron(vec, entry)
+                overhead["multiplications"] += len(vec)
+        if total is None:
+            total = vec.copy()
+        else:
+            total += vec
+            overhead["additions"] += len(total)
+    return total / 2 ** num_cuts, smart_order, overhead
+
+
+def ckt_generate_reconstructed_output(full_qubits, subcircuits, unordered, smart_order,
+                                      complete_path_map):          # wire_cutting_verification.py:80-136
+    out_qubits = {s: [] for s in smart_order}
+    for input_qubit in complete_path_map:
+        last = complete_path_map[input_qubit][-1]
+        out_qubits[last["subcircuit_idx"]].append((last["subcircuit_qubit"], full_qubits.index(input_qubit)))
+    for s in out_qubits:
+        ordered = sorted(out_qubits[s], key=lambda x: subcircuits[s].qubits.index(x[0]), reverse=True)
+        out_qubits[s] = [x[1] for x in ordered]
+    unordered_qubit = []
+    for s in smart_order:
+        unordered_qubit += out_qubits[s]
+    n = len(full_qubits)
+    out = np.zeros(len(unordered))
+    for state, p in enumerate(unordered):
+        bits = bin(state)[2:].zfill(n)
+        _, ordered = zip(*sorted(zip(unordered_qubit, bits), reverse=True))
+        out[int("".join(ordered), 2)] = p
+    return out

@@ -108,3 +108,30 @@ def test_fused_evaluate_matches_oracle_kron_vectors(cuda, name):
     for et in (0, 1):
         layer, = job.post_process(early_termination=et)
         assert np.abs(layer.dense().cpu().numpy() - full).max() < TOL
+
+
+@pytest.mark.parametrize("name", ["chain3", "dqva6_fused"])
+def test_ckt_wrappers_match_numpy_twin(cuda, name):
+    """S5: CKT-named `_attribute_shots`, `build`, `generate_reconstructed_output` on the device ==
+    the numpy twin (oracle) and the uncut distribution, from the same instance probabilities."""
+    from qdc_b200.cutqc import ckt
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    counter, _, terms, K, inter = co.evaluate(frags, cpm)
+    entries = {s: {("label", k): (k, list(term)) for term, k in inter["kronecker_terms"][s].items()}
+               for s in range(len(frags))}
+    inst = {s: {i: v for i, v in inter["measured"][s].items()} for s in range(len(frags))}
+    want_entries = co.ckt_attribute_shots(entries, inst)
+    got_entries = ckt._attribute_shots(entries, inst)
+    for s in want_entries:
+        for k, v in want_entries[s].items():
+            assert np.abs(got_entries[s][k].cpu().numpy() - v).max() < TOL
+    want, order_w, over_w = co.ckt_build(terms, want_entries, K)
+    got, order_g, over_g = ckt.build(terms, got_entries, K, num_threads=4)
+    assert order_g == order_w and over_g == over_w
+    assert np.abs(got.cpu().numpy() - want).max() < TOL
+    n = circ.num_qubits
+    full = sv.probabilities(sv.simulate(n, circ.to_instructions()))
+    ordered = ckt.generate_reconstructed_output(circ, frags, got, order_g, cpm).cpu().numpy()
+    assert np.abs(ordered - co.ckt_generate_reconstructed_output(list(circ.qubits), frags, want, order_w, cpm)).max() < TOL
+    assert np.abs(ordered - full).max() < TOL
