@@ -27,13 +27,22 @@
 
 namespace {
 
-constexpr int TM = 128, TN = 128, BK = 16, STAGES = 6;
-constexpr int CONSUMER_WARPS = 16, THREADS = CONSUMER_WARPS * 32;
+#ifndef QDC_TN
+#define QDC_TN 128
+#endif
+#ifndef QDC_STAGES
+#define QDC_STAGES (QDC_TN == 128 ? 6 : 4)
+#endif
+constexpr int TM = 128, TN = QDC_TN, BK = 16, STAGES = QDC_STAGES;
+constexpr int WARPS_N = TN / 32;                             // warp tile is 32 x 32
+constexpr int CONSUMER_WARPS = 4 * WARPS_N, THREADS = CONSUMER_WARPS * 32;
+constexpr int CTAS_PER_SM = TN == 128 ? 1 : 2;               // 128 registers per thread either way
 constexpr int LAG = 2;                                       // producer runs STAGES - LAG slices ahead
-constexpr int OPERAND_DOUBLES = (BK / 4) * TM * 4;          // 2048 doubles = 16 KB
-constexpr int STAGE_DOUBLES = 2 * OPERAND_DOUBLES;           // A then B
-constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8;       // 192 KB
-constexpr int PANEL_W = 16;                                  // tile columns per L2 panel
+constexpr int OPERAND_DOUBLES = (BK / 4) * TM * 4;          // A slice: 2048 doubles = 16 KB
+constexpr int OPERAND_B_DOUBLES = (BK / 4) * TN * 4;
+constexpr int STAGE_DOUBLES = OPERAND_DOUBLES + OPERAND_B_DOUBLES;   // A then B
+constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8;       // 192 KB (TN 128) / 96 KB (TN 64)
+constexpr int PANEL_W = 2048 / TN;                           // tile columns per L2 panel
 constexpr int PACK_PAD_ROWS = 2 * TM;                        // zero rows after the last real row
 
 __host__ __device__ __forceinline__ long long packed_rows(long long n_rows) {
@@ -204,7 +213,7 @@ __device__ __forceinline__ void tile_epilogue(const ContractArgs& a, double (&ac
 
 // STORE: 0 none, 1 united order, 2 circuit-order scatter.  OUT32: write float instead of double.
 template <int STORE, bool OUT32>
-__global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a) {
+__global__ void __launch_bounds__(THREADS, CTAS_PER_SM) contract_f64_kernel(ContractArgs a) {
     extern __shared__ __align__(128) double smem[];
     __shared__ double scratch[3 * (THREADS / 32)];
     __shared__ __align__(8) uint64_t bar_full[STAGES], bar_empty[STAGES];
@@ -262,7 +271,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_f64_kernel(ContractArgs a
 #pragma unroll 1
     for (int i = 0; i < STAGES - LAG; ++i) produce(i, 0u);
 
-    const int wm = warp >> 2, wn = warp & 3;
+    const int wm = warp / WARPS_N, wn = warp % WARPS_N;
     double acc[4][4][2];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -461,7 +470,7 @@ extern "C" int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const 
     const long long n_tiles = ((n_rows + TM - 1) / TM) * ((n_cols + TN - 1) / TN);
     QDC_REQUIRE(n_tiles < (1ll << 31) - 4096, "too many output tiles for one launch");
     const int sms = qdc_sm_count();
-    const int grid = (int)(n_tiles < sms ? n_tiles : sms);
+    const int grid = (int)(n_tiles < (long long)sms * CTAS_PER_SM ? n_tiles : (long long)sms * CTAS_PER_SM);
     int rc;
     if (store_mode == 0) rc = launch_contract<0, false>(args, grid, s);
     else if (store_mode == 1) rc = out_dtype ? launch_contract<1, true>(args, grid, s)

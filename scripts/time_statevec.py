@@ -61,6 +61,12 @@ def case(name, n_nodes, prep, meas, n_sets, tile_bits, coalesce, basis=None):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "sweep":
+        for t, c in [(12, 4), (11, 4), (10, 4), (9, 4), (11, 3), (10, 3), (13, 4)]:
+            case("C4 prep side", 16, [0, 5, 9, 13], [], 1, t, c)
+        for t, c in [(12, 4), (11, 4), (10, 4), (9, 4), (11, 3), (10, 3), (13, 4)]:
+            case("C4 meas side", 20, [], [3, 8, 12, 17], 1, t, c)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "one":
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4, basis=False)
         case("C4 prep side", 16, [0, 5, 9, 13], [], 1, 12, 4)
