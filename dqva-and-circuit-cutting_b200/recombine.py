@@ -139,7 +139,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                        store: Optional[str] = None, out_dtype=torch.float64,
                        out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
                        stream=None, kernel_events: Optional[list] = None,
-                       packed_cache: Optional[dict] = None) -> ScoreResult:
+                       packed_cache: Optional[dict] = None, method: str = "f64",
+                       slices: int = 6) -> ScoreResult:
     """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
 
     A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
@@ -149,6 +150,9 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
     alone (recorded on the launching stream) is appended to it.
     packed_cache: optional dict reused across calls; operands whose storage and version are
     unchanged are not re-packed (the kernel reads the k-group-major packed copies).
+    method: "f64" (FP64 DMMA, `qdc_contract_f64`) or "i8" (exact 7-bit slicing on the tcgen05 int8
+    tensor cores, `qdc_contract_i8`, `slices` slices per operand; kdim <= 256, store None or
+    "united"; error bound in include/qdc_b200.h).
     """
     lib = _lib.load()
     dev = A.device
@@ -182,6 +186,27 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             _lib.check(lib.qdc_contract_norm(_lib.ptr(A), M, _lib.ptr(Bt), N, kdim, scale,
                                              _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
                        "qdc_contract_norm")
+        if method == "i8":
+            assert store_mode in (0, 1) and out_dtype == torch.float64
+            ws_bytes = int(lib.qdc_contract_i8_workspace_bytes(n_rows, N, kdim, slices))
+            i8ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
+            off = (-i8ws.data_ptr()) % 256
+            if kernel_events is not None:
+                ev0 = torch.cuda.Event(enable_timing=True)
+                ev1 = torch.cuda.Event(enable_timing=True)
+                ev0.record(stream)
+            _lib.check(lib.qdc_contract_i8(
+                _lib.ptr(A), M, _lib.ptr(Bt), row_lo, n_rows, N, kdim, slices, scale, _lib.ptr(norm),
+                threshold, _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
+                _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), store_mode,
+                C.c_void_p(i8ws.data_ptr() + off), _lib.ptr(sums), _lib.ptr(ws["cand_x"]),
+                _lib.ptr(ws["cand_p"]), _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp),
+                "qdc_contract_i8")
+            if kernel_events is not None:
+                ev1.record(stream)
+                kernel_events.append((ev0, ev1))
+            _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
+            return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
         Ap = _packed(lib, A, sp, packed_cache)
         Bp = _packed(lib, Bt, sp, packed_cache)
         if kernel_events is not None:
