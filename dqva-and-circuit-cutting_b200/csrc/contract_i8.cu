@@ -1,43 +1,53 @@
 // K5 (alternative): the contraction on the 5th-generation tensor cores (tcgen05.mma kind::i8,
-// accumulators in TMEM) through an error-free split of the FP64 operands into signed 7-bit
-// slices ("Ozaki scheme"), with the same fused MIS epilogue as contract.cu.
+// accumulators in TMEM) through an error-free split of the FP64 operands into 8-bit digits
+// ("Ozaki scheme"), with the same fused MIS epilogue as contract.cu.
 //
-//   A[r, k] = 2^e_r  * 2^-6 * sum_i s_i[r, k] 2^-7i ,   s_i integer in [-64, 64]   (i < S)
-//   Bt[c, k] = 2^f_c * 2^-6 * sum_j t_j[c, k] 2^-7j
-//   P~[r, c] = scale * 2^(e_r + f_c - 12) * sum_d 2^-7d  D_d[r, c],   D_d = sum_{i+j=d} s_i . t_j
-//
-// Every D_d is an exact int32 dot product (|D_d| <= (d+1) * kdim * 2^12 < 2^23 for kdim <= 256);
-// X = sum_d D_d 2^(7(S-1-d)) is formed exactly in int64 and rounded to FP64 once.  What is
-// dropped: the operand residuals (|.| <= 2^(-7S-1) relative to the row maximum) and the slice
-// pairs with i + j >= S; for S = 6 the result differs from the FP64 product by at most
-//   |err| <= 2^(e_r + f_c) * scale * kdim * (S + 2) * 2^(-7S)   (= 4.7e-10 * 2^(e_r+f_c) * scale for kdim 256)
-// i.e. < 3e-11 for the normalised K = 4 fragment tensors (scale = 1/16), inside the 1e-10 bar of
-// the FP64 path; S is a run-time choice (6 or 7 slices fit the 512 TMEM columns as 64-column
-// accumulators; 6 keeps all A slices of a row block resident in shared memory).
+// Per row r, 2^e_r is a power-of-two ceiling of the row maximum and x' = x 2^(7 - e_r) lies in
+// [-127, 127].  x' (rounded to S radix-256 digits) is written with balanced digits:
+//   x' ~ sum_{i=0..S-1} s_i 256^-i ,   s_i integer in [-128, 127]   (signed bytes),
+// obtained as the two's-complement digits of x' + 128 (256^-1 + ... + 256^-(S-1)) minus 128 (no
+// carries, no overflow); likewise t_j for the columns of Bt.  Every slice pair is one exact
+// integer GEMM:
+//   P~[r, c] = scale * 2^(e_r + f_c - 14) * sum_d 256^-d D_d[r, c],   D_d = sum_{i+j=d} s_i . t_j
+// |D_d| <= (d+1) * kdim * 2^14 < 2^25 for kdim <= 256: exact in the int32 accumulators.
+// X = sum_d D_d 256^(S-1-d) is accumulated by FP64 FMAs (exact while |X| < 2^53; at most two
+// roundings of relative size 2^-53 for S = 6).  What is dropped: the operand rounding (<= 2^(-8S) relative to 2^e_r) and the
+// slice pairs with i + j >= S; both have random sign (balanced digits), and
+//   |err| <= 2^(e_r + f_c) * scale * kdim * (S + 1.1) * 2^(-8S)
+//   S = 5: 1.4e-9, S = 6: 6.5e-12  (x 2^(e_r + f_c) * scale, kdim 256); FP64 itself: 2.8e-14.
+// S is a run-time choice: 6 orders of 64 columns fit the 512 TMEM columns, and S slices of a row
+// block stay resident in shared memory (S = 6, kdim = 256: 192 KB, which leaves a 2-stage ring for
+// the streamed operand; S = 5: 4 stages).
 //
 // Structure (one persistent CTA per SM, 10 warps):
 //   warp 0  producer: bulk async copies (cp.async.bulk + mbarrier complete_tx).  The S slices of
 //           a 128-row block of A (S * 128 * kdim bytes) are loaded once and stay resident while
 //           the CTA walks all column blocks; the slices t_j of a 64-column block stream through a
-//           2-stage ring.
+//           ring whose depth is whatever shared memory is left (2..8 stages).
 //   warp 1  MMA issuer (one lane): for j (ring stage) for i <= S-1-j: 128x64x32 tcgen05.mma steps
 //           into accumulator d = i + j (TMEM columns 64 d .. 64 d + 63); order d is complete
 //           after the first pair of group j = d and is committed to its own mbarrier, so the
 //           epilogue drains orders while later pairs still run.
-//   warps 2-9  epilogue: tcgen05.ld the finished order, X = 128 X + D in registers (32 outputs
-//           per thread), release the accumulator; after the last order: one int64 -> FP64
-//           conversion, the row / column scale, and the MIS sums / candidates of qdc_common.cuh.
+//   warps 2-9  epilogue: tcgen05.ld two finished orders at a time, X = fma(X, 256, D_d) in FP64
+//           (int32 -> FP64 through the 2^52 trick, no conversion unit), release the
+//           accumulators; then, branch-free per output:
+//           q = X cs_c, four running sums per row (sum q, sum q w_c, both again under the
+//           independence mask) and a threshold bit; the row factor (2^e_r, normalisation, row
+//           weight) is applied once per row block, candidates are emitted on a rare slow path.
 // Operands are pre-sliced and stored in the K-major core-matrix order the MMA reads
 // ([8-row group][16-byte k chunk][8 rows][16 bytes]), so a block is one contiguous run.
 #include "qdc_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
 constexpr int TM = 128, TN = 64;
-constexpr int MAX_S = 7;
-constexpr int B_STAGES = 2;
-constexpr int N_EPI_WARPS = 8;
-constexpr int THREADS = (2 + N_EPI_WARPS) * 32;
+constexpr int MAX_S = 6;
+constexpr int MAX_STAGES = 8;                 // ring of streamed-operand slices
+constexpr int CPT = 32;                       // accumulator columns per epilogue thread
+constexpr int N_EPI_WARPS = 4 * (TN / CPT);
+constexpr int FIRST_EPI_WARP = 2;             // warp 0: producer, warp 1: MMA issuer
+constexpr int THREADS = (FIRST_EPI_WARP + N_EPI_WARPS) * 32;
 constexpr int TMEM_COLS = 512;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -56,12 +66,28 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
         " @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// polling costs shared-memory cycles the tensor core wants for its operands: waiters that are
+// not on the critical path back off between polls
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    uint32_t done = 0;
+    while (true) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(ns);
+    }
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -79,14 +105,48 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
         ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+constexpr uint64_t FLAG_ROW_BAD = 1ull << 63, FLAG_COL_BAD = 1ull << 62;   // as in contract.cu
+
+// CPT consecutive TMEM columns of this warp's 32 lanes (one accumulator row per thread)
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+
+// exact int32 -> FP64 without the conversion unit: 2^52 + 2^31 + y has y + 2^31 in its low word
+__device__ __forceinline__ double i32_to_f64(int32_t y) {
+    return __hiloint2double(0x43300000, y ^ (int)0x80000000) - 4503601774854144.0;
+}
+
+// debug counters of the MMA issuer per CTA: total clocks, clocks waiting for b_full / acc_empty /
+// a_full, elapsed ns (globaltimer), MMAs issued
+__device__ long long i8_dbg[QDC_NUM_SMS_B200 * 8];
+
 struct I8Args {
-    const int8_t* A8;        // [S][row blocks][128 x kdim core order]
-    const int8_t* B8;        // [S][col blocks][64 x kdim core order]
+    const uint8_t* A8;        // [S][row blocks][128 x kdim core order]
+    const uint8_t* B8;        // [S][col blocks][64 x kdim core order]
     const double* row_scale; // 2^e_r per row (padded rows: 0)
-    const double* col_scale; // 2^f_c per column
+    const double2* colq;     // per padded column: (2^f_c, 2^f_c * weight); padded columns: 0
+    const uint64_t* colx;    // per padded column: col_x | bit 63 | (column not independent ? bit 62 : 0)
+    int mode;                // debug: bit 0 skips the scoring, bit 1 the TMEM loads, bit 2 the whole epilogue; bit 3: tight polling; bit 4: issuer counters
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
-    int n_rb, n_cb, kdim, S;
-    double out_scale;        // scale * 2^(-12 - 7(S-1))
+    int n_rb, n_cb, kdim, S, n_stages;
+    double out_scale;        // scale * 256^-(S-1)
     const double* d_norm;
     MisTables tab;
     CandSink sink;
@@ -96,7 +156,7 @@ struct I8Args {
 
 __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t a_full, a_empty, b_full[B_STAGES], b_empty[B_STAGES],
+    __shared__ __align__(8) uint64_t a_full, a_empty, b_full[MAX_STAGES], b_empty[MAX_STAGES],
         acc_full[MAX_S], acc_empty[MAX_S];
     __shared__ uint32_t tmem_base_sh;
     __shared__ double scratch[3 * (THREADS / 32)];
@@ -105,11 +165,11 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
     const int S = a.S, kdim = a.kdim;
     const uint32_t a_slice_bytes = TM * kdim, b_slice_bytes = TN * kdim;
     uint8_t* sA = smem;                                   // [S][a_slice_bytes]
-    uint8_t* sB = smem + (size_t)S * a_slice_bytes;       // [B_STAGES][b_slice_bytes]
+    uint8_t* sB = smem + (size_t)S * a_slice_bytes;       // [n_stages][b_slice_bytes]
 
     if (tid == 0) {
         mbar_init(&a_full, 1); mbar_init(&a_empty, 1);
-        for (int s = 0; s < B_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
         for (int d = 0; d < MAX_S; ++d) { mbar_init(&acc_full[d], 1); mbar_init(&acc_empty[d], N_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -126,112 +186,183 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
 
     if (warp == 0) {
         // ================= producer =================
-        if (lane == 0) {
-            int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0;
-            for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
-                mbar_wait(&a_empty, rb_phase ^ 1u);
+        const bool leader = elect_one();
+        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0;
+        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
+            mbar_wait_relaxed(&a_empty, rb_phase ^ 1u, 200);
+            if (leader) {
                 mbar_expect_tx(&a_full, (uint32_t)S * a_slice_bytes);
                 for (int i = 0; i < S; ++i)
                     bulk_g2s(sA + (size_t)i * a_slice_bytes,
                              a.A8 + ((size_t)i * a.n_rb + rb) * a_slice_bytes, a_slice_bytes, &a_full);
-                for (int cb = 0; cb < a.n_cb; ++cb) {
-                    for (int j = 0; j < S; ++j) {
-                        mbar_wait(&b_empty[b_stage], b_phase ^ 1u);
+            }
+            for (int cb = 0; cb < a.n_cb; ++cb) {
+                for (int j = 0; j < S; ++j) {
+                    mbar_wait_relaxed(&b_empty[b_stage], b_phase ^ 1u, 100);
+                    if (leader) {
                         mbar_expect_tx(&b_full[b_stage], b_slice_bytes);
                         bulk_g2s(sB + (size_t)b_stage * b_slice_bytes,
                                  a.B8 + ((size_t)j * a.n_cb + cb) * b_slice_bytes, b_slice_bytes, &b_full[b_stage]);
-                        if (++b_stage == B_STAGES) { b_stage = 0; b_phase ^= 1u; }
                     }
+                    if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
-        if (lane == 0) {
-            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
-            const uint32_t sbo = (uint32_t)(kdim / 16) * 128u;
-            const int ksteps = kdim / 32;
-            int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
-            for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
-                mbar_wait(&a_full, rb_phase);
-                for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
-                    for (int j = 0; j < S; ++j) {
-                        mbar_wait(&b_full[b_stage], b_phase);
-                        tc_fence_after();
-                        const uint32_t b_addr = smem_u32(sB + (size_t)b_stage * b_slice_bytes);
-                        for (int i = 0; i + j < S; ++i) {
-                            const int d = i + j;
-                            if (j == 0) {                              // first touch of order d in this tile
-                                mbar_wait(&acc_empty[d], tile_phase ^ 1u);
-                                tc_fence_after();
-                            }
-                            const uint32_t a_addr = smem_u32(sA + (size_t)i * a_slice_bytes);
-                            const uint32_t tmem_d = tmem + (uint32_t)d * TN;
-                            for (int ks = 0; ks < ksteps; ++ks)
-                                umma_i8(tmem_d, smem_desc(a_addr + ks * 256, 128, sbo),
-                                        smem_desc(b_addr + ks * 256, 128, sbo), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+        // The whole warp walks the loops (so that addresses and descriptors live in uniform
+        // registers); one elected lane issues the MMAs and the commits.
+        const bool leader = elect_one();
+        // D = s32, A = B = signed bytes (bits 7, 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+        const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+        const int ksteps = kdim / 32;
+        // descriptor of address 0; a slice at byte address x is desc0 + (x >> 4), and a step of
+        // 32 k (two 16-byte chunks = 256 bytes in core-matrix order) adds 16
+        const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
+        const uint64_t a_desc0 = desc0 + (smem_u32(sA) >> 4), b_desc0 = desc0 + (smem_u32(sB) >> 4);
+        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
+        const bool dbg = a.mode & 16, no_epi = a.mode & 4;
+        long long w_b = 0, w_acc = 0, w_a = 0, n_mma = 0, t_start = 0, ns_start = 0, t0 = 0;
+        if (dbg) { t_start = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns_start)); }
+        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
+            if (dbg) t0 = clock64();
+            mbar_wait(&a_full, rb_phase);
+            if (dbg) w_a += clock64() - t0;
+            for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
+                for (int j = 0; j < S; ++j) {
+                    if (dbg) t0 = clock64();
+                    mbar_wait(&b_full[b_stage], b_phase);
+                    if (dbg) w_b += clock64() - t0;
+                    tc_fence_after();
+                    const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * (b_slice_bytes >> 4);
+                    for (int i = 0; i + j < S; ++i) {
+                        const int d = i + j;
+                        if (j == 0 && !no_epi) {                   // first touch of order d in this tile
+                            if (dbg) t0 = clock64();
+                            mbar_wait(&acc_empty[d], tile_phase ^ 1u);
+                            if (dbg) w_acc += clock64() - t0;
+                            tc_fence_after();
+                        }
+                        const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
+                        const uint32_t tmem_d = tmem + (uint32_t)d * TN;
+                        if (leader) {
+                            umma_i8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
+#pragma unroll
+                            for (int ks = 1; ks < 8; ++ks)
+                                if (ks < ksteps) umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, 1u);
                             if (i == 0) umma_commit(&acc_full[j]);     // order j is complete
                         }
-                        umma_commit(&b_empty[b_stage]);
-                        if (++b_stage == B_STAGES) { b_stage = 0; b_phase ^= 1u; }
+                        n_mma += ksteps;
                     }
+                    if (leader) umma_commit(&b_empty[b_stage]);
+                    if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
                 }
-                umma_commit(&a_empty);
             }
+            if (leader) umma_commit(&a_empty);
         }
-    } else {
+        if (dbg && leader && blockIdx.x < QDC_NUM_SMS_B200) {
+            long long ns_end;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns_end));
+            long long* o = i8_dbg + blockIdx.x * 8;
+            o[0] = clock64() - t_start; o[1] = w_b; o[2] = w_acc; o[3] = w_a; o[4] = ns_end - ns_start; o[5] = n_mma;
+        }
+    } else if (warp >= FIRST_EPI_WARP) {
         // ================= epilogue =================
-        const int ew = warp - 2;
+        const int ew = warp - FIRST_EPI_WARP;
         const int quarter = warp & 3;                      // TMEM lanes 32 * (warp % 4) .. + 31
-        const int half = ew >> 2;                          // column half of the 64-column accumulator
+        const int part = ew >> 2;                          // which CPT columns of the 64-column accumulator
         const double inv_norm = a.d_norm ? 1.0 / *a.d_norm : 1.0;
         const double thr = a.sink.threshold;
+        const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(part * CPT);
         uint32_t tile_phase = 0;
-        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x) {
+        for (int rb = blockIdx.x; rb < a.n_rb && !(a.mode & 4); rb += gridDim.x) {
             const long long r_loc = (long long)rb * TM + quarter * 32 + lane;       // row inside the slab
             const bool row_ok = r_loc < a.n_rows;
             const long long r = a.row_lo + r_loc;                                   // row in the tables
-            const uint64_t rx = row_ok ? a.tab.row_x[r] : 0ull;
-            const uint64_t rforb = row_ok ? a.tab.row_forb[r] : 0ull;
-            const uint32_t rwok = row_ok ? a.tab.row_wok[r] : 0u;
+            const uint64_t rx = row_ok ? __ldg(a.tab.row_x + r) : 0ull;
+            const uint32_t rwok = row_ok ? __ldg(a.tab.row_wok + r) : 0u;
+            const uint64_t rf = (row_ok ? __ldg(a.tab.row_forb + r) : 0ull) | FLAG_COL_BAD |
+                                ((rwok >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
             const double rs = row_ok ? a.row_scale[r_loc] * a.out_scale * inv_norm : 0.0;
+            // q = X cs_c is compared with the threshold divided by the row factor (rs > 0)
+            const double thr_q = rs > 0.0 ? thr / rs : __longlong_as_double(0x7ff0000000000000ll);
+            double s_q = 0.0, t_q = 0.0, s_ok = 0.0, t_ok = 0.0;   // sum q, sum q w_c, masked likewise
             for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
-                long long X[32];
+                double X[CPT];
 #pragma unroll
-                for (int c = 0; c < 32; ++c) X[c] = 0;
-                for (int d = 0; d < S; ++d) {
-                    mbar_wait(&acc_full[d], tile_phase);
+                for (int c = 0; c < CPT; ++c) X[c] = 0.0;
+                for (int d = 0; d < S; d += 2) {
+                    const bool two = d + 1 < S;
+                    if (a.mode & 8) {
+                        mbar_wait(&acc_full[d], tile_phase);
+                        if (two) mbar_wait(&acc_full[d + 1], tile_phase);
+                    } else {
+                        mbar_wait_relaxed(&acc_full[two ? d + 1 : d], tile_phase, 200);
+                    }
                     tc_fence_after();
-                    uint32_t v[32];
-                    const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(d * TN + half * 32);
-                    asm volatile(
-                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-                        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                        : "r"(taddr));
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    // 16 columns at a time: two orders of them are live next to X
+#pragma unroll
+                    for (int h = 0; h < CPT / 16; ++h) {
+                        uint32_t v0[16], v1[16];
+                        if (!(a.mode & 2)) {
+                            tmem_ld(lane_base + (uint32_t)(d * TN + h * 16), v0);
+                            if (two) tmem_ld(lane_base + (uint32_t)((d + 1) * TN + h * 16), v1);
+                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < 16; ++c) v0[c] = v1[c] = (uint32_t)c;
+                        }
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) {
+                            double x = fma(X[h * 16 + c], 256.0, i32_to_f64((int32_t)v0[c]));
+                            if (two) x = fma(x, 256.0, i32_to_f64((int32_t)v1[c]));
+                            X[h * 16 + c] = x;
+                        }
+                    }
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&acc_empty[d]);
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) X[c] = X[c] * 128 + (long long)(int32_t)v[c];
+                    if (lane == 0) {
+                        mbar_arrive(&acc_empty[d]);
+                        if (two) mbar_arrive(&acc_empty[d + 1]);
+                    }
                 }
-                // scale, score (mis_accumulate of qdc_common.cuh), optional store
-                const long long c0 = (long long)cb * TN + half * 32;
+                const long long c0 = (long long)cb * TN + part * CPT;
+                if (a.mode & 1) {
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const long long col = c0 + c;
-                    if (!row_ok || col >= a.n_cols) continue;
-                    const double p = (double)X[c] * rs * a.col_scale[col];
-                    mis_accumulate(macc, p, rx, rforb, rwok, a.tab.col_x[col], a.tab.col_wok[col], a.sink);
-                    if (a.P_out) a.P_out[r_loc * a.n_cols + col] = p;
+                    for (int c = 0; c < CPT; ++c) s_q += X[c];
+                    continue;
                 }
-                (void)thr;
+                uint32_t hit = 0;
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) {
+                    const double2 cq = __ldg(a.colq + c0 + c);
+                    const uint64_t cf = __ldg(a.colx + c0 + c);
+                    const double q = X[c] * cq.x;
+                    const double xo = (cf & rf) == 0ull ? X[c] : 0.0;
+                    s_q += q;
+                    t_q = fma(X[c], cq.y, t_q);
+                    s_ok = fma(xo, cq.x, s_ok);
+                    t_ok = fma(xo, cq.y, t_ok);
+                    hit |= (q > thr_q ? 1u : 0u) << c;
+                }
+                if (hit) {                                  // rare: outputs above the candidate threshold
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c)
+                        if ((hit >> c) & 1u) {
+                            const double p = X[c] * __ldg(a.colq + c0 + c).x * rs;
+                            cand_emit(a.sink, rx | (__ldg(a.colx + c0 + c) & ~(FLAG_ROW_BAD | FLAG_COL_BAD)), p);
+                        }
+                }
+                if (a.P_out && row_ok) {
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c)
+                        if (c0 + c < a.n_cols) a.P_out[r_loc * a.n_cols + c0 + c] = X[c] * __ldg(a.colq + c0 + c).x * rs;
+                }
             }
+            const double rwd = (double)(rwok & 0xffu);
+            macc.s_p += rs * s_q;
+            macc.s_pw += rs * fma(rwd, s_q, t_q);
+            macc.s_pwok += rs * fma(rwd, s_ok, t_ok);
         }
     }
     // teardown
@@ -242,15 +373,17 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
 }
 
 // ---- slicing pre-pass -----------------------------------------------------------------------
-// one warp per row: exponent from the row maximum, then S slices of every element, written in
-// core-matrix order.  All arithmetic is exact (scaling by powers of two, rint, subtraction).
+// one warp per row: exponent from the row maximum, then S radix-256 digits of every element
+// (two's complement: signed leading digit, unsigned fraction digits; rounded to nearest by adding
+// half a unit of the last digit before truncating), written in core-matrix order.  Scaling by
+// powers of two, floor and the subtractions are exact.
 __device__ __forceinline__ size_t core_offset(int row_in_block, int k, int kdim) {
     return ((size_t)(row_in_block >> 3) * (kdim / 16) + (k >> 4)) * 128 + (row_in_block & 7) * 16 + (k & 15);
 }
 
 __global__ void __launch_bounds__(256) slice_kernel(const double* __restrict__ X, long long n_rows, int kdim_src,
                                                     int kdim, int block_rows, long long n_blocks, int S,
-                                                    int8_t* __restrict__ out, double* __restrict__ scale_out) {
+                                                    uint8_t* __restrict__ out, double* __restrict__ scale_out) {
     const long long row = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const long long rows_pad = n_blocks * block_rows;
@@ -263,31 +396,69 @@ __global__ void __launch_bounds__(256) slice_kernel(const double* __restrict__ X
     for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     int e = 0;
     if (mx > 0.0) frexp(mx, &e);                       // mx = m 2^e, m in [0.5, 1)
-    const double up = ldexp(1.0, 6 - e);               // a' 2^6, |a'| < 1
-    if (lane == 0) scale_out[row] = live ? ldexp(1.0, e) : 0.0;
+    if (mx * ldexp(1.0, 7 - e) > 127.0) ++e;           // keeps the leading digit inside [-128, 127]
+    const double up = ldexp(1.0, 7 - e);               // |x'| <= 127
+    // offset = 128 * sum_{i=1..S-1} 256^-i (turns unsigned fraction digits into balanced ones)
+    // + half a unit of the last digit (round to nearest)
+    double offset = ldexp(1.0, -8 * (S - 1) - 1);
+    for (int i = S - 1; i >= 1; --i) offset += ldexp(1.0, 7 - 8 * i);
+    if (lane == 0) scale_out[row] = live ? ldexp(1.0, e - 7) : 0.0;
     const long long blk = row / block_rows;
     const int rib = (int)(row - blk * block_rows);
     const size_t slice_stride = (size_t)n_blocks * block_rows * kdim;
-    int8_t* base = out + (size_t)blk * block_rows * kdim;
+    uint8_t* base = out + (size_t)blk * block_rows * kdim;
     for (int k = lane; k < kdim; k += 32) {
-        double t = (live && k < kdim_src) ? X[row * kdim_src + k] * up : 0.0;
         const size_t off = core_offset(rib, k, kdim);
-        for (int i = 0; i < S; ++i) {
-            const double s = rint(t);
-            base[(size_t)i * slice_stride + off] = (int8_t)(int)s;
-            t = (t - s) * 128.0;
+        if (!(live && k < kdim_src)) {                 // padding: exact zeros in every slice
+            for (int i = 0; i < S; ++i) base[(size_t)i * slice_stride + off] = 0;
+            continue;
+        }
+        const double t = X[row * kdim_src + k] * up + offset;
+        const double s0 = floor(t);                    // in [-127, 127]
+        base[off] = (uint8_t)(int8_t)(int)s0;
+        double f = t - s0;                             // in [0, 1)
+        for (int i = 1; i < S; ++i) {
+            f *= 256.0;
+            const double u = floor(f);                 // in [0, 255]; the digit is u - 128
+            base[(size_t)i * slice_stride + off] = (uint8_t)(int8_t)((int)u - 128);
+            f -= u;
         }
     }
 }
 
+// per padded column: (2^f_c, 2^f_c * weight) and the flagged mask the epilogue ANDs with the row's
+__global__ void __launch_bounds__(256) coltab_kernel(const double* __restrict__ col_scale,
+                                                     const uint64_t* __restrict__ col_x,
+                                                     const uint32_t* __restrict__ col_wok, long long n_cols,
+                                                     long long cols_pad, double2* __restrict__ colq,
+                                                     uint64_t* __restrict__ colx) {
+    const long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (c >= cols_pad) return;
+    if (c < n_cols) {
+        const uint32_t wok = col_wok[c];
+        const double cs = col_scale[c];
+        colq[c] = make_double2(cs, cs * (double)(wok & 0xffu));
+        colx[c] = col_x[c] | FLAG_ROW_BAD | ((wok >> 8) & 1u ? 0ull : FLAG_COL_BAD);
+    } else {
+        colq[c] = make_double2(0.0, 0.0);
+        colx[c] = FLAG_ROW_BAD | FLAG_COL_BAD;
+    }
+}
+
 }  // namespace
+
+extern "C" int qdc_contract_i8_debug_read(long long* h_out, int n) {
+    QDC_CHECK_CUDA(cudaDeviceSynchronize());
+    QDC_CHECK_CUDA(cudaMemcpyFromSymbol(h_out, i8_dbg, sizeof(long long) * (size_t)(n < QDC_NUM_SMS_B200 * 8 ? n : QDC_NUM_SMS_B200 * 8)));
+    return QDC_OK;
+}
 
 extern "C" int64_t qdc_contract_i8_workspace_bytes(int64_t n_rows, int64_t n_cols, int kdim, int n_slices) {
     if (n_rows < 0 || n_cols < 0 || kdim < 1 || n_slices < 1) return 0;
     const int64_t kd = (kdim + 31) / 32 * 32;
     const int64_t rb = (n_rows + TM - 1) / TM, cb = (n_cols + TN - 1) / TN;
     const int64_t a8 = (rb * TM * kd * n_slices + 255) / 256 * 256, b8 = (cb * TN * kd * n_slices + 255) / 256 * 256;
-    return a8 + b8 + (rb * TM + cb * TN) * 8 + 256;
+    return a8 + b8 + rb * TM * 8 + cb * TN * 32 + 256;
 }
 
 extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const double* d_Bt, int64_t row_lo,
@@ -306,6 +477,7 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     QDC_REQUIRE(kdim >= 1 && kdim <= 256, "the int8 path keeps a row block resident: kdim <= 256");
     QDC_REQUIRE(n_slices >= 2 && n_slices <= 6, "n_slices in 2..6");
     QDC_REQUIRE(n_rows >= 0 && n_cols >= 1, "shape");
+    QDC_REQUIRE(threshold >= 0.0, "candidate threshold must be non-negative");
     QDC_REQUIRE(store_mode == 0 || (store_mode == 1 && d_P_out), "store_mode 0 (none) or 1 (united slab, float64)");
     if (n_rows == 0) return QDC_OK;
     cudaStream_t s = (cudaStream_t)stream;
@@ -316,10 +488,12 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     QDC_REQUIRE((((uintptr_t)ws) & 255) == 0, "workspace must be 256-byte aligned");
     const size_t a8_bytes = ((size_t)n_rb * TM * kd * n_slices + 255) / 256 * 256;
     const size_t b8_bytes = ((size_t)n_cb * TN * kd * n_slices + 255) / 256 * 256;
-    int8_t* A8 = (int8_t*)ws;
-    int8_t* B8 = (int8_t*)(ws + a8_bytes);
+    uint8_t* A8 = ws;
+    uint8_t* B8 = ws + a8_bytes;
     double* rs = (double*)(ws + a8_bytes + b8_bytes);
     double* cs = rs + n_rb * TM;
+    double2* colq = (double2*)(cs + n_cb * TN);
+    uint64_t* colx = (uint64_t*)(colq + n_cb * TN);
     {
         const long long warps = n_rb * TM;
         slice_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, s>>>(d_A + row_lo * kdim, n_rows, kdim, kd, TM, n_rb,
@@ -328,19 +502,27 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
         const long long warps_b = n_cb * TN;
         slice_kernel<<<(unsigned)((warps_b * 32 + 255) / 256), 256, 0, s>>>(d_Bt, n_cols, kdim, kd, TN, n_cb, n_slices, B8, cs);
         QDC_CHECK_LAUNCH();
+        coltab_kernel<<<(unsigned)((warps_b + 255) / 256), 256, 0, s>>>(cs, d_col_x, d_col_wok, n_cols, warps_b, colq, colx);
+        QDC_CHECK_LAUNCH();
     }
     I8Args a;
-    a.A8 = A8; a.B8 = B8; a.row_scale = rs; a.col_scale = cs;
+    a.A8 = A8; a.B8 = B8; a.row_scale = rs; a.colq = colq; a.colx = colx;
+    { const char* m = getenv("QDC_I8_DEBUG"); a.mode = m ? atoi(m) : 0; }
     a.n_rows = n_rows; a.n_cols = n_cols; a.row_lo = row_lo;
     a.n_rb = (int)n_rb; a.n_cb = (int)n_cb; a.kdim = kd; a.S = n_slices;
-    a.out_scale = scale * ldexp(1.0, -12 - 7 * (n_slices - 1));
+    a.out_scale = ldexp(scale, -8 * (n_slices - 1));   // the row / column factors carry 2^(e - 7)
     a.d_norm = d_norm;
     a.tab = {d_row_x, d_row_forb, d_row_wok, d_col_x, d_col_wok};
     a.sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
     a.P_out = store_mode ? (double*)d_P_out : nullptr;
     a.partials = d_partials;
-    const size_t smem = (size_t)n_slices * TM * kd + (size_t)B_STAGES * TN * kd;
-    QDC_REQUIRE(smem <= 227 * 1024 - 2048, "shared memory");
+    const size_t smem_max = 227 * 1024 - 2048, a_res = (size_t)n_slices * TM * kd, b_slice = (size_t)TN * kd;
+    QDC_REQUIRE(a_res + 2 * b_slice <= smem_max, "shared memory");
+    size_t n_stages = (smem_max - a_res) / b_slice;
+    if (n_stages > MAX_STAGES) n_stages = MAX_STAGES;
+    { const char* m = getenv("QDC_I8_STAGES"); if (m && atoi(m) >= 2 && (size_t)atoi(m) < n_stages) n_stages = atoi(m); }
+    a.n_stages = (int)n_stages;
+    const size_t smem = a_res + n_stages * b_slice;
     QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int sms = qdc_sm_count();
     const int grid = (int)(n_rb < sms ? n_rb : sms);

@@ -227,15 +227,15 @@ int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_B
                      double* d_partials, void* stream);
 
 /* The same contraction + fused scoring on the 5th-generation tensor cores (tcgen05.mma kind::i8,
- * TMEM accumulators): the FP64 operands are split, exactly, into n_slices signed 7-bit slices per
- * element with one power-of-two scale per row; all slice-pair products of order i + j < n_slices are
- * accumulated exactly in int32 / int64 and rounded to FP64 once.  Error bound (stated, not
- * measured): |P~ - P~_fp64| <= 2^(e_r + f_c) * scale * kdim * (n_slices + 2) * 2^(-7 n_slices), 2^e_r /
- * 2^f_c = power-of-two ceilings of the row maxima; n_slices = 6, kdim = 256: 4.7e-10 * 2^(e_r+f_c) *
- * scale (< 3e-11 for normalised K = 4 fragment tensors).  Operands are ROW-MAJOR here (d_A:
- * [a_rows_total][kdim], d_Bt: [n_cols][kdim]); slicing is part of the call.  kdim <= 256,
- * n_slices 2..6.  store_mode 0, or 1 = united slab float64.  d_workspace: 256-byte aligned,
- * qdc_contract_i8_workspace_bytes(n_rows, n_cols, kdim, n_slices) bytes. */
+ * TMEM accumulators): the FP64 operands are split into n_slices radix-256 digits per element
+ * (balanced digits in [-128, 127], rounded to nearest) with one power-of-two scale per row; all digit-pair products of order i + j < n_slices are accumulated
+ * exactly in int32 and combined by FP64 FMAs.  Error bound (stated, not measured):
+ * |P~ - P~_exact| <= 2^(e_r + f_c) * scale * kdim * (n_slices + 1.1) * 2^(-8 n_slices), 2^e_r / 2^f_c
+ * = power-of-two ceilings of the row maxima; kdim = 256: 1.4e-9 (5 slices), 6.5e-12 (6 slices)
+ * times 2^(e_r + f_c) * scale -- FP64 accumulation itself: 2.8e-14.  Operands are ROW-MAJOR here
+ * (d_A: [a_rows_total][kdim], d_Bt: [n_cols][kdim]); slicing is part of the call.  kdim <= 256,
+ * n_slices 2..6, threshold >= 0.  store_mode 0, or 1 = united slab float64.  d_workspace:
+ * 256-byte aligned, qdc_contract_i8_workspace_bytes(n_rows, n_cols, kdim, n_slices) bytes. */
 int64_t qdc_contract_i8_workspace_bytes(int64_t n_rows, int64_t n_cols, int kdim, int n_slices);
 int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const double* d_Bt, int64_t row_lo,
                     int64_t n_rows, int64_t n_cols, int kdim, int n_slices, double scale,
