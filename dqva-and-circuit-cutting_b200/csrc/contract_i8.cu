@@ -44,7 +44,7 @@ namespace {
 constexpr int TM = 128, TN = 64;
 constexpr int MAX_S = 6;
 constexpr int MAX_STAGES = 8;                 // ring of streamed-operand slices
-constexpr int CPT = 32;                       // accumulator columns per epilogue thread
+constexpr int CPT = 16;                       // accumulator columns per epilogue thread
 constexpr int N_EPI_WARPS = 4 * (TN / CPT);
 constexpr int FIRST_EPI_WARP = 2;             // warp 0: producer, warp 1: MMA issuer
 constexpr int THREADS = (FIRST_EPI_WARP + N_EPI_WARPS) * 32;
@@ -128,24 +128,29 @@ __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[32]) {
         : "r"(taddr));
 }
 
+__device__ __forceinline__ double opaque(double x) {
+    asm volatile("" : "+d"(x));
+    return x;
+}
+
 // exact int32 -> FP64 without the conversion unit: 2^52 + 2^31 + y has y + 2^31 in its low word
 __device__ __forceinline__ double i32_to_f64(int32_t y) {
     return __hiloint2double(0x43300000, y ^ (int)0x80000000) - 4503601774854144.0;
 }
 
-// debug counters of the MMA issuer per CTA: total clocks, clocks waiting for b_full / acc_empty /
-// a_full, elapsed ns (globaltimer), MMAs issued
-__device__ long long i8_dbg[QDC_NUM_SMS_B200 * 8];
+// exact int64 -> FP64 for |y| < 2^51, same trick (the constant only touches the high word)
+__device__ __forceinline__ double i64_to_f64(long long y) {
+    return __longlong_as_double(y + 0x4338000000000000ll) - 6755399441055744.0;
+}
 
 struct I8Args {
-    const uint8_t* A8;        // [S][row blocks][128 x kdim core order]
-    const uint8_t* B8;        // [S][col blocks][64 x kdim core order]
-    const double* row_scale; // 2^e_r per row (padded rows: 0)
-    const double2* colq;     // per padded column: (2^f_c, 2^f_c * weight); padded columns: 0
+    const uint8_t* A8;       // [S][row blocks][128 x kdim core order]
+    const uint8_t* B8;       // [S][col blocks][64 x kdim core order]
+    const double* row_scale; // 2^(e_r - 7) per row (padded rows: 0)
+    const double2* colq;     // per padded column: (2^(f_c - 7), 2^(f_c - 7) * weight); padded columns: 0
     const uint64_t* colx;    // per padded column: col_x | bit 63 | (column not independent ? bit 62 : 0)
-    int mode;                // debug: bit 0 skips the scoring, bit 1 the TMEM loads, bit 2 the whole epilogue; bit 3: tight polling; bit 4: issuer counters
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
-    int n_rb, n_cb, kdim, S, n_stages;
+    int n_rb, n_cb, kdim, n_stages;
     double out_scale;        // scale * 256^-(S-1)
     const double* d_norm;
     MisTables tab;
@@ -154,6 +159,8 @@ struct I8Args {
     double* partials;
 };
 
+// S = number of slices per operand (compile time: every loop over slice pairs and orders unrolls)
+template <int S>
 __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t a_full, a_empty, b_full[MAX_STAGES], b_empty[MAX_STAGES],
@@ -162,7 +169,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
     __shared__ double scratch[3 * (THREADS / 32)];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int S = a.S, kdim = a.kdim;
+    const int kdim = a.kdim;
     const uint32_t a_slice_bytes = TM * kdim, b_slice_bytes = TN * kdim;
     uint8_t* sA = smem;                                   // [S][a_slice_bytes]
     uint8_t* sB = smem + (size_t)S * a_slice_bytes;       // [n_stages][b_slice_bytes]
@@ -182,7 +189,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
     tc_fence_after();
     const uint32_t tmem = tmem_base_sh;
 
-    MisAccum macc = {0.0, 0.0, 0.0};
+    double cta_pwok = 0.0;                                // this thread's share of sum p w [independent]
 
     if (warp == 0) {
         // ================= producer =================
@@ -192,13 +199,15 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
             mbar_wait_relaxed(&a_empty, rb_phase ^ 1u, 200);
             if (leader) {
                 mbar_expect_tx(&a_full, (uint32_t)S * a_slice_bytes);
+#pragma unroll
                 for (int i = 0; i < S; ++i)
                     bulk_g2s(sA + (size_t)i * a_slice_bytes,
                              a.A8 + ((size_t)i * a.n_rb + rb) * a_slice_bytes, a_slice_bytes, &a_full);
             }
             for (int cb = 0; cb < a.n_cb; ++cb) {
+#pragma unroll
                 for (int j = 0; j < S; ++j) {
-                    mbar_wait_relaxed(&b_empty[b_stage], b_phase ^ 1u, 100);
+                    mbar_wait_relaxed(&b_empty[b_stage], b_phase ^ 1u, 64);
                     if (leader) {
                         mbar_expect_tx(&b_full[b_stage], b_slice_bytes);
                         bulk_g2s(sB + (size_t)b_stage * b_slice_bytes,
@@ -221,26 +230,19 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
         const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
         const uint64_t a_desc0 = desc0 + (smem_u32(sA) >> 4), b_desc0 = desc0 + (smem_u32(sB) >> 4);
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
-        const bool dbg = a.mode & 16, no_epi = a.mode & 4;
-        long long w_b = 0, w_acc = 0, w_a = 0, n_mma = 0, t_start = 0, ns_start = 0, t0 = 0;
-        if (dbg) { t_start = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns_start)); }
         for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
-            if (dbg) t0 = clock64();
             mbar_wait(&a_full, rb_phase);
-            if (dbg) w_a += clock64() - t0;
             for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
+#pragma unroll
                 for (int j = 0; j < S; ++j) {
-                    if (dbg) t0 = clock64();
                     mbar_wait(&b_full[b_stage], b_phase);
-                    if (dbg) w_b += clock64() - t0;
                     tc_fence_after();
                     const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * (b_slice_bytes >> 4);
+#pragma unroll
                     for (int i = 0; i + j < S; ++i) {
                         const int d = i + j;
-                        if (j == 0 && !no_epi) {                   // first touch of order d in this tile
-                            if (dbg) t0 = clock64();
+                        if (j == 0) {                              // first touch of order d in this tile
                             mbar_wait(&acc_empty[d], tile_phase ^ 1u);
-                            if (dbg) w_acc += clock64() - t0;
                             tc_fence_after();
                         }
                         const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
@@ -252,19 +254,12 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                                 if (ks < ksteps) umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, 1u);
                             if (i == 0) umma_commit(&acc_full[j]);     // order j is complete
                         }
-                        n_mma += ksteps;
                     }
                     if (leader) umma_commit(&b_empty[b_stage]);
                     if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
                 }
             }
             if (leader) umma_commit(&a_empty);
-        }
-        if (dbg && leader && blockIdx.x < QDC_NUM_SMS_B200) {
-            long long ns_end;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns_end));
-            long long* o = i8_dbg + blockIdx.x * 8;
-            o[0] = clock64() - t_start; o[1] = w_b; o[2] = w_acc; o[3] = w_a; o[4] = ns_end - ns_start; o[5] = n_mma;
         }
     } else if (warp >= FIRST_EPI_WARP) {
         // ================= epilogue =================
@@ -275,7 +270,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
         const double thr = a.sink.threshold;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(part * CPT);
         uint32_t tile_phase = 0;
-        for (int rb = blockIdx.x; rb < a.n_rb && !(a.mode & 4); rb += gridDim.x) {
+        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x) {
             const long long r_loc = (long long)rb * TM + quarter * 32 + lane;       // row inside the slab
             const bool row_ok = r_loc < a.n_rows;
             const long long r = a.row_lo + r_loc;                                   // row in the tables
@@ -284,91 +279,82 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
             const uint64_t rf = (row_ok ? __ldg(a.tab.row_forb + r) : 0ull) | FLAG_COL_BAD |
                                 ((rwok >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
             const double rs = row_ok ? a.row_scale[r_loc] * a.out_scale * inv_norm : 0.0;
-            // q = X cs_c is compared with the threshold divided by the row factor (rs > 0)
-            const double thr_q = rs > 0.0 ? thr / rs : __longlong_as_double(0x7ff0000000000000ll);
-            double s_q = 0.0, t_q = 0.0, s_ok = 0.0, t_ok = 0.0;   // sum q, sum q w_c, masked likewise
+            // Candidate filter on the high words only: q = X cs_c with cs_c a power of two, so
+            // hi(q) = hi(X) + hi(cs_c) - hi(1.0) for X > 0, and q > thr / rs needs
+            // hi(X) + hi(cs_c) >= hi(thr / rs) + hi(1.0)   (all terms non-negative: unsigned, no overflow).
+            // Exact test on the rare slow path.
+            const double thr_q = rs > 0.0 ? thr / rs : __longlong_as_double(0x7fe0000000000000ll);
+            const uint32_t thr_hi = rs > 0.0 ? (uint32_t)__double2hiint(thr_q) + 0x3ff00000u : 0xffffffffu;
+            double s_ok = 0.0, t_ok = 0.0;              // sum X cs_c and sum X cs_c w_c under the independence mask
             for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
+                // X = sum_d D_d 256^(S-1-d), two orders per round.  D_0 256 + D_1 fits int32
+                // (|D_0| <= 2^22); later pairs are formed in int64 (|.| < 2^34) and folded in by
+                // an FMA; integers enter FP64 through the 2^52 trick, exactly.
                 double X[CPT];
 #pragma unroll
-                for (int c = 0; c < CPT; ++c) X[c] = 0.0;
                 for (int d = 0; d < S; d += 2) {
+                    constexpr int dummy = 0; (void)dummy;
                     const bool two = d + 1 < S;
-                    if (a.mode & 8) {
-                        mbar_wait(&acc_full[d], tile_phase);
-                        if (two) mbar_wait(&acc_full[d + 1], tile_phase);
-                    } else {
-                        mbar_wait_relaxed(&acc_full[two ? d + 1 : d], tile_phase, 200);
-                    }
+                    mbar_wait_relaxed(&acc_full[two ? d + 1 : d], tile_phase, 32);
                     tc_fence_after();
-                    // 16 columns at a time: two orders of them are live next to X
-#pragma unroll
-                    for (int h = 0; h < CPT / 16; ++h) {
-                        uint32_t v0[16], v1[16];
-                        if (!(a.mode & 2)) {
-                            tmem_ld(lane_base + (uint32_t)(d * TN + h * 16), v0);
-                            if (two) tmem_ld(lane_base + (uint32_t)((d + 1) * TN + h * 16), v1);
-                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                        } else {
-#pragma unroll
-                            for (int c = 0; c < 16; ++c) v0[c] = v1[c] = (uint32_t)c;
-                        }
-#pragma unroll
-                        for (int c = 0; c < 16; ++c) {
-                            double x = fma(X[h * 16 + c], 256.0, i32_to_f64((int32_t)v0[c]));
-                            if (two) x = fma(x, 256.0, i32_to_f64((int32_t)v1[c]));
-                            X[h * 16 + c] = x;
-                        }
-                    }
+                    uint32_t v0[CPT], v1[CPT];
+                    tmem_ld(lane_base + (uint32_t)(d * TN), v0);
+                    if (two) tmem_ld(lane_base + (uint32_t)((d + 1) * TN), v1);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
                         mbar_arrive(&acc_empty[d]);
                         if (two) mbar_arrive(&acc_empty[d + 1]);
                     }
+#pragma unroll
+                    for (int c = 0; c < CPT; ++c) {
+                        if (d == 0)
+                            X[c] = i32_to_f64(two ? (int32_t)v0[c] * 256 + (int32_t)v1[c] : (int32_t)v0[c]);
+                        else if (two)
+                            X[c] = fma(X[c], 65536.0, i64_to_f64((long long)(int32_t)v0[c] * 256 + (long long)(int32_t)v1[c]));
+                        else
+                            X[c] = fma(X[c], 256.0, i32_to_f64((int32_t)v0[c]));
+                    }
                 }
                 const long long c0 = (long long)cb * TN + part * CPT;
-                if (a.mode & 1) {
-#pragma unroll
-                    for (int c = 0; c < CPT; ++c) s_q += X[c];
-                    continue;
-                }
-                uint32_t hit = 0;
+                bool any = false;
 #pragma unroll
                 for (int c = 0; c < CPT; ++c) {
                     const double2 cq = __ldg(a.colq + c0 + c);
                     const uint64_t cf = __ldg(a.colx + c0 + c);
-                    const double q = X[c] * cq.x;
-                    const double xo = (cf & rf) == 0ull ? X[c] : 0.0;
-                    s_q += q;
-                    t_q = fma(X[c], cq.y, t_q);
-                    s_ok = fma(xo, cq.x, s_ok);
-                    t_ok = fma(xo, cq.y, t_ok);
-                    hit |= (q > thr_q ? 1u : 0u) << c;
+                    // if ((cf & rf) == 0) { s_ok += X cs_c;  t_ok += X cs_c w_c; }
+                    asm("{\n .reg .pred p;\n .reg .b64 t;\n and.b64 t, %3, %4;\n setp.eq.u64 p, t, 0;\n"
+                        " @p fma.rn.f64 %0, %2, %5, %0;\n @p fma.rn.f64 %1, %2, %6, %1;\n}\n"
+                        : "+d"(s_ok), "+d"(t_ok) : "d"(X[c]), "l"(cf), "l"(rf), "d"(cq.x), "d"(cq.y));
+                    any |= (uint32_t)max(__double2hiint(X[c]), 0) + (uint32_t)__double2hiint(cq.x) >= thr_hi;
+                    if ((c & 3) == 3) asm volatile("" ::: "memory");   // keeps the table loads of 4 columns in flight, not 16
                 }
-                if (hit) {                                  // rare: outputs above the candidate threshold
+                if (any) {                                  // rare: some output may be above the candidate threshold
 #pragma unroll
-                    for (int c = 0; c < CPT; ++c)
-                        if ((hit >> c) & 1u) {
-                            const double p = X[c] * __ldg(a.colq + c0 + c).x * rs;
-                            cand_emit(a.sink, rx | (__ldg(a.colx + c0 + c) & ~(FLAG_ROW_BAD | FLAG_COL_BAD)), p);
-                        }
+                    for (int c = 0; c < CPT; ++c) {
+                        // (laundered: nothing of the fast loop is kept alive for this path)
+                        const double q = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0];
+                        if (q > thr_q)
+                            cand_emit(a.sink, rx | (*(const volatile uint64_t*)(a.colx + c0 + c) & ~(FLAG_ROW_BAD | FLAG_COL_BAD)), q * rs);
+                    }
                 }
                 if (a.P_out && row_ok) {
 #pragma unroll
                     for (int c = 0; c < CPT; ++c)
-                        if (c0 + c < a.n_cols) a.P_out[r_loc * a.n_cols + c0 + c] = X[c] * __ldg(a.colq + c0 + c).x * rs;
+                        if (c0 + c < a.n_cols)
+                            a.P_out[r_loc * a.n_cols + c0 + c] = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0] * rs;
                 }
             }
-            const double rwd = (double)(rwok & 0xffu);
-            macc.s_p += rs * s_q;
-            macc.s_pw += rs * fma(rwd, s_q, t_q);
-            macc.s_pwok += rs * fma(rwd, s_ok, t_ok);
+            // sum p and sum p w do not need the outputs at all (moments_kernel); here only the masked sum
+            cta_pwok += rs * fma((double)(rwok & 0xffu), s_ok, t_ok);
         }
     }
     // teardown
     tc_fence_before();
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+    MisAccum macc = {0.0, cta_pwok, 0.0};
     mis_block_store(macc, scratch, a.partials);
 }
 
@@ -445,11 +431,75 @@ __global__ void __launch_bounds__(256) coltab_kernel(const double* __restrict__ 
     }
 }
 
+// ---- sums that need no outputs ----------------------------------------------------------------
+// sum_{r,c} P~ = scale sum_k (sum_r A[r,k]) (sum_c Bt[c,k]) and, with per-row / per-column weights,
+// sum P~ (w_r + w_c) = scale sum_k (sum_r w_r A[r,k]) (sum_c Bt[c,k]) + (sum_r A[r,k]) (sum_c w_c Bt[c,k]):
+// two passes over the FP64 operands instead of two more FMAs per output.  One warp per row, lane
+// l owns k = l, l + 32, ...; per-CTA partials are combined in a fixed order (deterministic).
+constexpr int MOM_CTAS = 296, MOM_THREADS = 256;
+
+__global__ void __launch_bounds__(MOM_THREADS) moments_kernel(const double* __restrict__ X, long long n_rows, int kdim,
+                                                              const uint32_t* __restrict__ wok,
+                                                              double* __restrict__ partial /* [gridDim.x][2][kdim] */) {
+    __shared__ double red[2][MOM_THREADS / 32][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long gw = (long long)blockIdx.x * (MOM_THREADS / 32) + warp, nw = (long long)gridDim.x * (MOM_THREADS / 32);
+    for (int k0 = 0; k0 < kdim; k0 += 32) {
+        const int k = k0 + lane;
+        double s = 0.0, w = 0.0;
+        if (k < kdim)
+            for (long long r = gw; r < n_rows; r += nw) {
+                const double x = X[r * kdim + k];
+                s += x;
+                w = fma((double)(__ldg(wok + r) & 0xffu), x, w);
+            }
+        red[0][warp][lane] = s;
+        red[1][warp][lane] = w;
+        __syncthreads();
+        if (warp < 2 && k < kdim) {
+            double t = 0.0;
+            for (int i = 0; i < MOM_THREADS / 32; ++i) t += red[warp][i][lane];
+            partial[((size_t)blockIdx.x * 2 + warp) * kdim + k] = t;
+        }
+        __syncthreads();
+    }
+}
+
+// one CTA: sums[0] += scale / norm * sum_k sA sB, sums[2] += scale / norm * sum_k (wA sB + sA wB)
+__global__ void __launch_bounds__(256) moments_finish_kernel(const double* __restrict__ pa, const double* __restrict__ pb,
+                                                             int n_part, int kdim, double scale,
+                                                             const double* __restrict__ d_norm, double* __restrict__ sums) {
+    __shared__ double sp[256], spw[256];
+    const int k = threadIdx.x;
+    double sA = 0.0, wA = 0.0, sB = 0.0, wB = 0.0;
+    if (k < kdim)
+        for (int i = 0; i < n_part; ++i) {
+            sA += pa[((size_t)i * 2 + 0) * kdim + k];
+            wA += pa[((size_t)i * 2 + 1) * kdim + k];
+            sB += pb[((size_t)i * 2 + 0) * kdim + k];
+            wB += pb[((size_t)i * 2 + 1) * kdim + k];
+        }
+    sp[k] = sA * sB;
+    spw[k] = fma(wA, sB, sA * wB);
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (k < o) { sp[k] += sp[k + o]; spw[k] += spw[k + o]; }
+        __syncthreads();
+    }
+    if (k == 0) {
+        const double f = scale * (d_norm ? 1.0 / *d_norm : 1.0);
+        sums[0] += f * sp[0];
+        sums[2] += f * spw[0];
+    }
+}
+
 }  // namespace
 
-extern "C" int qdc_contract_i8_debug_read(long long* h_out, int n) {
-    QDC_CHECK_CUDA(cudaDeviceSynchronize());
-    QDC_CHECK_CUDA(cudaMemcpyFromSymbol(h_out, i8_dbg, sizeof(long long) * (size_t)(n < QDC_NUM_SMS_B200 * 8 ? n : QDC_NUM_SMS_B200 * 8)));
+template <int S>
+int launch_i8(const I8Args& a, int grid, size_t smem, cudaStream_t s) {
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    contract_i8_kernel<S><<<grid, THREADS, smem, s>>>(a);
+    QDC_CHECK_LAUNCH();
     return QDC_OK;
 }
 
@@ -458,7 +508,7 @@ extern "C" int64_t qdc_contract_i8_workspace_bytes(int64_t n_rows, int64_t n_col
     const int64_t kd = (kdim + 31) / 32 * 32;
     const int64_t rb = (n_rows + TM - 1) / TM, cb = (n_cols + TN - 1) / TN;
     const int64_t a8 = (rb * TM * kd * n_slices + 255) / 256 * 256, b8 = (cb * TN * kd * n_slices + 255) / 256 * 256;
-    return a8 + b8 + rb * TM * 8 + cb * TN * 32 + 256;
+    return a8 + b8 + rb * TM * 8 + cb * TN * 32 + 2 * 296 * 2 * 256 * 8 + 256;
 }
 
 extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const double* d_Bt, int64_t row_lo,
@@ -494,6 +544,8 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     double* cs = rs + n_rb * TM;
     double2* colq = (double2*)(cs + n_cb * TN);
     uint64_t* colx = (uint64_t*)(colq + n_cb * TN);
+    double* mom_a = (double*)(colx + n_cb * TN);
+    double* mom_b = mom_a + (size_t)MOM_CTAS * 2 * 256;
     {
         const long long warps = n_rb * TM;
         slice_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, s>>>(d_A + row_lo * kdim, n_rows, kdim, kd, TM, n_rb,
@@ -507,9 +559,8 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     }
     I8Args a;
     a.A8 = A8; a.B8 = B8; a.row_scale = rs; a.colq = colq; a.colx = colx;
-    { const char* m = getenv("QDC_I8_DEBUG"); a.mode = m ? atoi(m) : 0; }
     a.n_rows = n_rows; a.n_cols = n_cols; a.row_lo = row_lo;
-    a.n_rb = (int)n_rb; a.n_cb = (int)n_cb; a.kdim = kd; a.S = n_slices;
+    a.n_rb = (int)n_rb; a.n_cb = (int)n_cb; a.kdim = kd;
     a.out_scale = ldexp(scale, -8 * (n_slices - 1));   // the row / column factors carry 2^(e - 7)
     a.d_norm = d_norm;
     a.tab = {d_row_x, d_row_forb, d_row_wok, d_col_x, d_col_wok};
@@ -523,10 +574,24 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     { const char* m = getenv("QDC_I8_STAGES"); if (m && atoi(m) >= 2 && (size_t)atoi(m) < n_stages) n_stages = atoi(m); }
     a.n_stages = (int)n_stages;
     const size_t smem = a_res + n_stages * b_slice;
-    QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int sms = qdc_sm_count();
     const int grid = (int)(n_rb < sms ? n_rb : sms);
-    contract_i8_kernel<<<grid, THREADS, smem, s>>>(a);
+    int rc = QDC_ERR_ARG;
+    switch (n_slices) {
+        case 2: rc = launch_i8<2>(a, grid, smem, s); break;
+        case 3: rc = launch_i8<3>(a, grid, smem, s); break;
+        case 4: rc = launch_i8<4>(a, grid, smem, s); break;
+        case 5: rc = launch_i8<5>(a, grid, smem, s); break;
+        case 6: rc = launch_i8<6>(a, grid, smem, s); break;
+    }
+    if (rc != QDC_OK) return rc;
+    rc = qdc_launch_finalize_sums(d_partials, grid, d_sums, s);     // the masked sum (slots 0, 2 are zero)
+    if (rc != QDC_OK) return rc;
+    moments_kernel<<<MOM_CTAS, MOM_THREADS, 0, s>>>(d_A + row_lo * kdim, n_rows, kdim, d_row_wok + row_lo, mom_a);
     QDC_CHECK_LAUNCH();
-    return qdc_launch_finalize_sums(d_partials, grid, d_sums, s);
+    moments_kernel<<<MOM_CTAS, MOM_THREADS, 0, s>>>(d_Bt, n_cols, kdim, d_col_wok, mom_b);
+    QDC_CHECK_LAUNCH();
+    moments_finish_kernel<<<1, 256, 0, s>>>(mom_a, mom_b, MOM_CTAS, kdim, scale, d_norm, d_sums);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
 }

@@ -42,15 +42,3 @@ for S in slice_list:
           f"{2 * outs * kdim * pairs / t / 1e9:7.1f} int8 TOP/s  "
           f"d_sum_p {r['sum_p'] - r64['sum_p']:.2e} d_pw_indset {r['sum_pw_indset'] - r64['sum_pw_indset']:.2e}")
 
-if int(os.environ.get("QDC_I8_DEBUG", "0")) & 16:
-    import ctypes, numpy as np
-    from qdc_b200 import _lib
-    lib = ctypes.CDLL(_lib.load()._name)
-    buf = (ctypes.c_longlong * (148 * 8))()
-    lib.qdc_contract_i8_debug_read(buf, 148 * 8)
-    d = np.array(buf[:]).reshape(148, 8)
-    med = np.median(d, axis=0)
-    print("issuer counters (median over CTAs): clocks %.3e  wait b_full %.3e  acc_empty %.3e  a_full %.3e  ns %.3e  mma %d"
-          % tuple(med[:6]))
-    print("  effective SM clock %.0f MHz, clocks per MMA %.1f (excluding waits %.1f)"
-          % (med[0] / med[4] * 1e3, med[0] / med[5], (med[0] - med[1] - med[2] - med[3]) / med[5]))
