@@ -51,6 +51,12 @@ def parse_args():
     ap.add_argument("--cpu-sample-bits", type=int, default=None,
                     help="log2 of the outputs the CPU baseline evaluates (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--method", default="i8", choices=["i8", "f64"],
+                    help="contraction kernel: i8 = radix-256 slices on tcgen05 int8 tensor cores "
+                         "(stated error bound), f64 = FP64 DMMA")
+    ap.add_argument("--slices", type=int, default=6,
+                    help="slices per operand of the i8 method (6: 48-bit operands, bound 6.5e-12 x "
+                         "row/column scale; 5: 40-bit, 1.4e-9)")
     return ap.parse_args()
 
 
@@ -333,14 +339,16 @@ def run_b200(args):
     def step_device():
         # inputs resident in HBM (row-major); packing for the bulk-copy pipeline is part of the step
         res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
-                                    row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events)
+                                    row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
+                                    method=args.method, slices=args.slices)
         return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
 
     def step_e2e():
         A_stage.copy_(A_pin, non_blocking=True)
         Bt_stage.copy_(Bt_pin, non_blocking=True)
         res = rc.contract_and_score(A_stage, Bt_stage, tabs, scale=scale, threshold=1e-5, k=k,
-                                    row_lo=row_lo, n_rows=n_rows)
+                                    row_lo=row_lo, n_rows=n_rows, method=args.method,
+                                    slices=args.slices)
         if ws > 1:
             sums, top = qdist.finish(res.sums, res.top_x, res.top_p, k)
             return sums.cpu().numpy(), top
@@ -393,31 +401,62 @@ def run_b200(args):
     # launching stream inside the timed region, average over the timed steps
     evs = kernel_events[-args.steps:]
     t_kernel = float(np.mean([a.elapsed_time(b) for a, b in evs])) * 1e-3
-    achieved = flops / ws / t_kernel / 1e12
+    if args.method == "i8":
+        # every one of the S (S + 1) / 2 slice pairs is a full int8 GEMM of the same shape
+        pairs = args.slices * (args.slices + 1) // 2
+        int8_ops = flops * pairs / ws
+        peaks = measured_peaks()
+        bf16 = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
+        peak = 2.0 * bf16 if bf16 else 4500.0
+        achieved = int8_ops / t_kernel / 1e12
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s",
+                    "frac": achieved / peak,
+                    "traffic": ncu_traffic(rb, cb, KDIM, ws, "i8"),
+                    "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops_sustained (dense int8 = 2 x "
+                                    "dense bf16 on the tcgen05 pipe; the issue-rate probe "
+                                    "profiles/r1_umma_rate_probe.log reaches 4.50 POP/s at N=256 and "
+                                    "2.52 at the N=64 instruction this kernel issues)") if bf16 else
+                                   "nominal 4.5 POP/s dense int8 (MEASURED_PEAKS.json absent)",
+                    "algorithmic_ops_per_launch": int8_ops,
+                    "algorithmic_ops_note": f"2 x outputs x kdim x {pairs} slice pairs (S = {args.slices})",
+                    "fp64_equivalent_tflops": flops / ws / t_kernel / 1e12,
+                    "fp64_pipe_peak_tflops": dgemm_peak,
+                    "kernel": f"contract_i8_kernel<{args.slices}> (+ slice / column-table / moments kernels)",
+                    "kernel_ms": t_kernel * 1e3}
+        dtype = f"i8 x {args.slices} slices (Ozaki split of FP64 operands, int32 accumulation, FP64 fold)"
+        launches = 11 * args.steps
+    else:
+        achieved = flops / ws / t_kernel / 1e12
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
+                    "unit": "TFLOP/s", "frac": achieved / dgemm_peak,
+                    "traffic": ncu_traffic(rb, cb, KDIM, ws, "f64"),
+                    "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64 DMMA pipe; "
+                                   "MEASURED_PEAKS.json has no FP64 entry; nominal 37 TFLOP/s)",
+                    "algorithmic_flops_per_launch": flops / ws,
+                    "kernel": "contract_f64_kernel", "kernel_ms": t_kernel * 1e3}
+        dtype = "f64"
+        launches = 8 * args.steps
     line = {
         "metric": METRIC, "value": value, "unit": "probs/s", "n_gpus": ws, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": t_dev * 1e3, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": dtype, "data": "synthetic",
         "config": {"workload": f"C4 synthetic 2-fragment 17+17-qubit K=4 recombination + MIS "
                                f"scoring, 2^{n} outputs (BASELINE.json configs[3])",
                    "row_bits": rb, "col_bits": cb, "kdim": KDIM, "topk": k,
+                   "method": args.method, "slices": args.slices if args.method == "i8" else None,
                    "parallelism": f"prefix-shard x{ws}",
                    "l2": "operands 0.5 GB > 126 MB L2; no flush needed"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(A_pin.numel() * 8 + Bt_pin.numel() * 8),
                 "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
-        "gpu_launches": 8 * args.steps,
-        "roofline": {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
-                     "unit": "TFLOP/s", "frac": achieved / dgemm_peak,
-                     "traffic": ncu_traffic(rb, cb, KDIM, ws),
-                     "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64 DMMA pipe; "
-                                    "MEASURED_PEAKS.json has no FP64 entry; nominal 37 TFLOP/s)",
-                     "algorithmic_flops_per_launch": flops / ws,
-                     "kernel": "contract_f64_kernel", "kernel_ms": t_kernel * 1e3},
+        "gpu_launches": launches,
+        "roofline": roofline,
         "result": {"sum_p": sum_p, "avg_cost": -cost, "top": top[:k]},
     }
     if ws == 1:
+        line["other_methods"] = other_methods_leg(torch, rc, A_d, Bt_d, tabs, scale, k, args,
+                                                  outputs_total, cost)
         try:
             line["variant_sims"] = variant_sims_leg(torch, dev)
         except Exception as exc:
@@ -439,13 +478,52 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def ncu_traffic(rb, cb, kdim, ws):
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+def other_methods_leg(torch, rc, A_d, Bt_d, tabs, scale, k, args, outputs_total, cost_headline):
+    """The same step with the other contraction kernels (device-timed, 2 runs after 1 warm-up),
+    and how far their MIS cost is from the headline method's."""
+    out = {}
+    variants = [("f64", None), ("i8", 5), ("i8", 6)]
+    for method, slices in variants:
+        if method == args.method and (method == "f64" or slices == args.slices):
+            continue
+        name = method if slices is None else f"i8_s{slices}"
+        try:
+            ts, res = [], None
+            for it in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
+                                            method=method, slices=slices or 6)
+                e1.record()
+                torch.cuda.synchronize()
+                if it:
+                    ts.append(e0.elapsed_time(e1))
+            r = res.get()
+            out[name] = {"ms_per_step": min(ts), "value": outputs_total / (min(ts) * 1e-3),
+                         "unit": "probs/s",
+                         "cost_minus_headline": r["sum_pw_indset"] - cost_headline,
+                         "sum_p_minus_1": r["sum_p"] - 1.0}
+        except Exception as exc:
+            out[name] = {"value": None, "note": f"failed: {exc}"}
+    return out
+
+
+def ncu_traffic(rb, cb, kdim, ws, method="f64"):
     """dram read + write bytes per launch of the contraction kernel from the committed
     `ncu --set full` capture of this exact configuration (profiles/contract_traffic.json);
     None when the configuration differs."""
     try:
         with open(os.path.join(ROOT, "profiles", "contract_traffic.json")) as f:
             rec = json.load(f)
+        rec = rec.get(method, rec if method == "f64" else {})
         if (rec["row_bits"], rec["col_bits"], rec["kdim"], rec["n_gpus"]) == (rb, cb, kdim, ws):
             return rec["dram_bytes_read"] + rec["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
