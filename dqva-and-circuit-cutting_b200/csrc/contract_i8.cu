@@ -151,6 +151,7 @@ struct I8Args {
     const uint64_t* colx;    // per padded column: col_x | bit 63 | (column not independent ? bit 62 : 0)
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
     int n_rb, n_cb, kdim, n_stages;
+    int n_chunks, chunk_len;  // work item = (row block, chunk of chunk_len column blocks); item = chunk * n_rb + rb
     double out_scale;        // scale * 256^-(S-1)
     const double* d_norm;
     MisTables tab;
@@ -190,12 +191,15 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
     const uint32_t tmem = tmem_base_sh;
 
     double cta_pwok = 0.0;                                // this thread's share of sum p w [independent]
+    const int n_items = a.n_rb * a.n_chunks;
 
     if (warp == 0) {
         // ================= producer =================
         const bool leader = elect_one();
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0;
-        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+            const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
+            const int cb1 = min(a.n_cb, cb0 + a.chunk_len);
             mbar_wait_relaxed(&a_empty, rb_phase ^ 1u, 200);
             if (leader) {
                 mbar_expect_tx(&a_full, (uint32_t)S * a_slice_bytes);
@@ -204,7 +208,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                     bulk_g2s(sA + (size_t)i * a_slice_bytes,
                              a.A8 + ((size_t)i * a.n_rb + rb) * a_slice_bytes, a_slice_bytes, &a_full);
             }
-            for (int cb = 0; cb < a.n_cb; ++cb) {
+            for (int cb = cb0; cb < cb1; ++cb) {
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
                     mbar_wait_relaxed(&b_empty[b_stage], b_phase ^ 1u, 64);
@@ -230,9 +234,10 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
         const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
         const uint64_t a_desc0 = desc0 + (smem_u32(sA) >> 4), b_desc0 = desc0 + (smem_u32(sB) >> 4);
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
-        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x, rb_phase ^= 1u) {
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+            const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
             mbar_wait(&a_full, rb_phase);
-            for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
+            for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
                     mbar_wait(&b_full[b_stage], b_phase);
@@ -266,27 +271,32 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
         const int ew = warp - FIRST_EPI_WARP;
         const int quarter = warp & 3;                      // TMEM lanes 32 * (warp % 4) .. + 31
         const int part = ew >> 2;                          // which CPT columns of the 64-column accumulator
-        const double inv_norm = a.d_norm ? 1.0 / *a.d_norm : 1.0;
-        const double thr = a.sink.threshold;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(part * CPT);
         uint32_t tile_phase = 0;
-        for (int rb = blockIdx.x; rb < a.n_rb; rb += gridDim.x) {
-            const long long r_loc = (long long)rb * TM + quarter * 32 + lane;       // row inside the slab
+        // (few registers here: whatever only the rare paths and the end of an item need -- row
+        // factor, row bits, exact threshold -- is recomputed there from the tables)
+        auto row_factor = [&](int r_loc) -> double {
+            return r_loc < a.n_rows ? a.row_scale[r_loc] * a.out_scale * (a.d_norm ? 1.0 / *a.d_norm : 1.0) : 0.0;
+        };
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
+            const int cb1 = min(a.n_cb, cb0 + a.chunk_len);
+            const int r_loc = rb * TM + quarter * 32 + lane;                        // row inside the slab
             const bool row_ok = r_loc < a.n_rows;
-            const long long r = a.row_lo + r_loc;                                   // row in the tables
-            const uint64_t rx = row_ok ? __ldg(a.tab.row_x + r) : 0ull;
-            const uint32_t rwok = row_ok ? __ldg(a.tab.row_wok + r) : 0u;
-            const uint64_t rf = (row_ok ? __ldg(a.tab.row_forb + r) : 0ull) | FLAG_COL_BAD |
+            const uint32_t rwok = row_ok ? __ldg(a.tab.row_wok + a.row_lo + r_loc) : 0u;
+            const uint64_t rf = (row_ok ? __ldg(a.tab.row_forb + a.row_lo + r_loc) : 0ull) | FLAG_COL_BAD |
                                 ((rwok >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
-            const double rs = row_ok ? a.row_scale[r_loc] * a.out_scale * inv_norm : 0.0;
             // Candidate filter on the high words only: q = X cs_c with cs_c a power of two, so
             // hi(q) = hi(X) + hi(cs_c) - hi(1.0) for X > 0, and q > thr / rs needs
             // hi(X) + hi(cs_c) >= hi(thr / rs) + hi(1.0)   (all terms non-negative: unsigned, no overflow).
             // Exact test on the rare slow path.
-            const double thr_q = rs > 0.0 ? thr / rs : __longlong_as_double(0x7fe0000000000000ll);
-            const uint32_t thr_hi = rs > 0.0 ? (uint32_t)__double2hiint(thr_q) + 0x3ff00000u : 0xffffffffu;
+            uint32_t thr_hi = 0xffffffffu;
+            {
+                const double rs = row_factor(r_loc);
+                if (rs > 0.0) thr_hi = (uint32_t)__double2hiint(a.sink.threshold / rs) + 0x3ff00000u;
+            }
             double s_ok = 0.0, t_ok = 0.0;              // sum X cs_c and sum X cs_c w_c under the independence mask
-            for (int cb = 0; cb < a.n_cb; ++cb, tile_phase ^= 1u) {
+            for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
                 // X = sum_d D_d 256^(S-1-d), two orders per round.  D_0 256 + D_1 fits int32
                 // (|D_0| <= 2^22); later pairs are formed in int64 (|.| < 2^34) and folded in by
                 // an FMA; integers enter FP64 through the 2^52 trick, exactly.
@@ -317,7 +327,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                             X[c] = fma(X[c], 256.0, i32_to_f64((int32_t)v0[c]));
                     }
                 }
-                const long long c0 = (long long)cb * TN + part * CPT;
+                const int c0 = cb * TN + part * CPT;
                 bool any = false;
 #pragma unroll
                 for (int c = 0; c < CPT; ++c) {
@@ -331,6 +341,9 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                     if ((c & 3) == 3) asm volatile("" ::: "memory");   // keeps the table loads of 4 columns in flight, not 16
                 }
                 if (any) {                                  // rare: some output may be above the candidate threshold
+                    const double rs = row_factor(r_loc);
+                    const double thr_q = a.sink.threshold / rs;
+                    const uint64_t rx = __ldg(a.tab.row_x + a.row_lo + r_loc);
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) {
                         // (laundered: nothing of the fast loop is kept alive for this path)
@@ -340,14 +353,15 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                     }
                 }
                 if (a.P_out && row_ok) {
+                    const double rs = row_factor(r_loc);
 #pragma unroll
                     for (int c = 0; c < CPT; ++c)
                         if (c0 + c < a.n_cols)
-                            a.P_out[r_loc * a.n_cols + c0 + c] = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0] * rs;
+                            a.P_out[(long long)r_loc * a.n_cols + c0 + c] = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0] * rs;
                 }
             }
             // sum p and sum p w do not need the outputs at all (moments_kernel); here only the masked sum
-            cta_pwok += rs * fma((double)(rwok & 0xffu), s_ok, t_ok);
+            cta_pwok += row_factor(r_loc) * fma((double)(rwok & 0xffu), s_ok, t_ok);
         }
     }
     // teardown
@@ -575,7 +589,23 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     a.n_stages = (int)n_stages;
     const size_t smem = a_res + n_stages * b_slice;
     const int sms = qdc_sm_count();
-    const int grid = (int)(n_rb < sms ? n_rb : sms);
+    // Work items = row blocks x column chunks, dealt round-robin to one CTA per SM.  Splitting the
+    // column walk costs one more load of the resident slices per item, so chunks stay >= 64 tiles;
+    // among 1, 2, 4, ... chunks take the split that wastes the least of the last wave.
+    int n_chunks = 1;
+    {
+        double best = 1e30;
+        for (int c = 1; c <= 64 && (n_cb + c - 1) / c >= (c == 1 ? 1 : 64); c *= 2) {
+            const long long items = n_rb * c, waves = (items + sms - 1) / sms;
+            const double waste = (double)(waves * sms) / (double)items + 0.002 * c;
+            if (waste < best - 1e-9) { best = waste; n_chunks = c; }
+        }
+    }
+    a.n_chunks = n_chunks;
+    a.chunk_len = (int)((n_cb + n_chunks - 1) / n_chunks);
+    const long long n_items = n_rb * n_chunks;
+    QDC_REQUIRE(n_items < (1ll << 31), "too many work items");
+    const int grid = (int)(n_items < sms ? n_items : sms);
     int rc = QDC_ERR_ARG;
     switch (n_slices) {
         case 2: rc = launch_i8<2>(a, grid, smem, s); break;

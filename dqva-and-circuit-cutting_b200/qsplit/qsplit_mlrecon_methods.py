@@ -635,7 +635,8 @@ def _row_operand(models, sorted_T, sorted_labels, col_labels, s):
 
 
 def recombine_fragment_models(frag_models, wire_path_map, method="network", backend=None,
-                              graph=None, threshold=1e-5, topk=1, store=None, compact="auto"):
+                              graph=None, threshold=1e-5, topk=1, store=None, compact="auto",
+                              contraction=None):
     """Full-circuit distribution from fragment models (:463-472): sum over the 4^K cut-basis
     index of the product of fragment tensors, bits permuted to circuit order, normalised.
 
@@ -643,7 +644,10 @@ def recombine_fragment_models(frag_models, wire_path_map, method="network", back
     Extensions: `graph` (or `backend.graph`) fuses the MIS objective and top-k into the
     contraction; `store=False` never materialises the 2^N array (required beyond ~2^31 outputs);
     `compact` ("auto": from 2^24 outputs on) restricts the contraction to the fragment outcomes
-    that occur at all (all-zero tensor rows are dropped, exactly; see recombine.compact_operands)."""
+    that occur at all (all-zero tensor rows are dropped, exactly; see recombine.compact_operands);
+    `contraction` picks the contraction kernel: "f64" (FP64 DMMA, the default) or "i8" / "i8:S"
+    (S radix-256 slices on the int8 tensor cores, stated error bound in include/qdc_b200.h;
+    needs store=False and 4^K <= 256)."""
     if method not in ("network", "insertion"):
         raise ValueError("recombination method {method} not recognized")     # :469 (sic)
     if not all(isinstance(m, FragmentModel) and m.cut_labels is not None for m in frag_models):
@@ -682,7 +686,13 @@ def recombine_fragment_models(frag_models, wire_path_map, method="network", back
         tabs = tables
         if compact is True or (compact == "auto" and N >= 24):
             A, Bt, tabs, _ = _rc.compact_operands(A, Bt, tables)
+        c_method, c_slices = _rc.resolve_contraction(contraction)
+        if c_method == "i8" and (store or A.shape[1] > 256):
+            if contraction is not None:
+                raise _lib.QdcError("contraction='i8' needs store=False and at most 256 cut-basis terms")
+            c_method = "f64"                              # environment default: fall back to the exact kernel
         res = _rc.contract_and_score(A, Bt, tabs, scale=0.5 ** K, threshold=threshold, k=topk,
-                                     store="circuit" if store else None)
+                                     store="circuit" if store else None, method=c_method,
+                                     slices=c_slices)
         results.append(DeviceDistribution(n_wires, res.P, res, res.norm))
     return results[0] if n_sets == 1 else results

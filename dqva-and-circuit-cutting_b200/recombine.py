@@ -8,6 +8,7 @@ Replaces `recombine_fragment_models` (qsplit/qsplit_mlrecon_methods.py:463-472) 
 """
 from __future__ import annotations
 
+import os
 import ctypes as C
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
@@ -123,6 +124,21 @@ class _Workspace:
             }
             cls._cache[key] = ws
         return ws
+
+
+def resolve_contraction(spec: Optional[str]):
+    """"f64" | "i8" | "i8:S" (S slices, 2..6) -> (method, slices).  None reads the environment
+    variable QDC_CONTRACTION (default "f64": FP64 DMMA, no approximation of any kind)."""
+    if spec is None:
+        spec = os.environ.get("QDC_CONTRACTION", "f64")
+    if spec == "f64":
+        return "f64", 6
+    if spec.startswith("i8"):
+        slices = int(spec[3:]) if len(spec) > 2 else 6
+        if spec[2:3] not in ("", ":") or not 2 <= slices <= 6:
+            raise ValueError(f"contraction {spec!r}: expected 'i8' or 'i8:S' with S in 2..6")
+        return "i8", slices
+    raise ValueError(f"contraction {spec!r} not recognized ('f64', 'i8', 'i8:S')")
 
 
 def _default_cap(total: int, threshold: float) -> int:

@@ -144,3 +144,30 @@ def test_c3_n33_three_fragments_properties(cuda, golden_dir):
     assert abs(out["sum_p"] - 1) < 1e-9
     assert 0 <= out["sum_pw_indset"] <= out["sum_pw"] + 1e-12 <= 33
     assert all(0 < p <= 1 for _, p in out["top"])
+
+
+def test_c3_n33_int8_contraction_matches_fp64(cuda, golden_dir):
+    """The same 3-fragment, 2^36-output evaluation through the int8-sliced contraction
+    (contraction="i8:6" and "i8:5") against the FP64 DMMA kernel: costs within 1e-10, same top-k."""
+    from qdc_b200.engine import B200Backend
+    from qdc_b200.utils.cutting_funcs import sim_with_cutting
+    G = _graph(golden_dir, "N33_com3_pin80_pout2_G1")
+    partition = [list(range(0, 11)), list(range(11, 22)), list(range(22, 33))]
+    for max_cuts in (2, 3, 4):
+        try:
+            circ, cuts, frags, wpm, meta = _cut_circuit(G, partition, max_cuts, 2, fused=False)
+            break
+        except IndexError:
+            continue
+    else:
+        pytest.skip("no feasible hot-node set")
+    be = B200Backend(device=cuda, graph=G)
+    kw = dict(mode="direct", store=False, threshold=1e-3, topk=2)
+    ref = sim_with_cutting(frags, wpm, 1, be, contraction="f64", **kw).score.get()
+    for spec in ("i8:6", "i8:5"):
+        out = sim_with_cutting(frags, wpm, 1, be, contraction=spec, **kw).score.get()
+        for key in ("sum_p", "sum_pw", "sum_pw_indset"):
+            assert abs(out[key] - ref[key]) < 1e-10, (spec, key, out[key], ref[key])
+        assert [x for x, _ in out["top"]] == [x for x, _ in ref["top"]]
+        for (_, p), (_, q) in zip(out["top"], ref["top"]):
+            assert abs(p - q) < 1e-10
