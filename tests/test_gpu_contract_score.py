@@ -168,3 +168,39 @@ def test_int8_sliced_contraction_matches_fp64(cuda, rb, cb, kdim, slices):
     if slices >= 5:
         assert [x for x, _ in s_got["top"]] == [x for x, _ in ref["top"]]
     assert abs(s_got["sum_p"] - want.sum()) <= tot_bound + 1e-9 * abs(want.sum())
+
+
+@pytest.mark.parametrize("slices", [4, 5, 6])
+def test_int8_sliced_contraction_per_output_bound(cuda, slices):
+    """Every output of qdc_contract_i8 (united store) against the float64 product: the stated bound
+    kdim (S + 1.1) 2^(-8S) 2^(e_r + f_c) scale holds per output, on operands whose rows span twelve
+    orders of magnitude and include zero rows, negative entries and exact powers of two."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rb, cb, kdim = 8, 7, 256
+    rng = np.random.default_rng(slices)
+    M, N = 1 << rb, 1 << cb
+    A = rng.standard_normal((M, kdim)) * 10.0 ** rng.uniform(-12, 0, (M, 1))
+    Bt = rng.standard_normal((N, kdim)) * 10.0 ** rng.uniform(-6, 0, (N, 1))
+    A[3] = 0.0
+    A[5] = 2.0 ** -7                                      # row maximum an exact power of two
+    Bt[7, :] = np.where(np.arange(kdim) % 2 == 0, 1.0, -1.0)
+    G = __import__("networkx").gnm_random_graph(rb + cb, 30, seed=2)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    scale = 1.0 / 16
+    res = rc.contract_and_score(torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda), tabs,
+                                scale=scale, threshold=float("inf"), k=1, normalize=False,
+                                store="united", method="i8", slices=slices)
+    got = res.P.cpu().numpy()
+    want = scale * (A @ Bt.T)
+    with np.errstate(divide="ignore"):
+        ea = np.where(np.abs(A).max(axis=1) > 0, np.floor(np.log2(np.abs(A).max(axis=1))) + 1, -2000.0)[:, None]
+        fb = np.floor(np.log2(np.abs(Bt).max(axis=1)))[None, :] + 1
+    # + 1: the exponent is bumped when the scaled maximum would exceed 127 / 128
+    bound = 2.0 ** (ea + fb + 2) * scale * kdim * (slices + 1.1) * 2.0 ** (-8 * slices)
+    fp64_noise = 4 * kdim * 2.0 ** -53 * scale * (np.abs(A) @ np.abs(Bt).T)
+    assert np.all(np.abs(got - want) <= bound + fp64_noise), float(np.max(np.abs(got - want) / (bound + fp64_noise + 1e-300)))
+    assert np.all(got[3] == 0.0)
+    s = res.get()
+    assert abs(s["sum_p"] - want.sum()) <= bound.sum() + 1e-12 * np.abs(want).sum()
