@@ -98,3 +98,17 @@ def test_maximum_likelihood_matches_oracle(noise):
         assert set(got.keys()) == set(want.keys())
         for bits in want:
             assert np.abs(got[bits] - want[bits]).max() < 1e-10
+
+
+def test_contraction_spec_parsing(monkeypatch):
+    """recombine.resolve_contraction: 'f64' | 'i8' | 'i8:S', environment default, loud errors."""
+    from qdc_b200 import recombine as rc
+    monkeypatch.delenv("QDC_CONTRACTION", raising=False)
+    assert rc.resolve_contraction(None) == ("f64", 6)
+    assert rc.resolve_contraction("i8") == ("i8", 6)
+    assert rc.resolve_contraction("i8:5") == ("i8", 5)
+    monkeypatch.setenv("QDC_CONTRACTION", "i8:4")
+    assert rc.resolve_contraction(None) == ("i8", 4)
+    for bad in ("i8:7", "i8:1", "i8x", "tf32", ""):
+        with pytest.raises(ValueError):
+            rc.resolve_contraction(bad)
