@@ -326,8 +326,15 @@ def run_b200(args):
     Bt_d = torch.from_numpy(Bt_h).to(dev)
     A_pin = torch.from_numpy(A_h).pin_memory()
     Bt_pin = torch.from_numpy(Bt_h).pin_memory()
-    A_stage = torch.empty_like(A_d)
+    # e2e at N > 1: every rank receives only ITS rows of the row operand (and the whole column
+    # operand); the normalisation then needs the column sums of all slabs: dist.sharded_norm
+    A_pin_slab = A_pin[row_lo:row_lo + n_rows]
+    A_stage = torch.empty(n_rows, KDIM, dtype=torch.float64, device=dev)
     Bt_stage = torch.empty_like(Bt_d)
+    tabs_slab = rc.MisTables(tabs.row_bits, tabs.col_bits, tabs.row_x[row_lo:row_lo + n_rows].contiguous(),
+                             tabs.row_forb[row_lo:row_lo + n_rows].contiguous(),
+                             tabs.row_wok[row_lo:row_lo + n_rows].contiguous(), tabs.col_x, tabs.col_wok,
+                             tabs.bitpos, tabs.node_mask)
 
     def barrier():
         if ws > 1:
@@ -344,11 +351,11 @@ def run_b200(args):
         return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
 
     def step_e2e():
-        A_stage.copy_(A_pin, non_blocking=True)
+        A_stage.copy_(A_pin_slab, non_blocking=True)
         Bt_stage.copy_(Bt_pin, non_blocking=True)
-        res = rc.contract_and_score(A_stage, Bt_stage, tabs, scale=scale, threshold=1e-5, k=k,
-                                    row_lo=row_lo, n_rows=n_rows, method=args.method,
-                                    slices=args.slices)
+        norm = qdist.sharded_norm(A_stage, Bt_stage, scale) if ws > 1 else None
+        res = rc.contract_and_score(A_stage, Bt_stage, tabs_slab, scale=scale, threshold=1e-5, k=k,
+                                    method=args.method, slices=args.slices, norm=norm)
         if ws > 1:
             sums, top = qdist.finish(res.sums, res.top_x, res.top_p, k)
             return sums.cpu().numpy(), top
@@ -387,6 +394,13 @@ def run_b200(args):
         sums, top = last_dev
         sum_p, cost = float(sums[0].item()), float(sums[1].item())
     assert abs(sum_p - 1.0) < 1e-9, f"distribution does not sum to 1: {sum_p}"
+    # the end-to-end leg (host operands, sharded row operand at N > 1) must land on the same numbers
+    if ws == 1:
+        e2e_sum_p, e2e_cost = last_e2e["sum_p"], last_e2e["sum_pw_indset"]
+    else:
+        e2e_sum_p, e2e_cost = float(last_e2e[0][0]), float(last_e2e[0][1])
+    assert abs(e2e_sum_p - sum_p) < 1e-12 and abs(e2e_cost - cost) < 1e-12, \
+        f"e2e leg disagrees with the device leg: {e2e_sum_p} {e2e_cost} vs {sum_p} {cost}"
 
     if rank != 0:
         if ws > 1:
@@ -448,7 +462,7 @@ def run_b200(args):
                    "l2": "operands 0.5 GB > 126 MB L2; no flush needed"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
-                "h2d_bytes_per_step": int(A_pin.numel() * 8 + Bt_pin.numel() * 8),
+                "h2d_bytes_per_step": int(A_pin.numel() * 8 + ws * Bt_pin.numel() * 8),
                 "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
         "gpu_launches": launches,
         "roofline": roofline,

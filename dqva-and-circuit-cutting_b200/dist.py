@@ -15,7 +15,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "merge_topk",
-           "sharded_over_parameter_sets"]
+           "sharded_over_parameter_sets", "sharded_norm"]
 
 
 def init_from_env(backend: str | None = None) -> Tuple[int, int, int]:
@@ -54,6 +54,19 @@ def row_shard(n_rows: int, rank: int, world_size: int) -> Tuple[int, int]:
 def round_robin(n_items: int, rank: int, world_size: int) -> List[int]:
     """Indices of the (fragment variant x parameter set) work items owned by `rank`."""
     return list(range(rank, n_items, world_size))
+
+
+def sharded_norm(A_slab: torch.Tensor, Bt: torch.Tensor, scale: float) -> torch.Tensor:
+    """Normalisation of the recombined distribution when every rank holds only ITS rows of the row
+    operand: sum_{r,c} P~ = scale * sum_k (sum_r A[r,k]) (sum_c Bt[c,k]), so the ranks all-reduce
+    the kdim column sums of their slabs (the one real exchange of the sharded-operand layout:
+    kdim doubles per rank).  Returns a 1-element float64 tensor on A_slab's device, the form
+    `recombine.contract_and_score(norm=...)` takes."""
+    col = A_slab.sum(dim=0, dtype=torch.float64)
+    _, ws = world()
+    if ws > 1:
+        dist.all_reduce(col, op=dist.ReduceOp.SUM)
+    return (scale * torch.dot(col, Bt.sum(dim=0, dtype=torch.float64))).reshape(1)
 
 
 def merge_topk(cands: Sequence[Tuple[int, float]], k: int) -> List[Tuple[int, float]]:

@@ -156,7 +156,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                        out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
                        stream=None, kernel_events: Optional[list] = None,
                        packed_cache: Optional[dict] = None, method: str = "f64",
-                       slices: int = 6) -> ScoreResult:
+                       slices: int = 6, norm: Optional[torch.Tensor] = None) -> ScoreResult:
     """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
 
     A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
@@ -166,6 +166,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
     alone (recorded on the launching stream) is appended to it.
     packed_cache: optional dict reused across calls; operands whose storage and version are
     unchanged are not re-packed (the kernel reads the k-group-major packed copies).
+    norm: a 1-element float64 device tensor to divide by instead of the total of THIS call's
+    operands (a rank that holds only its row slab passes `dist.sharded_norm`).
     method: "f64" (FP64 DMMA, `qdc_contract_f64`) or "i8" (exact 7-bit slicing on the tcgen05 int8
     tensor cores, `qdc_contract_i8`, `slices` slices per operand; kdim <= 256, store None or
     "united"; error bound in include/qdc_b200.h).
@@ -188,7 +190,11 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
     cand_count = torch.zeros(1, dtype=torch.int64, device=dev)
     top_x = torch.empty(k, dtype=torch.int64, device=dev)
     top_p = torch.empty(k, **f64)
-    norm = torch.empty(1, **f64) if normalize else None
+    given_norm = norm is not None
+    if given_norm:
+        assert norm.dtype == torch.float64 and norm.numel() == 1 and norm.device == dev
+    elif normalize:
+        norm = torch.empty(1, **f64)
     store_mode = {None: 0, "united": 1, "circuit": 2}[store]
     odt = 0 if out_dtype == torch.float64 else 1
     if store_mode and out is None:
@@ -198,7 +204,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             out = torch.zeros(1 << (tables.row_bits + tables.col_bits), dtype=out_dtype, device=dev)
     sp = _lib.stream_ptr(stream)
     with torch.cuda.device(dev):
-        if normalize:
+        if normalize and not given_norm:
             _lib.check(lib.qdc_contract_norm(_lib.ptr(A), M, _lib.ptr(Bt), N, kdim, scale,
                                              _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
                        "qdc_contract_norm")

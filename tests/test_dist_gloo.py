@@ -84,3 +84,33 @@ def test_parameter_sets_sharded_world_size_2():
     want = [2.0 * sum(range(3 * i, 3 * i + 3)) for i in range(7)]
     assert out[0][0] == want and out[1][0] == want
     assert out[0][1] == [4] and out[1][1] == [3]
+
+
+def _worker_norm(rank, ws, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
+    import importlib, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import dist as qd
+    qd.init_from_env(backend="gloo")
+    g = torch.Generator().manual_seed(5)
+    A = torch.randn(37, 16, dtype=torch.float64, generator=g)
+    Bt = torch.randn(21, 16, dtype=torch.float64, generator=g)
+    lo, cnt = qd.row_shard(A.shape[0], rank, ws)
+    norm = qd.sharded_norm(A[lo:lo + cnt], Bt, 0.25)
+    out[rank] = (float(norm.item()), float(0.25 * (A @ Bt.T).sum().item()))
+    dist.destroy_process_group()
+
+
+def test_sharded_norm_world_size_2():
+    """Every rank holds only its row slab; the all-reduced column sums give the total of the
+    whole product on every rank."""
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_norm, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    for rank in range(ws):
+        got, want = out[rank]
+        assert abs(got - want) < 1e-12 * max(1.0, abs(want))
+    assert out[0][0] == out[1][0]
