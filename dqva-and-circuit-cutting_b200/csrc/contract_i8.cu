@@ -105,6 +105,18 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
         ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+// the same with the A operand in tensor memory (128 lanes x 8 columns = 128 rows x 32 bytes)
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+        " tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n}\n"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 128 rows x 32 bytes of a K-major core-matrix image (the descriptor the MMA would take) -> 8 TMEM columns
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t tmem_dst, uint64_t sdesc) {
+    asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(tmem_dst), "l"(sdesc) : "memory");
+}
+
 constexpr uint64_t FLAG_ROW_BAD = 1ull << 63, FLAG_COL_BAD = 1ull << 62;   // as in contract.cu
 
 // CPT consecutive TMEM columns of this warp's 32 lanes (one accumulator row per thread)
@@ -151,6 +163,7 @@ struct I8Args {
     const uint64_t* colx;    // per padded column: col_x | bit 63 | (column not independent ? bit 62 : 0)
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
     int n_rb, n_cb, kdim, n_stages;
+    int tmem_a;              // 1: leading resident slices are read from tensor memory (QDC_I8_TMEM_A=0 turns it off)
     int n_chunks, chunk_len;  // work item = (row block, chunk of chunk_len column blocks); item = chunk * n_rb + rb
     double out_scale;        // scale * 256^-(S-1)
     const double* d_norm;
@@ -233,10 +246,24 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
         // 32 k (two 16-byte chunks = 256 bytes in core-matrix order) adds 16
         const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
         const uint64_t a_desc0 = desc0 + (smem_u32(sA) >> 4), b_desc0 = desc0 + (smem_u32(sB) >> 4);
+        // TMEM columns [S * TN, 512) hold the first n_ta resident slices (kdim / 4 columns each)
+        const uint32_t tmem_a0 = tmem + (uint32_t)(S * TN);
+        const int n_ta = a.tmem_a ? min(S, (TMEM_COLS - S * TN) / (kdim / 4)) : 0;
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
             const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
             mbar_wait(&a_full, rb_phase);
+            tc_fence_after();
+            // The leading slices of the resident operand (the most used ones: slice i enters S - i
+            // pairs) go to the TMEM columns the accumulators leave free: an MMA that takes A from
+            // tensor memory reads only the 2 KB of its B tile from shared memory instead of 6 KB
+            // (the N = 64 instruction is bound by that read).  tcgen05 operations of one thread
+            // execute in issue order, so the copies wait for the previous item's MMAs.
+            if (leader)
+                for (int i = 0; i < n_ta; ++i)
+                    for (int ks = 0; ks < ksteps; ++ks)
+                        tmem_cp_128x256b(tmem_a0 + (uint32_t)(i * ksteps + ks) * 8u,
+                                         a_desc0 + (uint32_t)i * (a_slice_bytes >> 4) + ks * 16);
             for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
@@ -253,10 +280,18 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                         const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
                         const uint32_t tmem_d = tmem + (uint32_t)d * TN;
                         if (leader) {
-                            umma_i8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
+                            if (i < n_ta) {
+                                const uint32_t ta = tmem_a0 + (uint32_t)(i * ksteps) * 8u;
+                                umma_i8_ts(tmem_d, ta, b_desc, idesc, j > 0 ? 1u : 0u);
 #pragma unroll
-                            for (int ks = 1; ks < 8; ++ks)
-                                if (ks < ksteps) umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, 1u);
+                                for (int ks = 1; ks < 8; ++ks)
+                                    if (ks < ksteps) umma_i8_ts(tmem_d, ta + ks * 8, b_desc + ks * 16, idesc, 1u);
+                            } else {
+                                umma_i8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
+#pragma unroll
+                                for (int ks = 1; ks < 8; ++ks)
+                                    if (ks < ksteps) umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, 1u);
+                            }
                             if (i == 0) umma_commit(&acc_full[j]);     // order j is complete
                         }
                     }
@@ -601,6 +636,7 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
             if (waste < best - 1e-9) { best = waste; n_chunks = c; }
         }
     }
+    { const char* m = getenv("QDC_I8_TMEM_A"); a.tmem_a = m ? atoi(m) : 1; }
     a.n_chunks = n_chunks;
     a.chunk_len = (int)((n_cb + n_chunks - 1) / n_chunks);
     const long long n_items = n_rb * n_chunks;
