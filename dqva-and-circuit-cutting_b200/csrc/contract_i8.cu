@@ -27,7 +27,10 @@
 //   warp 1  MMA issuer (one lane): for j (ring stage) for i <= S-1-j: 128x64x32 tcgen05.mma steps
 //           into accumulator d = i + j (TMEM columns 64 d .. 64 d + 63); order d is complete
 //           after the first pair of group j = d and is committed to its own mbarrier, so the
-//           epilogue drains orders while later pairs still run.
+//           epilogue drains orders while later pairs still run.  The first n_ta resident slices are
+//           copied to the TMEM columns the accumulators leave free (tcgen05.cp.128x256b) at the
+//           start of a work item; their pairs take A from tensor memory and read only the B tile
+//           from shared memory (the N = 64 instruction is bound by the 6 KB operand read).
 //   warps 2-9  epilogue: tcgen05.ld two finished orders at a time, X = fma(X, 256, D_d) in FP64
 //           (int32 -> FP64 through the 2^52 trick, no conversion unit), release the
 //           accumulators; then, branch-free per output:
