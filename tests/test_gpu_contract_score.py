@@ -204,3 +204,48 @@ def test_int8_sliced_contraction_per_output_bound(cuda, slices):
     assert np.all(got[3] == 0.0)
     s = res.get()
     assert abs(s["sum_p"] - want.sum()) <= bound.sum() + 1e-12 * np.abs(want).sum()
+
+
+def test_int8_contraction_row_slabs_and_given_norm(cuda):
+    """The sharded layout of bench.py's e2e leg on one GPU: every 'rank' holds only its rows of the
+    row operand and divides by a norm computed from all slabs (dist.sharded_norm, world size 1 per
+    call here, so the column sums are added by hand); slab sums add up to the full evaluation and
+    the union of the slab candidates is the full candidate set."""
+    import torch
+    from qdc_b200 import recombine as rc, dist as qdist
+    rb, cb, kdim = 9, 8, 64
+    rng = np.random.default_rng(11)
+    M, N = 1 << rb, 1 << cb
+    A = torch.as_tensor(rng.random((M, kdim)) * 10.0 ** rng.uniform(-4, 0, (M, 1)), device=cuda)
+    Bt = torch.as_tensor(rng.random((N, kdim)), device=cuda)
+    G = __import__("networkx").gnm_random_graph(rb + cb, 24, seed=3)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    scale, thr = 0.125, 2e-5
+    full = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=6).get()
+    norm = scale * torch.dot(A.sum(0), Bt.sum(0)).reshape(1)
+    assert abs(float(qdist.sharded_norm(A, Bt, scale)) - float(norm)) < 1e-12 * float(norm)
+    tot = {"sum_p": 0.0, "sum_pw": 0.0, "sum_pw_indset": 0.0}
+    cands = []
+    for lo, cnt in [qdist.row_shard(M, r, 3) for r in range(3)]:
+        slab_tabs = rc.MisTables(rb, cb, tabs.row_x[lo:lo + cnt].contiguous(), tabs.row_forb[lo:lo + cnt].contiguous(),
+                                 tabs.row_wok[lo:lo + cnt].contiguous(), tabs.col_x, tabs.col_wok, tabs.bitpos,
+                                 tabs.node_mask)
+        part = rc.contract_and_score(A[lo:lo + cnt].contiguous(), Bt, slab_tabs, scale=scale, threshold=thr, k=8,
+                                     method="i8", slices=6, norm=norm).get()
+        # the same slab addressed inside the full operand (row_lo / n_rows form) must agree exactly
+        part2 = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=6,
+                                      row_lo=lo, n_rows=cnt).get()
+        # (the given norm and the library's own differ in the last bit)
+        assert abs(part["sum_pw_indset"] - part2["sum_pw_indset"]) < 1e-13
+        assert [x for x, _ in part["top"]] == [x for x, _ in part2["top"]]
+        assert all(abs(p - q) < 1e-15 for (_, p), (_, q) in zip(part["top"], part2["top"]))
+        for key in tot:
+            tot[key] += part[key]
+        cands += part["top"]
+    for key in tot:
+        assert abs(tot[key] - full[key]) < 1e-12, (key, tot[key], full[key])
+    assert abs(tot["sum_p"] - 1.0) < 1e-12
+    merged = qdist.merge_topk(cands, 8)
+    assert [x for x, _ in merged] == [x for x, _ in full["top"]]
+    assert all(abs(p - q) < 1e-15 for (_, p), (_, q) in zip(merged, full["top"]))
