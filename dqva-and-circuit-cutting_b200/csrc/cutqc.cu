@@ -110,6 +110,143 @@ __global__ void __launch_bounds__(256) merge_kernel(const double* __restrict__ i
     }
 }
 
+// ---- tiled signed marginal (measure and merge at HBM speed) ---------------------------------------
+//   out[v][a] = sum_m (-1)^popc(x & sign_v) in[v][x],   x = dep(a, keep) | dep(m, summed) | fixed
+// The per-element bit deposits of the kernels above cost ~100 instructions per element (5-15 % of
+// the HBM rate).  Here the index is split at bit TILE_BITS: one CTA owns (vector, high kept bits)
+// and walks the high summed bits; each step loads one contiguous tile of 2^TILE_BITS elements
+// (coalesced 16-byte loads, sign of the low bits applied on the way) into shared memory, and the
+// low bits are resolved through two small tables, so an element costs one shared-memory read, an
+// OR and an add.  Accumulation order is fixed (deterministic).  Algorithmic bytes: the input once,
+// the output once.
+constexpr int TILE_BITS = 12, MARG_THREADS = 256, MARG_ACC = (1 << TILE_BITS) / MARG_THREADS;
+
+struct MargArgs {
+    const void* in;
+    double* out;
+    const uint64_t* sign_masks;      // per vector, or null
+    long long n_vec;
+    int d, tile_bits;                // total index bits; low bits inside a tile (<= TILE_BITS)
+    uint64_t keep_mask, sum_mask, fixed_val;
+};
+
+template <typename T, bool LOOP>
+__global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(const MargArgs a) {
+    __shared__ double tile[1 << TILE_BITS];
+    __shared__ uint16_t lut_a[1 << TILE_BITS], lut_m[1 << TILE_BITS];
+    constexpr int VEC = 16 / (int)sizeof(T), VEC_BITS = VEC == 4 ? 2 : 1;
+    const int L = a.tile_bits, tid = threadIdx.x;
+    const uint64_t low = (1ull << L) - 1ull;
+    // trailing summed bits that fall inside one 16-byte load are added up in registers on the way
+    // in (tz of them): the tile in shared memory then starts at the first bit that is not summed
+    int tz = 0;
+    while (tz < VEC_BITS && tz < L && ((a.sum_mask >> tz) & 1ull)) ++tz;
+    const int Lt = L - tz;                                         // bits of the compacted tile
+    const uint64_t keep_lo = (a.keep_mask & low) >> tz, sum_lo = (a.sum_mask & low) >> tz, fixed_lo = (a.fixed_val & low) >> tz;
+    const uint64_t keep_hi = a.keep_mask >> L, sum_hi = a.sum_mask >> L, fixed_hi = a.fixed_val >> L;
+    const int n_klo = __popcll(keep_lo), n_slo = __popcll(sum_lo), n_khi = __popcll(keep_hi), n_shi = __popcll(sum_hi);
+    const int n_keep = n_klo + n_khi;
+    for (int i = tid; i < (1 << n_klo); i += MARG_THREADS) lut_a[i] = (uint16_t)(deposit_bits((uint64_t)i, keep_lo) | fixed_lo);
+    for (int i = tid; i < (1 << n_slo); i += MARG_THREADS) lut_m[i] = (uint16_t)deposit_bits((uint64_t)i, sum_lo);
+    // Work split of the low bits: with 2^n_klo >= 256 outputs per tile a thread owns outputs
+    // tid, tid + 256, ... and walks all 2^n_slo summed states; with fewer outputs P = 256 / 2^n_klo
+    // adjacent lanes share one output and split the summed states (their partial sums meet in a
+    // shuffle reduction after the last tile, P <= 32).
+    const int n_out = 1 << n_klo;
+    int p_bits = 0;
+    while ((n_out << p_bits) < MARG_THREADS && p_bits < 5 && p_bits < n_slo) ++p_bits;
+    const int P = 1 << p_bits;
+    const int my_part = tid & (P - 1), my_out0 = tid >> p_bits;     // outputs my_out0 + j * (256 / P)
+    const int out_stride = MARG_THREADS >> p_bits;
+    const int m_per = (1 << n_slo) >> p_bits, m0 = my_part * m_per;
+    uint32_t la[MARG_ACC];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < MARG_ACC; ++j) la[j] = lut_a[(my_out0 + j * out_stride) & (n_out - 1)];
+    // persistent CTAs: work item = (vector, high kept bits); the tables above are built once
+    const long long n_work = a.n_vec << n_khi;
+    long long w = blockIdx.x;
+    do {
+    const long long v = w >> n_khi;
+    const uint64_t a_hi = (uint64_t)w & ((1ull << n_khi) - 1ull);
+    const uint64_t x_keep_hi = deposit_bits(a_hi, keep_hi) | fixed_hi;
+    const uint64_t sign = a.sign_masks ? a.sign_masks[v] : 0ull;
+    const uint32_t sign_lo = (uint32_t)(sign & low);
+    const T* src = reinterpret_cast<const T*>(a.in) + (v << a.d);
+    double acc[MARG_ACC];
+#pragma unroll
+    for (int j = 0; j < MARG_ACC; ++j) acc[j] = 0.0;
+    for (long long m_hi = 0; m_hi < (1ll << n_shi); ++m_hi) {
+        const uint64_t x_hi = x_keep_hi | deposit_bits((uint64_t)m_hi, sum_hi);
+        const double hi_sign = (__popcll((long long)((x_hi << L) & sign)) & 1) ? -1.0 : 1.0;
+        const T* t_src = src + (x_hi << L);
+        if ((1 << L) >= VEC * MARG_THREADS) {
+            for (int i = tid * VEC; i < (1 << L); i += VEC * MARG_THREADS) {
+                T e[VEC];
+                *reinterpret_cast<int4*>(e) = __ldcs(reinterpret_cast<const int4*>(t_src + i));
+                double f[VEC];
+#pragma unroll
+                for (int k = 0; k < VEC; ++k)
+                    f[k] = (__popc((uint32_t)(i + k) & sign_lo) & 1) ? -hi_sign * (double)e[k] : hi_sign * (double)e[k];
+                if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
+                else if (tz == 1) {
+#pragma unroll
+                    for (int k = 0; k < VEC; k += 2) tile[(i + k) >> 1] = f[k] + f[k + 1];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) tile[i + k] = f[k];
+                }
+            }
+        } else {                                                   // small vectors: tz = 0 path only
+            for (int i = tid; i < (1 << L); i += MARG_THREADS) {
+                const double f = (__popc((uint32_t)i & sign_lo) & 1) ? -hi_sign * (double)t_src[i] : hi_sign * (double)t_src[i];
+                if (tz == 0) tile[i] = f;
+                else atomicAdd(&tile[i >> tz], f);                 // (never taken: see launch_marginal)
+            }
+        }
+        __syncthreads();
+        for (int m = m0; m < m0 + m_per; ++m) {
+            const uint32_t lm = lut_m[m];
+#pragma unroll
+            for (int j = 0; j < MARG_ACC; ++j)
+                if (my_out0 + j * out_stride < n_out) acc[j] += tile[la[j] | lm];
+        }
+        __syncthreads();
+    }
+    double* dst = a.out + (v << n_keep) + ((long long)a_hi << n_klo);
+#pragma unroll
+    for (int j = 0; j < MARG_ACC; ++j) {
+        double r = acc[j];
+        for (int o = 1; o < P; o <<= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+        if (my_part == 0 && my_out0 + j * out_stride < n_out) dst[my_out0 + j * out_stride] = r;
+    }
+    w += gridDim.x;
+    } while (LOOP && w < n_work);
+    (void)Lt;
+}
+
+// true when the tiled kernel applies (enough index bits for a tile, a launchable grid)
+template <typename T>
+bool launch_marginal(const void* in, double* out, const uint64_t* sign_masks, long long n_vec, int d,
+                     uint64_t keep_mask, uint64_t sum_mask, uint64_t fixed_val, cudaStream_t s) {
+    const int L = d < TILE_BITS ? d : TILE_BITS;
+    if (L < 10) return false;                              // a tile is at least one 16-byte load per thread
+    const int n_khi = __builtin_popcountll(keep_mask >> L);
+    const long long work = n_vec << n_khi;
+    if (work <= 0 || n_khi > 40) return false;
+    // one tile per work item (no high summed bits): a few resident CTAs per SM walk the items, so
+    // the tables and the launch cost are paid once per many tiles; several tiles per item: one CTA
+    // each, the hardware scheduler balances them
+    const int n_shi = __builtin_popcountll(sum_mask >> L);
+    MargArgs a = {in, out, sign_masks, n_vec, d, L, keep_mask, sum_mask, fixed_val};
+    const long long resident = 4ll * qdc_sm_count();
+    if ((n_shi == 0 && work > resident) || work >= (1ll << 31))
+        marginal_kernel<T, true><<<(unsigned)resident, MARG_THREADS, 0, s>>>(a);
+    else
+        marginal_kernel<T, false><<<(unsigned)work, MARG_THREADS, 0, s>>>(a);
+    return true;
+}
+
 // ---- operand gather: A[i][t] = vecs[idx[t]][i]  (idx < 0 or t >= n_terms: 0) ---------------------
 // 32x32 shared-memory transpose so both the vector reads and the operand writes are coalesced.
 __global__ void __launch_bounds__(256) gather_kernel(const double* __restrict__ vecs, long long len,
@@ -169,6 +306,13 @@ extern "C" int qdc_cutqc_measure(const void* d_raw, int dtype, int n_qubits, int
     const int n_eff = __builtin_popcountll(keep_mask);
     const int n_o = n_qubits - n_eff;
     cudaStream_t s = (cudaStream_t)stream;
+    {
+        const uint64_t all = (1ull << n_qubits) - 1ull;
+        const bool done = dtype == 0
+            ? launch_marginal<double>(d_raw, d_out, d_sign_masks, n_inst, n_qubits, keep_mask, all & ~keep_mask, 0ull, s)
+            : launch_marginal<float>(d_raw, d_out, d_sign_masks, n_inst, n_qubits, keep_mask, all & ~keep_mask, 0ull, s);
+        if (done) { QDC_CHECK_LAUNCH(); return QDC_OK; }
+    }
     const long long teams = n_inst << n_eff;
 #define QDC_LAUNCH_MEASURE(T, TEAM)                                                              \
     measure_kernel<T, TEAM><<<grid_for(teams * TEAM, 256), 256, 0, s>>>(                         \
@@ -212,6 +356,10 @@ extern "C" int qdc_cutqc_merge(const double* d_in, int64_t n_vec, int n_effectiv
     const uint64_t merged_mask = all & ~active_mask & ~zoom_mask;
     const int n_active = __builtin_popcountll(active_mask), n_merged = __builtin_popcountll(merged_mask);
     cudaStream_t s = (cudaStream_t)stream;
+    if (launch_marginal<double>(d_in, d_out, nullptr, n_vec, n_effective, active_mask, merged_mask, zoom_val, s)) {
+        QDC_CHECK_LAUNCH();
+        return QDC_OK;
+    }
     const long long teams = n_vec << n_active;
     if (n_merged >= 5)
         merge_kernel<32><<<grid_for(teams * 32, 256), 256, 0, s>>>(d_in, n_effective, n_active, n_merged, n_vec,
