@@ -172,7 +172,8 @@ struct I8Args {
     const double* d_norm;
     MisTables tab;
     CandSink sink;
-    double* P_out;           // optional united slab [n_rows][n_cols]
+    void* P_out;             // optional united slab [n_rows][n_cols], float64 or (out32) float32
+    int out32;
     double* partials;
 };
 
@@ -395,7 +396,12 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
 #pragma unroll
                     for (int c = 0; c < CPT; ++c)
                         if (c0 + c < a.n_cols)
-                            a.P_out[(long long)r_loc * a.n_cols + c0 + c] = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0] * rs;
+                        {
+                            const double p = opaque(X[c]) * ((const volatile double*)(a.colq + c0 + c))[0] * rs;
+                            const long long o = (long long)r_loc * a.n_cols + c0 + c;
+                            if (a.out32) ((float*)a.P_out)[o] = (float)p;
+                            else ((double*)a.P_out)[o] = p;
+                        }
                 }
             }
             // sum p and sum p w do not need the outputs at all (moments_kernel); here only the masked sum
@@ -580,7 +586,8 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     QDC_REQUIRE(n_slices >= 2 && n_slices <= 6, "n_slices in 2..6");
     QDC_REQUIRE(n_rows >= 0 && n_cols >= 1, "shape");
     QDC_REQUIRE(threshold >= 0.0, "candidate threshold must be non-negative");
-    QDC_REQUIRE(store_mode == 0 || (store_mode == 1 && d_P_out), "store_mode 0 (none) or 1 (united slab, float64)");
+    QDC_REQUIRE(store_mode == 0 || ((store_mode == 1 || store_mode == 2) && d_P_out),
+                "store_mode 0 (none), 1 (united slab, float64) or 2 (united slab, float32)");
     if (n_rows == 0) return QDC_OK;
     cudaStream_t s = (cudaStream_t)stream;
     const int kd = (kdim + 31) / 32 * 32;
@@ -617,7 +624,8 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     a.d_norm = d_norm;
     a.tab = {d_row_x, d_row_forb, d_row_wok, d_col_x, d_col_wok};
     a.sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
-    a.P_out = store_mode ? (double*)d_P_out : nullptr;
+    a.P_out = store_mode ? d_P_out : nullptr;
+    a.out32 = store_mode == 2;
     a.partials = d_partials;
     const size_t smem_max = 227 * 1024 - 2048, a_res = (size_t)n_slices * TM * kd, b_slice = (size_t)TN * kd;
     QDC_REQUIRE(a_res + 2 * b_slice <= smem_max, "shared memory");

@@ -102,11 +102,13 @@ def _operand(lib, vecs: torch.Tensor, idx: Sequence[int], kdim: int, sp) -> torc
 
 
 def build(kron: Sequence[torch.Tensor], term_index: Sequence[Sequence[int]], num_cuts: int,
-          out_dtype=torch.float64, stream=None) -> torch.Tensor:
+          out_dtype=torch.float64, stream=None, contraction: Optional[str] = None) -> torch.Tensor:
     """reconstructed = 0.5^num_cuts * sum_t kron(v_0[t], v_1[t], ...)  (cutqc/build.c:69-196).
 
     kron[s]: [n_kron_s, 2^active_s] float64 vectors of subcircuit s, in build order (first =
-    most significant, the reference's `smart_order`); term_index[s][t] = row of kron[s] used by
+    most significant, the reference's `smart_order`); `contraction`: "f64" | "i8[:S]" as in
+    `recombine.resolve_contraction` (None: the QDC_CONTRACTION environment default; the int8
+    kernel needs at most 256 summation terms).  term_index[s][t] = row of kron[s] used by
     summation term t, or -1 when that kron file does not exist (the term is skipped,
     build.c:35-67).  Returns the 2^total_active vector."""
     lib = _lib.load()
@@ -134,7 +136,12 @@ def build(kron: Sequence[torch.Tensor], term_index: Sequence[Sequence[int]], num
         rb = int(A.shape[0]).bit_length() - 1
         cb = int(Bt.shape[0]).bit_length() - 1
         tabs = _rc.build_tables(rb, cb, list(range(rb + cb)), [0] * (rb + cb), 0, device=dev)
+        method, slices = _rc.resolve_contraction(contraction)
+        if method == "i8" and kdim > 256:
+            if contraction is not None:
+                raise _lib.QdcError("contraction='i8' takes at most 256 summation terms")
+            method = "f64"
         res = _rc.contract_and_score(A, Bt, tabs, scale=0.5 ** num_cuts, threshold=float("inf"),
                                      k=1, normalize=False, store="united", out_dtype=out_dtype,
-                                     cand_cap=1, stream=stream)
+                                     cand_cap=1, stream=stream, method=method, slices=slices)
     return res.P.reshape(-1)

@@ -209,7 +209,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                                              _lib.ptr(ws["colsums"]), _lib.ptr(norm), sp),
                        "qdc_contract_norm")
         if method == "i8":
-            assert store_mode in (0, 1) and out_dtype == torch.float64
+            assert store_mode in (0, 1)
+            i8_store = 0 if store_mode == 0 else (1 if out_dtype == torch.float64 else 2)
             ws_bytes = int(lib.qdc_contract_i8_workspace_bytes(n_rows, N, kdim, slices))
             i8ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
             off = (-i8ws.data_ptr()) % 256
@@ -220,7 +221,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
             _lib.check(lib.qdc_contract_i8(
                 _lib.ptr(A), M, _lib.ptr(Bt), row_lo, n_rows, N, kdim, slices, scale, _lib.ptr(norm),
                 threshold, _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
-                _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), store_mode,
+                _lib.ptr(tables.col_x), _lib.ptr(tables.col_wok), _lib.ptr(out), i8_store,
                 C.c_void_p(i8ws.data_ptr() + off), _lib.ptr(sums), _lib.ptr(ws["cand_x"]),
                 _lib.ptr(ws["cand_p"]), _lib.ptr(cand_count), cand_cap, _lib.ptr(ws["partials"]), sp),
                 "qdc_contract_i8")

@@ -207,3 +207,25 @@ def test_kernels_match_float64_formulas(cuda):
             continue
         want += np.kron(np.kron(kron[0][index[0][t]], kron[1][index[1][t]]), kron[2][index[2][t]])
     assert np.abs(got - want / 8).max() < 1e-10
+
+
+@pytest.mark.parametrize("out_dtype", ["f64", "f32"])
+def test_build_int8_contraction_matches_fp64(cuda, out_dtype):
+    """kernels.build through the int8-sliced contraction (contraction="i8:6") against the FP64
+    DMMA kernel: three subcircuits (Khatri-Rao fold), a missing kron file, float64 and float32 out."""
+    import torch
+    from qdc_b200.cutqc import kernels as ck
+    rng = np.random.default_rng(8)
+    K, n_terms = 3, 64
+    actives = (5, 4, 6)
+    kron = [torch.as_tensor(rng.standard_normal((n_terms, 1 << a)) * 10.0 ** rng.uniform(-3, 0, (n_terms, 1)),
+                            device=cuda) for a in actives]
+    idx = [list(range(n_terms)) for _ in actives]
+    idx[1][7] = -1                                         # that summation term is skipped everywhere
+    dt = torch.float64 if out_dtype == "f64" else torch.float32
+    ref = ck.build(kron, idx, K, out_dtype=dt, contraction="f64").cpu().numpy().astype(np.float64)
+    got = ck.build(kron, idx, K, out_dtype=dt, contraction="i8:6").cpu().numpy().astype(np.float64)
+    scale = np.abs(ref).max()
+    tol = 1e-10 * scale if out_dtype == "f64" else 2e-7 * scale
+    assert got.shape == ref.shape == (1 << sum(actives),)
+    assert np.abs(got - ref).max() <= tol, np.abs(got - ref).max() / scale
