@@ -249,3 +249,44 @@ def test_int8_contraction_row_slabs_and_given_norm(cuda):
     merged = qdist.merge_topk(cands, 8)
     assert [x for x, _ in merged] == [x for x, _ in full["top"]]
     assert all(abs(p - q) < 1e-15 for (_, p), (_, q) in zip(merged, full["top"]))
+
+
+@pytest.mark.parametrize("M,N,kdim,slices", [
+    (20000, 200, 32, 6),     # more row blocks than SMs: CTAs take several work items; all slices fit in TMEM
+    (19500, 130, 64, 5),
+    (300, 9000, 256, 6),     # few row blocks, many column blocks: the column walk is split into chunks
+    (129, 66, 256, 2),       # one row and two columns past a tile edge (the FP64 kernel wants an even column count)
+    (1000, 1000, 128, 3),
+    (37, 5000, 16, 4),
+])
+def test_int8_contraction_shapes(cuda, M, N, kdim, slices):
+    """Work-item scheduling, TMEM-resident slices and ragged edges of qdc_contract_i8 on shapes that
+    the power-of-two configs never produce, against the FP64 kernel (sums within the stated bound,
+    same candidates)."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rng = np.random.default_rng(M + N + kdim)
+    A = rng.random((M, kdim)) * 10.0 ** rng.uniform(-3, 0, (M, 1))
+    Bt = rng.random((N, kdim)) * 10.0 ** rng.uniform(-3, 0, (N, 1))
+    f64 = dict(dtype=torch.float64, device=cuda)
+    # tables by hand: arbitrary 40-bit "bitstrings", a third of the rows / columns not independent
+    row_x = torch.as_tensor(rng.integers(0, 1 << 20, M) << 20, device=cuda)
+    col_x = torch.as_tensor(rng.integers(0, 1 << 20, N), device=cuda)
+    row_forb = torch.as_tensor(rng.integers(0, 1 << 20, M) & rng.integers(0, 1 << 20, M), device=cuda)
+    row_wok = torch.as_tensor((rng.integers(0, 20, M) | ((rng.random(M) > 0.33).astype(np.int64) << 8)).astype(np.int32), device=cuda)
+    col_wok = torch.as_tensor((rng.integers(0, 20, N) | ((rng.random(N) > 0.33).astype(np.int64) << 8)).astype(np.int32), device=cuda)
+    tabs = rc.MisTables(20, 20, row_x, row_forb, row_wok, col_x, col_wok, tuple(range(40)), (1 << 40) - 1)
+    A_d, B_d = torch.as_tensor(A, **f64), torch.as_tensor(Bt, **f64)
+    want = A @ Bt.T
+    top13 = np.sort(np.partition(want.reshape(-1), -13)[-13:])
+    thr = float(0.5 * (top13[0] + top13[1])) / want.sum()                   # 12 candidates, none on the edge
+    ref = rc.contract_and_score(rc.pad_kdim(A_d), rc.pad_kdim(B_d), tabs, threshold=thr, k=6).get()
+    got = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=6, method="i8", slices=slices).get()
+    ea = np.floor(np.log2(A.max(axis=1)))[:, None] + 2
+    fb = np.floor(np.log2(Bt.max(axis=1)))[None, :] + 2
+    bound = float((2.0 ** (ea + fb)).sum()) * kdim * (slices + 1.1) * 2.0 ** (-8 * slices) / want.sum() * 40
+    for key in ("sum_p", "sum_pw", "sum_pw_indset"):
+        assert abs(got[key] - ref[key]) <= bound + 1e-12, (key, got[key], ref[key], bound)
+    if slices >= 5:
+        assert got["n_candidates"] == ref["n_candidates"]
+        assert [x for x, _ in got["top"]] == [x for x, _ in ref["top"]]
