@@ -21,8 +21,9 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint
 
 // mode 0: correctness (one pass, results written); mode 1: timing of `iters` x 8 MMAs with A in TMEM;
 // mode 2: the same with A from shared memory
+template <int mode>
 __global__ void __launch_bounds__(128) probe(const int8_t* __restrict__ A, const int8_t* __restrict__ B,
-                                             int32_t* __restrict__ D, int mode, int iters, long long* cyc) {
+                                             int32_t* __restrict__ D, int iters, long long* cyc) {
     extern __shared__ __align__(1024) int8_t dyn[];
     int8_t* sA = dyn;
     int8_t* sB = dyn + M * K;
@@ -106,9 +107,11 @@ int main() {
     cudaMalloc(&dA, M * K); cudaMalloc(&dB, N * K); cudaMalloc(&dD, M * N * 4); cudaMalloc(&dC, 148 * 8);
     cudaMemcpy(dA, ap.data(), M * K, cudaMemcpyHostToDevice);
     cudaMemcpy(dB, bp.data(), N * K, cudaMemcpyHostToDevice);
-    cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (M + N) * K);
+    cudaFuncSetAttribute(probe<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (M + N) * K);
+    cudaFuncSetAttribute(probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (M + N) * K);
+    cudaFuncSetAttribute(probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (M + N) * K);
     cudaMemset(dD, 0xff, M * N * 4);
-    probe<<<1, 128, (M + N) * K>>>(dA, dB, dD, 0, 1, nullptr);
+    probe<0><<<1, 128, (M + N) * K>>>(dA, dB, dD, 1, nullptr);
     cudaError_t e = cudaDeviceSynchronize();
     std::vector<int32_t> got(M * N);
     cudaMemcpy(got.data(), dD, M * N * 4, cudaMemcpyDeviceToHost);
@@ -118,7 +121,8 @@ int main() {
            bad, M * N, got[0], got[1], got[N], want[0], want[1], want[N]);
     for (int mode = 1; mode <= 2; ++mode) {
         const int iters = 2048;
-        probe<<<148, 128, (M + N) * K>>>(dA, dB, dD, mode, iters, dC);
+        if (mode == 1) probe<1><<<148, 128, (M + N) * K>>>(dA, dB, dD, iters, dC);
+        else probe<2><<<148, 128, (M + N) * K>>>(dA, dB, dD, iters, dC);
         e = cudaDeviceSynchronize();
         long long h[148];
         cudaMemcpy(h, dC, sizeof(h), cudaMemcpyDeviceToHost);
