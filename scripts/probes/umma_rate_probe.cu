@@ -112,7 +112,7 @@ void run(const char* name, int N, int swz, int n_acc, int grid) {
 int main() {
     for (int grid : {1, 148}) {
         for (int swz = 0; swz < 2; ++swz)
-            for (int N : {64, 128, 256}) {
+            for (int N : {64, 80, 96, 112, 128, 256}) {
                 run<0>("i8", N, swz, 1, grid);
                 run<1>("f8f6f4", N, swz, 1, grid);
                 run<2>("f16", N, swz, 1, grid);
