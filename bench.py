@@ -54,10 +54,16 @@ def parse_args():
     ap.add_argument("--method", default="i8", choices=["i8", "f64"],
                     help="contraction kernel: i8 = radix-256 slices on tcgen05 int8 tensor cores "
                          "(stated error bound), f64 = FP64 DMMA")
-    ap.add_argument("--slices", type=int, default=6,
-                    help="slices per operand of the i8 method (6: 48-bit operands, bound 6.5e-12 x "
-                         "row/column scale; 5: 40-bit, 1.4e-9)")
-    return ap.parse_args()
+    ap.add_argument("--slices", default="auto",
+                    help="slices per operand of the i8 method: 2..6 (6: 48-bit operands, bound 6.5e-12 x "
+                         "row/column scale; 5: 40-bit, 1.4e-9) or auto = the smallest count whose "
+                         "a-posteriori bounds for these operands (per output and on the MIS cost, "
+                         "recombine.i8_error_bounds) stay below --tol")
+    ap.add_argument("--tol", type=float, default=1e-10)
+    args = ap.parse_args()
+    if args.slices != "auto":
+        args.slices = int(args.slices)
+    return args
 
 
 # ---------------------------------------------------------------------------------------------
@@ -342,12 +348,20 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     kernel_events = []
+    chosen = {}                        # slice count and bounds of the last i8 call (slices = auto)
+    tol = args.tol / ws                # every rank keeps its share of the cost error below tol / N
+
+    def note(res):
+        if res.slices is not None:
+            chosen["slices"] = res.slices
+            chosen["bounds"] = res.error_bound
+        return res
 
     def step_device():
         # inputs resident in HBM (row-major); packing for the bulk-copy pipeline is part of the step
-        res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
-                                    row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
-                                    method=args.method, slices=args.slices)
+        res = note(rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
+                                         row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
+                                         method=args.method, slices=args.slices, tol=tol))
         return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
 
     def step_e2e():
@@ -355,7 +369,7 @@ def run_b200(args):
         Bt_stage.copy_(Bt_pin, non_blocking=True)
         norm = qdist.sharded_norm(A_stage, Bt_stage, scale) if ws > 1 else None
         res = rc.contract_and_score(A_stage, Bt_stage, tabs_slab, scale=scale, threshold=1e-5, k=k,
-                                    method=args.method, slices=args.slices, norm=norm)
+                                    method=args.method, slices=args.slices, norm=norm, tol=tol)
         if ws > 1:
             sums, top = qdist.finish(res.sums, res.top_x, res.top_p, k)
             return sums.cpu().numpy(), top
@@ -417,7 +431,8 @@ def run_b200(args):
     t_kernel = float(np.mean([a.elapsed_time(b) for a, b in evs])) * 1e-3
     if args.method == "i8":
         # every one of the S (S + 1) / 2 slice pairs is a full int8 GEMM of the same shape
-        pairs = args.slices * (args.slices + 1) // 2
+        n_sl = chosen.get("slices", args.slices)
+        pairs = n_sl * (n_sl + 1) // 2
         int8_ops = flops * pairs / ws
         peaks = measured_peaks()
         bf16 = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
@@ -432,12 +447,13 @@ def run_b200(args):
                                     "2.52 at the N=64 instruction this kernel issues)") if bf16 else
                                    "nominal 4.5 POP/s dense int8 (MEASURED_PEAKS.json absent)",
                     "algorithmic_ops_per_launch": int8_ops,
-                    "algorithmic_ops_note": f"2 x outputs x kdim x {pairs} slice pairs (S = {args.slices})",
+                    "algorithmic_ops_note": f"2 x outputs x kdim x {pairs} slice pairs (S = {n_sl})",
                     "fp64_equivalent_tflops": flops / ws / t_kernel / 1e12,
                     "fp64_pipe_peak_tflops": dgemm_peak,
-                    "kernel": f"contract_i8_kernel<{args.slices}> (+ slice / column-table / moments kernels)",
+                    "kernel": f"contract_i8_kernel<{n_sl}> (+ slice / column-table / moments kernels)",
+                    "slices": n_sl, "slices_chosen_by": chosen.get("bounds") if args.slices == "auto" else "command line",
                     "kernel_ms": t_kernel * 1e3}
-        dtype = f"i8 x {args.slices} slices (Ozaki split of FP64 operands, int32 accumulation, FP64 fold)"
+        dtype = f"i8 x {n_sl} slices (Ozaki split of FP64 operands, int32 accumulation, FP64 fold)"
         launches = 11 * args.steps
     else:
         achieved = flops / ws / t_kernel / 1e12
@@ -457,7 +473,7 @@ def run_b200(args):
         "config": {"workload": f"C4 synthetic 2-fragment 17+17-qubit K=4 recombination + MIS "
                                f"scoring, 2^{n} outputs (BASELINE.json configs[3])",
                    "row_bits": rb, "col_bits": cb, "kdim": KDIM, "topk": k,
-                   "method": args.method, "slices": args.slices if args.method == "i8" else None,
+                   "method": args.method, "slices": args.slices if args.method == "i8" else None, "tol": args.tol,
                    "parallelism": f"prefix-shard x{ws}",
                    "l2": "operands 0.5 GB > 126 MB L2; no flush needed"},
         "clocks": clocks,

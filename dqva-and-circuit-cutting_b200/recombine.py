@@ -80,6 +80,8 @@ class ScoreResult:
     cand_cap: int
     P: Optional[torch.Tensor] = None
     norm: Optional[torch.Tensor] = None
+    slices: Optional[int] = None            # int8 method: slices used
+    error_bound: Optional[dict] = None      # int8 method with slices="auto": the bounds that picked it
 
     def get(self):
         sums = self.sums.cpu().numpy()
@@ -127,18 +129,53 @@ class _Workspace:
 
 
 def resolve_contraction(spec: Optional[str]):
-    """"f64" | "i8" | "i8:S" (S slices, 2..6) -> (method, slices).  None reads the environment
+    """"f64" | "i8" | "i8:S" (S slices, 2..6) | "i8:auto" (slice count from the a-posteriori error
+    bounds, see contract_and_score) -> (method, slices).  None reads the environment
     variable QDC_CONTRACTION (default "f64": FP64 DMMA, no approximation of any kind)."""
     if spec is None:
         spec = os.environ.get("QDC_CONTRACTION", "f64")
     if spec == "f64":
         return "f64", 6
     if spec.startswith("i8"):
+        if spec == "i8:auto":
+            return "i8", "auto"
         slices = int(spec[3:]) if len(spec) > 2 else 6
         if spec[2:3] not in ("", ":") or not 2 <= slices <= 6:
             raise ValueError(f"contraction {spec!r}: expected 'i8' or 'i8:S' with S in 2..6")
         return "i8", slices
     raise ValueError(f"contraction {spec!r} not recognized ('f64', 'i8', 'i8:S')")
+
+
+def i8_error_bounds(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, scale: float,
+                    norm: Optional[torch.Tensor], row_lo: int = 0, n_rows: Optional[int] = None):
+    """A-posteriori bounds of the int8-sliced contraction for THESE operands, per slice count.
+
+    Per output |err| <= 2^(e_r + f_c) * scale / norm * kdim * (S + 1.1) * 2^(-8 S) (include/qdc_b200.h;
+    2^e_r, 2^f_c: power-of-two ceilings of the row maxima, one more factor 2 each for the kernel's
+    exponent bump).  The MIS cost only sums outputs whose row and column are themselves independent
+    sets, each weighted by at most the number of graph nodes, so
+        |cost error| <= n_nodes * (sum_{r ok} 2^e_r) * (sum_{c ok} 2^f_c) * scale / norm * kdim * (S + 1.1) * 2^(-8 S)
+    (the edges between the fragments are ignored: an upper bound).  One pass over the operands and
+    one host sync.  Returns {S: {"per_output": ..., "cost": ...}} for S = 2..6."""
+    if n_rows is None:
+        n_rows = A.shape[0] - row_lo
+    kdim = A.shape[1]
+    a_slab = A[row_lo:row_lo + n_rows]
+    a_mx, b_mx = a_slab.abs().amax(dim=1), Bt.abs().amax(dim=1)
+    ea = torch.where(a_mx > 0, torch.ldexp(torch.ones_like(a_mx), torch.frexp(a_mx)[1] + 1), torch.zeros_like(a_mx))
+    fb = torch.where(b_mx > 0, torch.ldexp(torch.ones_like(b_mx), torch.frexp(b_mx)[1] + 1), torch.zeros_like(b_mx))
+    r_ok = ((tables.row_wok[row_lo:row_lo + n_rows] >> 8) & 1).to(torch.float64)
+    c_ok = ((tables.col_wok >> 8) & 1).to(torch.float64)
+    f = torch.full((), float(scale), dtype=torch.float64, device=A.device)
+    if norm is not None:
+        f = f / norm.reshape(()).abs()
+    stats = torch.stack([ea.max() * fb.max() * f, (ea * r_ok).sum() * (fb * c_ok).sum() * f]).cpu().tolist()
+    n_nodes = bin(int(tables.node_mask)).count("1")
+    out = {}
+    for S in range(2, 7):
+        g = kdim * (S + 1.1) * 2.0 ** (-8 * S)
+        out[S] = {"per_output": stats[0] * g, "cost": stats[1] * g * n_nodes}
+    return out
 
 
 def _default_cap(total: int, threshold: float) -> int:
@@ -156,7 +193,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                        out: Optional[torch.Tensor] = None, cand_cap: Optional[int] = None,
                        stream=None, kernel_events: Optional[list] = None,
                        packed_cache: Optional[dict] = None, method: str = "f64",
-                       slices: int = 6, norm: Optional[torch.Tensor] = None) -> ScoreResult:
+                       slices=6, norm: Optional[torch.Tensor] = None, tol: float = 1e-10) -> ScoreResult:
     """P~ = scale * A @ Bt.T over rows [row_lo, row_lo + n_rows) of A, scored on the fly.
 
     A: [2^row_bits, kdim] float64 cuda, Bt: [2^col_bits, kdim]; kdim % 16 == 0 (see pad_kdim).
@@ -168,6 +205,8 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
     unchanged are not re-packed (the kernel reads the k-group-major packed copies).
     norm: a 1-element float64 device tensor to divide by instead of the total of THIS call's
     operands (a rank that holds only its row slab passes `dist.sharded_norm`).
+    slices: 2..6, or "auto" = the smallest count whose a-posteriori bounds (`i8_error_bounds`: per
+    output and on the MIS cost) are both below `tol` for these operands (6 if none is).
     method: "f64" (FP64 DMMA, `qdc_contract_f64`) or "i8" (exact 7-bit slicing on the tcgen05 int8
     tensor cores, `qdc_contract_i8`, `slices` slices per operand; kdim <= 256, store None or
     "united"; error bound in include/qdc_b200.h).
@@ -211,6 +250,12 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
         if method == "i8":
             assert store_mode in (0, 1)
             i8_store = 0 if store_mode == 0 else (1 if out_dtype == torch.float64 else 2)
+            bounds = None
+            if slices == "auto":
+                bounds = i8_error_bounds(A, Bt, tables, scale, norm if (normalize or given_norm) else None,
+                                         row_lo, n_rows)
+                slices = next((S for S in range(3, 7) if max(bounds[S].values()) <= tol), 6)
+                bounds = {"slices": slices, "tol": tol, **bounds[slices]}
             ws_bytes = int(lib.qdc_contract_i8_workspace_bytes(n_rows, N, kdim, slices))
             i8ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
             off = (-i8ws.data_ptr()) % 256
@@ -229,7 +274,7 @@ def contract_and_score(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, sca
                 ev1.record(stream)
                 kernel_events.append((ev0, ev1))
             _select_topk(lib, ws, cand_count, cand_cap, k, top_x, top_p, sp)
-            return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm)
+            return ScoreResult(sums, top_x, top_p, cand_count, cand_cap, out, norm, slices, bounds)
         Ap = _packed(lib, A, sp, packed_cache)
         Bp = _packed(lib, Bt, sp, packed_cache)
         if kernel_events is not None:

@@ -232,7 +232,8 @@ int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_B
  * exactly in int32 and combined by FP64 FMAs.  Error bound (stated, not measured):
  * |P~ - P~_exact| <= 2^(e_r + f_c) * scale * kdim * (n_slices + 1.1) * 2^(-8 n_slices), 2^e_r / 2^f_c
  * = power-of-two ceilings of the row maxima; kdim = 256: 1.4e-9 (5 slices), 6.5e-12 (6 slices)
- * times 2^(e_r + f_c) * scale -- FP64 accumulation itself: 2.8e-14.  Operands are ROW-MAJOR here
+ * times 2^(e_r + f_c) * scale -- FP64 accumulation itself: 2.8e-14.  (The Python wrapper can pick
+ * n_slices from these bounds evaluated on the actual operands: recombine.i8_error_bounds.)  Operands are ROW-MAJOR here
  * (d_A: [a_rows_total][kdim], d_Bt: [n_cols][kdim]); slicing is part of the call.  kdim <= 256,
  * n_slices 2..6, threshold >= 0.  store_mode 0, 1 = united slab float64, 2 = united slab float32.  d_workspace:
  * 256-byte aligned, qdc_contract_i8_workspace_bytes(n_rows, n_cols, kdim, n_slices) bytes. */

@@ -290,3 +290,36 @@ def test_int8_contraction_shapes(cuda, M, N, kdim, slices):
     if slices >= 5:
         assert got["n_candidates"] == ref["n_candidates"]
         assert [x for x, _ in got["top"]] == [x for x, _ in ref["top"]]
+
+
+@pytest.mark.parametrize("tol,spread", [(1e-10, 0), (1e-6, 0), (1e-10, 8), (1e-14, 0)])
+def test_int8_auto_slices_keeps_its_bounds(cuda, tol, spread):
+    """slices="auto": the chosen count's a-posteriori bounds (recombine.i8_error_bounds) are below
+    tol unless even 6 slices cannot do it, one slice fewer would violate them, and the measured
+    differences from the FP64 kernel stay inside the bounds."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rb, cb, kdim = 9, 8, 64
+    rng = np.random.default_rng(int(-np.log10(tol)) + spread)
+    M, N = 1 << rb, 1 << cb
+    A = rng.random((M, kdim)) * 10.0 ** rng.uniform(-spread, 0, (M, 1))
+    Bt = rng.random((N, kdim)) * 10.0 ** rng.uniform(-spread, 0, (N, 1))
+    G = __import__("networkx").gnm_random_graph(rb + cb, 20, seed=5)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    A_d, B_d = torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda)
+    res = rc.contract_and_score(A_d, B_d, tabs, scale=0.25, k=4, method="i8", slices="auto", tol=tol,
+                                store="united")
+    ref = rc.contract_and_score(A_d, B_d, tabs, scale=0.25, k=4, store="united")
+    S, eb = res.slices, res.error_bound
+    assert 3 <= S <= 6 and eb["slices"] == S
+    all_bounds = rc.i8_error_bounds(A_d, B_d, tabs, 0.25, ref.norm)
+    assert abs(all_bounds[S]["cost"] - eb["cost"]) <= 1e-12 * eb["cost"]
+    if S < 6 or max(all_bounds[6].values()) <= tol:
+        assert eb["per_output"] <= tol and eb["cost"] <= tol
+    if S > 3:
+        assert max(all_bounds[S - 1].values()) > tol
+    got, want = res.get(), ref.get()
+    fp64_noise = 1e-13
+    assert abs(got["sum_pw_indset"] - want["sum_pw_indset"]) <= eb["cost"] + fp64_noise
+    assert float((res.P - ref.P).abs().max()) <= eb["per_output"] + fp64_noise

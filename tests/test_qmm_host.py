@@ -112,3 +112,23 @@ def test_contraction_spec_parsing(monkeypatch):
     for bad in ("i8:7", "i8:1", "i8x", "tf32", ""):
         with pytest.raises(ValueError):
             rc.resolve_contraction(bad)
+
+
+def test_i8_error_bounds_formula():
+    """recombine.i8_error_bounds on the CPU (pure torch): the per-output bound is
+    2^(e_r + f_c) scale / norm kdim (S + 1.1) 2^(-8S) at the largest rows, the cost bound only
+    counts rows / columns that are independent sets themselves, both shrink 256-fold per slice."""
+    from qdc_b200 import recombine as rc
+    A = torch.tensor([[0.3, -0.7, 0.0, 0.1], [0.01, 0.02, 0.0, 0.0], [0.0, 0.0, 0.0, 0.0]], dtype=torch.float64)
+    Bt = torch.tensor([[1.5, 0.0, 0.0, 0.2], [0.2, 0.1, 0.0, 0.0]], dtype=torch.float64)
+    row_wok = torch.tensor([256 | 2, 1, 256], dtype=torch.int32)      # rows 0 and 2 independent
+    col_wok = torch.tensor([256 | 1, 256], dtype=torch.int32)
+    tabs = rc.MisTables(2, 1, None, None, row_wok, None, col_wok, (0, 1, 2), 0b111)
+    norm = torch.tensor([2.0], dtype=torch.float64)
+    b = rc.i8_error_bounds(A, Bt, tabs, 0.5, norm)
+    g5 = 4 * 6.1 * 2.0 ** -40
+    # power-of-two ceilings with the bump: 0.7 -> 2, 0.02 -> 1/16, 1.5 -> 4, 0.2 -> 1/2
+    assert abs(b[5]["per_output"] - 2 * 4 * 0.25 * g5) < 1e-25
+    assert abs(b[5]["cost"] - 3 * (2 + 0) * (4 + 0.5) * 0.25 * g5) < 1e-25
+    assert abs(b[4]["cost"] / b[5]["cost"] - 256 * 5.1 / 6.1) < 1e-9
+    assert set(b) == {2, 3, 4, 5, 6}
