@@ -454,7 +454,8 @@ def run_b200(args):
                     "slices": n_sl, "slices_chosen_by": chosen.get("bounds") if args.slices == "auto" else "command line",
                     "kernel_ms": t_kernel * 1e3}
         dtype = f"i8 x {n_sl} slices (Ozaki split of FP64 operands, int32 accumulation, FP64 fold)"
-        launches = 11 * args.steps
+        launches = 12 * args.steps        # colsum x2, norm_finalize, slice x2, coltab, contract_i8, finalize_sums,
+                                          # moments x2, moments_finish, topk (profiles/r1_launches_i8.csv)
     else:
         achieved = flops / ws / t_kernel / 1e12
         roofline = {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,

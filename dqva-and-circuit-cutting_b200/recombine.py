@@ -161,7 +161,8 @@ def i8_error_bounds(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, scale:
         n_rows = A.shape[0] - row_lo
     kdim = A.shape[1]
     a_slab = A[row_lo:row_lo + n_rows]
-    a_mx, b_mx = a_slab.abs().amax(dim=1), Bt.abs().amax(dim=1)
+    inf = float("inf")                                   # one fused pass each, no |A| temporary
+    a_mx, b_mx = torch.linalg.vector_norm(a_slab, ord=inf, dim=1), torch.linalg.vector_norm(Bt, ord=inf, dim=1)
     ea = torch.where(a_mx > 0, torch.ldexp(torch.ones_like(a_mx), torch.frexp(a_mx)[1] + 1), torch.zeros_like(a_mx))
     fb = torch.where(b_mx > 0, torch.ldexp(torch.ones_like(b_mx), torch.frexp(b_mx)[1] + 1), torch.zeros_like(b_mx))
     r_ok = ((tables.row_wok[row_lo:row_lo + n_rows] >> 8) & 1).to(torch.float64)
