@@ -19,7 +19,8 @@
 // block stay resident in shared memory (S = 6, kdim = 256: 192 KB, which leaves a 2-stage ring for
 // the streamed operand; S = 5: 4 stages).
 //
-// Structure (one persistent CTA per SM, 10 warps):
+// Structure (one persistent CTA per SM; tile = 128 rows x TN columns, TN = 64, or 96 at S = 5 where
+// 5 x 96 accumulator columns fit TMEM -- an N = 96 instruction costs what N = 64 does; 2 + TN / 4 warps):
 //   warp 0  producer: bulk async copies (cp.async.bulk + mbarrier complete_tx).  The S slices of
 //           a 128-row block of A (S * 128 * kdim bytes) are loaded once and stay resident while
 //           the CTA walks all column blocks; the slices t_j of a 64-column block stream through a
@@ -31,7 +32,7 @@
 //           copied to the TMEM columns the accumulators leave free (tcgen05.cp.128x256b) at the
 //           start of a work item; their pairs take A from tensor memory and read only the B tile
 //           from shared memory (the N = 64 instruction is bound by the 6 KB operand read).
-//   warps 2-9  epilogue: tcgen05.ld two finished orders at a time, X = fma(X, 256, D_d) in FP64
+//   warps 2..  epilogue (4 TMEM lane quarters x TN / 16 column groups of 16): tcgen05.ld two finished orders at a time, X = fma(X, 256, D_d) in FP64
 //           (int32 -> FP64 through the 2^52 trick, no conversion unit), release the
 //           accumulators; then, branch-free per output:
 //           q = X cs_c, four running sums per row (sum q, sum q w_c, both again under the
@@ -44,13 +45,12 @@
 
 namespace {
 
-constexpr int TM = 128, TN = 64;
+constexpr int TM = 128;                       // tile rows; tile columns TN and columns per epilogue thread CPT are
+                                              // template parameters of the kernel: (64, 16), or (96, 32) where S * 96 <= 512
 constexpr int MAX_S = 6;
 constexpr int MAX_STAGES = 8;                 // ring of streamed-operand slices
-constexpr int CPT = 16;                       // accumulator columns per epilogue thread
-constexpr int N_EPI_WARPS = 4 * (TN / CPT);
 constexpr int FIRST_EPI_WARP = 2;             // warp 0: producer, warp 1: MMA issuer
-constexpr int THREADS = (FIRST_EPI_WARP + N_EPI_WARPS) * 32;
+constexpr int MAX_WARPS = 32;
 constexpr int TMEM_COLS = 512;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -178,13 +178,14 @@ struct I8Args {
 };
 
 // S = number of slices per operand (compile time: every loop over slice pairs and orders unrolls)
-template <int S>
-__global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a) {
+template <int S, int TN, int CPT>
+__global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) contract_i8_kernel(const I8Args a) {
+    constexpr int N_EPI_WARPS = 4 * (TN / CPT);
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t a_full, a_empty, b_full[MAX_STAGES], b_empty[MAX_STAGES],
         acc_full[MAX_S], acc_empty[MAX_S];
     __shared__ uint32_t tmem_base_sh;
-    __shared__ double scratch[3 * (THREADS / 32)];
+    __shared__ double scratch[3 * MAX_WARPS];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int kdim = a.kdim;
@@ -346,6 +347,7 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                     const bool two = d + 1 < S;
                     mbar_wait_relaxed(&acc_full[two ? d + 1 : d], tile_phase, 32);
                     tc_fence_after();
+                    if constexpr (CPT == 16) {
                     uint32_t v0[CPT], v1[CPT];
                     tmem_ld(lane_base + (uint32_t)(d * TN), v0);
                     if (two) tmem_ld(lane_base + (uint32_t)((d + 1) * TN), v1);
@@ -364,6 +366,31 @@ __global__ void __launch_bounds__(THREADS, 1) contract_i8_kernel(const I8Args a)
                             X[c] = fma(X[c], 65536.0, i64_to_f64((long long)(int32_t)v0[c] * 256 + (long long)(int32_t)v1[c]));
                         else
                             X[c] = fma(X[c], 256.0, i32_to_f64((int32_t)v0[c]));
+                    }
+                    } else {                                       // 16 columns at a time (registers)
+#pragma unroll
+                    for (int h = 0; h < CPT / 16; ++h) {
+                        uint32_t v0[16], v1[16];
+                        tmem_ld(lane_base + (uint32_t)(d * TN + h * 16), v0);
+                        if (two) tmem_ld(lane_base + (uint32_t)((d + 1) * TN + h * 16), v1);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) {
+                            double& x = X[h * 16 + c];
+                            if (d == 0)
+                                x = i32_to_f64(two ? (int32_t)v0[c] * 256 + (int32_t)v1[c] : (int32_t)v0[c]);
+                            else if (two)
+                                x = fma(x, 65536.0, i64_to_f64((long long)(int32_t)v0[c] * 256 + (long long)(int32_t)v1[c]));
+                            else
+                                x = fma(x, 256.0, i32_to_f64((int32_t)v0[c]));
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive(&acc_empty[d]);
+                        if (two) mbar_arrive(&acc_empty[d + 1]);
+                    }
                     }
                 }
                 const int c0 = cb * TN + part * CPT;
@@ -553,17 +580,27 @@ __global__ void __launch_bounds__(256) moments_finish_kernel(const double* __res
 
 }  // namespace
 
-template <int S>
+template <int S, int TN, int CPT>
 int launch_i8(const I8Args& a, int grid, size_t smem, cudaStream_t s) {
-    QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    contract_i8_kernel<S><<<grid, THREADS, smem, s>>>(a);
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel<S, TN, CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    contract_i8_kernel<S, TN, CPT><<<grid, (FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, smem, s>>>(a);
     QDC_CHECK_LAUNCH();
     return QDC_OK;
+}
+
+// tile width: 96 columns where the S accumulators of 96 columns fit the 512 of TMEM and two stages of
+// the streamed operand fit beside the resident slices (an N = 96 instruction costs what N = 64 does)
+static int i8_tile_n(int n_slices, int kd) {
+    const char* m = getenv("QDC_I8_TN");
+    if (m && atoi(m) == 64) return 64;
+    if (n_slices == 5 && (size_t)n_slices * TM * kd + 2 * (size_t)96 * kd <= 227 * 1024 - 2048) return 96;
+    return 64;
 }
 
 extern "C" int64_t qdc_contract_i8_workspace_bytes(int64_t n_rows, int64_t n_cols, int kdim, int n_slices) {
     if (n_rows < 0 || n_cols < 0 || kdim < 1 || n_slices < 1) return 0;
     const int64_t kd = (kdim + 31) / 32 * 32;
+    const int64_t TN = i8_tile_n(n_slices, (int)kd);
     const int64_t rb = (n_rows + TM - 1) / TM, cb = (n_cols + TN - 1) / TN;
     const int64_t a8 = (rb * TM * kd * n_slices + 255) / 256 * 256, b8 = (cb * TN * kd * n_slices + 255) / 256 * 256;
     return a8 + b8 + rb * TM * 8 + cb * TN * 32 + 2 * 296 * 2 * 256 * 8 + 256;
@@ -591,6 +628,7 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     if (n_rows == 0) return QDC_OK;
     cudaStream_t s = (cudaStream_t)stream;
     const int kd = (kdim + 31) / 32 * 32;
+    const int TN = i8_tile_n(n_slices, kd);
     const long long n_rb = (n_rows + TM - 1) / TM, n_cb = (n_cols + TN - 1) / TN;
     QDC_REQUIRE(n_rb < (1ll << 31) && n_cb < (1ll << 31), "too many tiles");
     uint8_t* ws = (uint8_t*)d_workspace;
@@ -655,11 +693,11 @@ extern "C" int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const do
     const int grid = (int)(n_items < sms ? n_items : sms);
     int rc = QDC_ERR_ARG;
     switch (n_slices) {
-        case 2: rc = launch_i8<2>(a, grid, smem, s); break;
-        case 3: rc = launch_i8<3>(a, grid, smem, s); break;
-        case 4: rc = launch_i8<4>(a, grid, smem, s); break;
-        case 5: rc = launch_i8<5>(a, grid, smem, s); break;
-        case 6: rc = launch_i8<6>(a, grid, smem, s); break;
+        case 2: rc = launch_i8<2, 64, 16>(a, grid, smem, s); break;
+        case 3: rc = launch_i8<3, 64, 16>(a, grid, smem, s); break;
+        case 4: rc = launch_i8<4, 64, 16>(a, grid, smem, s); break;
+        case 5: rc = TN == 96 ? launch_i8<5, 96, 16>(a, grid, smem, s) : launch_i8<5, 64, 16>(a, grid, smem, s); break;
+        case 6: rc = launch_i8<6, 64, 16>(a, grid, smem, s); break;
     }
     if (rc != QDC_OK) return rc;
     rc = qdc_launch_finalize_sums(d_partials, grid, d_sums, s);     // the masked sum (slots 0, 2 are zero)
