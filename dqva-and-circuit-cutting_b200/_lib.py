@@ -50,10 +50,14 @@ SIGNATURES = {
                                    vp, vp, vp, vp, c_i64, vp, vp]),
     "qdc_penalty_workspace_bytes": (C.c_int, []),
     "qdc_penalty_reduce": (C.c_int, [vp, C.c_int, C.c_int, C.c_uint64, vp, C.c_int, C.c_uint64, vp, vp, vp, vp]),
-    "qdc_contract_i8_workspace_bytes": (c_i64, [c_i64, c_i64, C.c_int, C.c_int]),
-    "qdc_contract_i8": (C.c_int, [vp, c_i64, vp, c_i64, c_i64, c_i64, C.c_int, C.c_int, C.c_double, vp,
-                                  C.c_double, vp, vp, vp, vp, vp, vp, C.c_int, vp,
-                                  vp, vp, vp, vp, c_i64, vp, vp]),
+    "qdc_i8_operand_bytes": (c_i64, [c_i64, C.c_int, C.c_int]),
+    "qdc_i8_prepare": (C.c_int, [vp, c_i64, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
+    "qdc_colsum_partials": (C.c_int, []),
+    "qdc_colsum": (C.c_int, [vp, c_i64, c_i64, c_i64, c_i64, C.c_int, vp, vp]),
+    "qdc_contract_i8_prepared": (C.c_int, [vp, c_i64, vp, c_i64, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int,
+                                           C.c_double, C.c_int, vp, vp, C.c_int, C.c_double,
+                                           vp, vp, c_i64, vp, vp, vp, vp, C.c_int,
+                                           vp, vp, vp, c_i64, C.c_int, vp, vp, vp, vp]),
     "qdc_cutqc_measure": (C.c_int, [vp, C.c_int, C.c_int, c_i64, C.c_uint64, vp, vp, vp]),
     "qdc_cutqc_collapse": (C.c_int, [vp, c_i64, C.c_int, vp, vp, vp, vp, vp, vp]),
     "qdc_cutqc_merge": (C.c_int, [vp, c_i64, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, vp, vp]),

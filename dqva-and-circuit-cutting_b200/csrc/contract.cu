@@ -339,73 +339,9 @@ __global__ void __launch_bounds__(256) pack_kernel(const double* __restrict__ X,
     }
 }
 
-// ---- norm: column sums --------------------------------------------------------------------
-constexpr int NORM_BLOCKS = 64;
-
-__global__ void __launch_bounds__(256) colsum_kernel(const double* __restrict__ X, long long n_rows,
-                                                     int kdim, double* __restrict__ out /*[NORM_BLOCKS][kdim]*/) {
-    // thread t owns column (t % kdim) when kdim <= 256, else loops over columns
-    const long long rows_per_block = (n_rows + gridDim.x - 1) / gridDim.x;
-    const long long r_begin = blockIdx.x * rows_per_block;
-    const long long r_end = r_begin + rows_per_block < n_rows ? r_begin + rows_per_block : n_rows;
-    extern __shared__ double sh[];                                  // [256]
-    for (int k0 = 0; k0 < kdim; k0 += 256) {
-        const int kw = kdim - k0 < 256 ? kdim - k0 : 256;           // columns this pass
-        const int lanes_per_col = 256 / kw;                          // >= 1 (kw divides 256 or kw == 256)
-        const int k = threadIdx.x % kw, sub = threadIdx.x / kw;
-        double s = 0.0;
-        if (sub < lanes_per_col)
-            for (long long r = r_begin + sub; r < r_end; r += lanes_per_col) s += X[r * kdim + k0 + k];
-        sh[threadIdx.x] = s;
-        __syncthreads();
-        if (threadIdx.x < kw) {
-            double t = 0.0;
-            for (int j = 0; j < lanes_per_col; ++j) t += sh[j * kw + threadIdx.x];
-            out[(long long)blockIdx.x * kdim + k0 + threadIdx.x] = t;
-        }
-        __syncthreads();
-    }
-}
-
-__global__ void norm_finalize_kernel(const double* __restrict__ pa, const double* __restrict__ pb,
-                                     int kdim, double scale, double* __restrict__ norm) {
-    __shared__ double sh[8];
-    double s = 0.0;
-    for (int k = threadIdx.x; k < kdim; k += blockDim.x) {
-        double ca = 0.0, cb = 0.0;
-        for (int b = 0; b < NORM_BLOCKS; ++b) { ca += pa[(long long)b * kdim + k]; cb += pb[(long long)b * kdim + k]; }
-        s += ca * cb;
-    }
-    s = warp_sum(s);
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int w = 0; w < 8; ++w) t += sh[w];
-        *norm = t * scale;
-    }
-}
-
 }  // namespace
 
-extern "C" int qdc_norm_workspace_doubles(int kdim) { return 2 * NORM_BLOCKS * kdim; }
-
-extern "C" int qdc_contract_norm(const double* d_A, int64_t n_rows_total, const double* d_Bt,
-                                 int64_t n_cols, int kdim, double scale, double* d_colsums,
-                                 double* d_norm, void* stream) {
-    QDC_REQUIRE(d_A && d_Bt && d_colsums && d_norm, "null buffer");
-    QDC_REQUIRE(kdim >= 1 && (kdim <= 256 ? 256 % kdim == 0 : kdim % 256 == 0), "kdim");
-    cudaStream_t s = (cudaStream_t)stream;
-    double* pa = d_colsums;
-    double* pb = d_colsums + (long long)NORM_BLOCKS * kdim;
-    colsum_kernel<<<NORM_BLOCKS, 256, 256 * sizeof(double), s>>>(d_A, n_rows_total, kdim, pa);
-    QDC_CHECK_LAUNCH();
-    colsum_kernel<<<NORM_BLOCKS, 256, 256 * sizeof(double), s>>>(d_Bt, n_cols, kdim, pb);
-    QDC_CHECK_LAUNCH();
-    norm_finalize_kernel<<<1, 256, 0, s>>>(pa, pb, kdim, scale, d_norm);
-    QDC_CHECK_LAUNCH();
-    return QDC_OK;
-}
+// (column sums and the normalisation: i8_prep.cu, qdc_colsum / qdc_contract_norm)
 
 template <int STORE, bool OUT32>
 static int launch_contract(const ContractArgs& args, int grid, cudaStream_t s) {

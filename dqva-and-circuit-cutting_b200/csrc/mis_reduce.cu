@@ -322,14 +322,32 @@ __device__ __forceinline__ bool better(double p, uint64_t x, double q, uint64_t 
     return p > q || (p == q && x < y);
 }
 
+// optionally first: sums[j] += sum_i partials[3 i + j] in a fixed order (what finalize_sums_kernel
+// does), so that scoring kernels need one finishing launch, not two
 __global__ void __launch_bounds__(1024) topk_kernel(const uint64_t* __restrict__ cx, double* cp,
                                                     const unsigned long long* __restrict__ count,
                                                     long long cap, int k, uint64_t* top_x,
-                                                    double* top_p) {
-    const long long n = (long long)*count < cap ? (long long)*count : cap;
+                                                    double* top_p, const double* __restrict__ partials,
+                                                    int n_partials, double* sums) {
     __shared__ double sp[32];
     __shared__ uint64_t sx[32];
     __shared__ long long si[32];
+    if (partials) {
+        __shared__ double fs[3 * 32];
+        double a = 0, b = 0, c = 0;
+        for (int i = threadIdx.x; i < n_partials; i += blockDim.x) {
+            a += partials[3 * i]; b += partials[3 * i + 1]; c += partials[3 * i + 2];
+        }
+        a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+        if ((threadIdx.x & 31) == 0) { fs[threadIdx.x >> 5] = a; fs[32 + (threadIdx.x >> 5)] = b; fs[64 + (threadIdx.x >> 5)] = c; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double x = 0, y = 0, z = 0;
+            for (int w = 0; w < 32; ++w) { x += fs[w]; y += fs[32 + w]; z += fs[64 + w]; }
+            sums[0] += x; sums[1] += y; sums[2] += z;
+        }
+    }
+    const long long n = (long long)*count < cap ? (long long)*count : cap;
     const double NEG = -1.0 / 0.0;
     for (int round = 0; round < k; ++round) {
         double bp = NEG; uint64_t bx = ~0ull; long long bi = -1;
@@ -372,7 +390,17 @@ extern "C" int qdc_topk_select(const uint64_t* d_cand_x, double* d_cand_p,
     QDC_REQUIRE(cand_cap >= 0 && d_top_x && d_top_p && d_cand_count, "buffers");
     QDC_REQUIRE(d_cand_x && d_cand_p, "candidates");
     topk_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(d_cand_x, d_cand_p, d_cand_count, cand_cap, k,
-                                                      d_top_x, d_top_p);
+                                                      d_top_x, d_top_p, nullptr, 0, nullptr);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+// finalize the partial sums and select the top-k in one launch (k = 0: sums only)
+int qdc_launch_finish(const double* d_partials, int n_partials, double* d_sums, const uint64_t* d_cand_x,
+                      double* d_cand_p, const unsigned long long* d_cand_count, long long cand_cap, int k,
+                      uint64_t* d_top_x, double* d_top_p, cudaStream_t stream) {
+    topk_kernel<<<1, 1024, 0, stream>>>(d_cand_x, d_cand_p, d_cand_count, cand_cap, k, d_top_x, d_top_p,
+                                        d_partials, n_partials, d_sums);
     QDC_CHECK_LAUNCH();
     return QDC_OK;
 }

@@ -227,26 +227,59 @@ int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_B
                      double* d_partials, void* stream);
 
 /* The same contraction + fused scoring on the 5th-generation tensor cores (tcgen05.mma kind::i8,
- * TMEM accumulators): the FP64 operands are split into n_slices radix-256 digits per element
- * (balanced digits in [-128, 127], rounded to nearest) with one power-of-two scale per row; all digit-pair products of order i + j < n_slices are accumulated
- * exactly in int32 and combined by FP64 FMAs.  Error bound (stated, not measured):
+ * TMEM accumulators): the FP64 operands are split into radix-256 digits per element (balanced
+ * digits in [-128, 127]) with one power-of-two scale per row; all digit-pair products of order
+ * i + j < n_slices are accumulated exactly in int32 and combined exactly in integers.  Error bound
+ * (stated, not measured):
  * |P~ - P~_exact| <= 2^(e_r + f_c) * scale * kdim * (n_slices + 1.1) * 2^(-8 n_slices), 2^e_r / 2^f_c
  * = power-of-two ceilings of the row maxima; kdim = 256: 1.4e-9 (5 slices), 6.5e-12 (6 slices)
- * times 2^(e_r + f_c) * scale -- FP64 accumulation itself: 2.8e-14.  (The Python wrapper can pick
- * n_slices from these bounds evaluated on the actual operands: recombine.i8_error_bounds.)  Operands are ROW-MAJOR here
- * (d_A: [a_rows_total][kdim], d_Bt: [n_cols][kdim]); slicing is part of the call.  kdim <= 256,
- * n_slices 2..6, threshold >= 0.  store_mode 0, 1 = united slab float64, 2 = united slab float32.  d_workspace:
- * 256-byte aligned, qdc_contract_i8_workspace_bytes(n_rows, n_cols, kdim, n_slices) bytes. */
-int64_t qdc_contract_i8_workspace_bytes(int64_t n_rows, int64_t n_cols, int kdim, int n_slices);
-int qdc_contract_i8(const double* d_A, int64_t a_rows_total, const double* d_Bt, int64_t row_lo,
-                    int64_t n_rows, int64_t n_cols, int kdim, int n_slices, double scale,
-                    const double* d_norm, double threshold,
-                    const uint64_t* d_row_x, const uint64_t* d_row_forb,
-                    const uint32_t* d_row_wok, const uint64_t* d_col_x,
-                    const uint32_t* d_col_wok, void* d_P_out, int store_mode,
-                    void* d_workspace, double* d_sums, uint64_t* d_cand_x, double* d_cand_p,
-                    unsigned long long* d_cand_count, int64_t cand_cap,
-                    double* d_partials, void* stream);
+ * times 2^(e_r + f_c) * scale -- FP64 accumulation itself: 2.8e-14.  kdim <= 256.
+ *
+ * Step 1, once per operand and evaluation (qdc_i8_prepare): ONE pass over the row-major FP64
+ * operand d_X[n_rows][kdim] writes, into a caller-owned 256-byte aligned buffer of
+ * qdc_i8_operand_bytes(n_rows, kdim, n_slices) bytes, the n_slices digit planes in the tensor
+ * cores' core-matrix order, the row scales, the scoring tables of the column role, the column sums
+ * (sum_r x, sum_r weight_r x: they give combined_norm, qsplit_mlrecon_methods.py:471-472, sum p and
+ * sum p w without touching the outputs) and the statistics of the error bounds.
+ * d_wok: weight | ok << 8 per row (qdc_mis_build_tables; NULL: weight 0, ok).  column_role != 0 for
+ * the operand of fragment 0 (streamed through the tiles): d_x = its col_x table; every 16 adjacent
+ * columns then share an integer unit (a column more than 2^20 below the largest of its group is
+ * sliced at that floor; the bounds use the exponent actually applied).
+ *
+ * Step 2 (qdc_contract_i8_prepared): plan + contraction + finish, no host synchronisation.
+ *   n_stored: digit planes the operands hold; n_slices: planes used, 2..n_stored, or 0 = the
+ *   smallest count in 3..n_stored whose a-posteriori bounds for THESE operands -- per output, and
+ *   on the masked sum (n_nodes * (sum_{r ok} 2^e_r) (sum_{c ok} 2^f_c) * ... ) -- are both <= tol,
+ *   chosen on the device (the kernels of the other counts return at once).
+ *   norm_mode 0: none; 1: the total of the distribution, from the column sums of both operands
+ *   plus d_extra_colsums (n_extra x kdim partial column sums of row-operand rows that are not in
+ *   this slab: qdc_colsum; NULL if the slab is the whole operand); 2: *d_norm_in.
+ *   d_A_src / d_Bt_src: the FP64 rows the operands were prepared from (store_mode 0: outputs the
+ *   integer candidate filter flags are re-evaluated exactly from them).
+ *   row tables: indexed row_lo + local row.  store_mode 0, 1 = united slab float64, 2 = float32.
+ *   d_result: 16 doubles [sum p, sum p w [indset], sum p w, norm, slices used, bound per output,
+ *   bound on the masked sum, candidate count (uint64), largest column exponent, ...] -- written,
+ *   not accumulated.  d_cand_*: candidate sink as qdc_mis_reduce; k, d_top_*: as qdc_topk_select
+ *   (k = 0: no selection).  d_partials: 3 * qdc_reduce_partials() doubles. */
+int64_t qdc_i8_operand_bytes(int64_t n_rows, int kdim, int n_slices);
+int qdc_i8_prepare(const double* d_X, int64_t n_rows, int kdim, int n_slices, int column_role,
+                   const uint32_t* d_wok, const uint64_t* d_x, void* d_operand, void* stream);
+int qdc_contract_i8_prepared(const void* d_opA, int64_t n_rows, const void* d_opB, int64_t n_cols,
+                             int kdim, int n_stored, int n_slices, double tol, int n_nodes,
+                             double scale, int norm_mode, const double* d_norm_in,
+                             const double* d_extra_colsums, int n_extra, double threshold,
+                             const double* d_A_src, const double* d_Bt_src, int64_t row_lo,
+                             const uint64_t* d_row_x, const uint64_t* d_row_forb,
+                             const uint32_t* d_row_wok, void* d_P_out, int store_mode,
+                             double* d_result, uint64_t* d_cand_x, double* d_cand_p, int64_t cand_cap,
+                             int k, uint64_t* d_top_x, double* d_top_p, double* d_partials, void* stream);
+
+/* Column sums of rows [r0_begin, r0_end) and [r1_begin, r1_end) of a row-major FP64 matrix:
+ * d_partials[qdc_colsum_partials()][kdim], one row per CTA, to be added in row order (fixed order:
+ * run-to-run deterministic).  Full grid, 16-byte loads. */
+int qdc_colsum_partials(void);
+int qdc_colsum(const double* d_X, int64_t r0_begin, int64_t r0_end, int64_t r1_begin, int64_t r1_end,
+               int kdim, double* d_partials, void* stream);
 
 /* sum over all (r, c) of P~ without forming it: scale * sum_k (sum_r A[r,k]) (sum_c Bt[c,k]).
  * This is combined_norm of qsplit_mlrecon_methods.py:471.  d_colsums: workspace of

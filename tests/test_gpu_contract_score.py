@@ -130,8 +130,10 @@ def test_indset_mask_against_python_is_indset(cuda):
 
 @pytest.mark.parametrize("rb,cb,kdim,slices", [(7, 6, 256, 6), (8, 7, 64, 6), (5, 9, 16, 5), (9, 6, 256, 4), (8, 8, 256, 5), (7, 7, 128, 3)])
 def test_int8_sliced_contraction_matches_fp64(cuda, rb, cb, kdim, slices):
-    """qdc_contract_i8 (tcgen05 int8 tensor cores, exact radix-256 slicing) against the FP64 kernel
-    and the stated error bound: kdim (S + 1.1) 2^(-8S) 2^(e_r + f_c) scale per output."""
+    """The int8 contraction (tcgen05 int8 tensor cores, exact radix-256 slicing, all-integer scoring
+    epilogue) against the FP64 kernel: the three sums within the summed stated bound
+    kdim (S + 1.1) 2^(-8S) 2^(e_r + f_c) scale, the same top-k, the same numbers on a second call.
+    (Per-output check: test_int8_sliced_contraction_per_output_bound.)"""
     import torch
     from qdc_b200 import recombine as rc
     rng = np.random.default_rng(rb * 100 + cb)
@@ -153,13 +155,10 @@ def test_int8_sliced_contraction_matches_fp64(cuda, rb, cb, kdim, slices):
     ea = np.ceil(np.log2(np.abs(A).max(axis=1)))[:, None]
     fb = np.ceil(np.log2(np.abs(Bt).max(axis=1)))[None, :]
     bound = 2.0 ** (ea + fb + 1) * scale * kdim * (slices + 1.1) * 2.0 ** (-8 * slices)
-    # per-output check through the united store of a second call
-    M2 = M
-    tabs2 = tabs
-    res = rc.contract_and_score(A_d, B_d, tabs2, scale=scale, threshold=thr, k=4, normalize=False,
+    res = rc.contract_and_score(A_d, B_d, tabs, scale=scale, threshold=thr, k=4, normalize=False,
                                 store=None, method="i8", slices=slices)
     s_got = got.get()
-    assert s_got == res.get()                               # deterministic
+    assert s_got == res.get()                               # run-to-run deterministic
     ref = rc.contract_and_score(rc.pad_kdim(A_d), rc.pad_kdim(B_d), tabs, scale=scale, threshold=thr, k=4,
                                 normalize=False, store=None).get()
     tot_bound = float(bound.sum()) * (rb + cb)
@@ -172,7 +171,7 @@ def test_int8_sliced_contraction_matches_fp64(cuda, rb, cb, kdim, slices):
 
 @pytest.mark.parametrize("slices", [4, 5, 6])
 def test_int8_sliced_contraction_per_output_bound(cuda, slices):
-    """Every output of qdc_contract_i8 (united store) against the float64 product: the stated bound
+    """Every output of the int8 contraction (united store) against the float64 product: the stated bound
     kdim (S + 1.1) 2^(-8S) 2^(e_r + f_c) scale holds per output, on operands whose rows span twelve
     orders of magnitude and include zero rows, negative entries and exact powers of two."""
     import torch
@@ -196,7 +195,9 @@ def test_int8_sliced_contraction_per_output_bound(cuda, slices):
     want = scale * (A @ Bt.T)
     with np.errstate(divide="ignore"):
         ea = np.where(np.abs(A).max(axis=1) > 0, np.floor(np.log2(np.abs(A).max(axis=1))) + 1, -2000.0)[:, None]
-        fb = np.floor(np.log2(np.abs(Bt).max(axis=1)))[None, :] + 1
+        fb = np.floor(np.log2(np.abs(Bt).max(axis=1))) + 1
+    # a column more than 2^20 below the largest of its 16-column group is sliced at that floor
+    fb = np.maximum(fb, np.repeat(fb.reshape(-1, 16).max(axis=1), 16) - 20)[None, :]
     # + 1: the exponent is bumped when the scaled maximum would exceed 127 / 128
     bound = 2.0 ** (ea + fb + 2) * scale * kdim * (slices + 1.1) * 2.0 ** (-8 * slices)
     fp64_noise = 4 * kdim * 2.0 ** -53 * scale * (np.abs(A) @ np.abs(Bt).T)
@@ -260,7 +261,7 @@ def test_int8_contraction_row_slabs_and_given_norm(cuda):
     (37, 5000, 16, 4),
 ])
 def test_int8_contraction_shapes(cuda, M, N, kdim, slices):
-    """Work-item scheduling, TMEM-resident slices and ragged edges of qdc_contract_i8 on shapes that
+    """Work-item scheduling, TMEM-resident slices and ragged edges of the int8 contraction on shapes that
     the power-of-two configs never produce, against the FP64 kernel (sums within the stated bound,
     same candidates)."""
     import torch
@@ -294,9 +295,10 @@ def test_int8_contraction_shapes(cuda, M, N, kdim, slices):
 
 @pytest.mark.parametrize("tol,spread", [(1e-10, 0), (1e-6, 0), (1e-10, 8), (1e-14, 0)])
 def test_int8_auto_slices_keeps_its_bounds(cuda, tol, spread):
-    """slices="auto": the chosen count's a-posteriori bounds (recombine.i8_error_bounds) are below
-    tol unless even 6 slices cannot do it, one slice fewer would violate them, and the measured
-    differences from the FP64 kernel stay inside the bounds."""
+    """slices="auto": the count is chosen ON THE DEVICE (i8_plan_kernel); its a-posteriori bounds
+    equal the torch restatement recombine.i8_error_bounds, are below tol unless even 6 slices cannot
+    do it, one slice fewer would violate them, and the measured differences from the FP64 kernel
+    stay inside the bounds."""
     import torch
     from qdc_b200 import recombine as rc
     rb, cb, kdim = 9, 8, 64
@@ -315,6 +317,11 @@ def test_int8_auto_slices_keeps_its_bounds(cuda, tol, spread):
     assert 3 <= S <= 6 and eb["slices"] == S
     all_bounds = rc.i8_error_bounds(A_d, B_d, tabs, 0.25, ref.norm)
     assert abs(all_bounds[S]["cost"] - eb["cost"]) <= 1e-12 * eb["cost"]
+    assert abs(all_bounds[S]["per_output"] - eb["per_output"]) <= 1e-12 * eb["per_output"]
+    # the unstored (all-integer epilogue) form picks the same count and lands on the same cost
+    res0 = rc.contract_and_score(A_d, B_d, tabs, scale=0.25, k=4, method="i8", slices="auto", tol=tol)
+    assert res0.slices == S
+    assert abs(res0.get()["sum_pw_indset"] - ref.get()["sum_pw_indset"]) <= eb["cost"] + 1e-13
     if S < 6 or max(all_bounds[6].values()) <= tol:
         assert eb["per_output"] <= tol and eb["cost"] <= tol
     if S > 3:
@@ -323,3 +330,95 @@ def test_int8_auto_slices_keeps_its_bounds(cuda, tol, spread):
     fp64_noise = 1e-13
     assert abs(got["sum_pw_indset"] - want["sum_pw_indset"]) <= eb["cost"] + fp64_noise
     assert float((res.P - ref.P).abs().max()) <= eb["per_output"] + fp64_noise
+
+
+def test_int8_prepared_operands_are_reusable(cuda):
+    """prepare_i8 once, contract many times: the column operand of a fragment whose tensor does not
+    change between parameter sets is prepared once and reused with different row operands; results
+    equal the one-call form bit for bit, and a 6-slice buffer serves a 4-slice contraction."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rb, cb, kdim = 8, 9, 64
+    rng = np.random.default_rng(21)
+    M, N = 1 << rb, 1 << cb
+    Bt = torch.as_tensor(rng.random((N, kdim)) * 10.0 ** rng.uniform(-3, 0, (N, 1)), device=cuda)
+    G = __import__("networkx").gnm_random_graph(rb + cb, 30, seed=4)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    pb = rc.prepare_i8(Bt, tabs.col_wok, tabs.col_x, slices=6, column_role=True)
+    for seed in (1, 2):
+        A = torch.as_tensor(np.random.default_rng(seed).random((M, kdim)), device=cuda)
+        one = rc.contract_and_score(A, Bt, tabs, scale=0.5, threshold=1e-4, k=3, method="i8", slices=6).get()
+        pa = rc.prepare_i8(A, tabs.row_wok, slices=6)
+        two = rc.contract_and_score(pa, pb, tabs, scale=0.5, threshold=1e-4, k=3, method="i8", slices=6).get()
+        assert one == two
+        ref = rc.contract_and_score(A, Bt, tabs, scale=0.5, threshold=1e-4, k=3).get()
+        assert abs(one["sum_pw_indset"] - ref["sum_pw_indset"]) < 1e-12
+        assert [x for x, _ in one["top"]] == [x for x, _ in ref["top"]]
+    # fewer slices than stored: truncation of the balanced digits, inside the 4-slice bound
+    auto = rc.contract_and_score(pa, pb, tabs, scale=0.5, threshold=1e-4, k=3, method="i8", slices="auto", tol=1e-6)
+    assert auto.slices in (3, 4) and auto.error_bound["cost"] <= 1e-6
+    assert abs(auto.get()["sum_pw_indset"] - ref["sum_pw_indset"]) <= auto.error_bound["cost"] + 1e-13
+
+
+def test_int8_candidates_of_a_peaked_distribution(cuda):
+    """The all-integer epilogue flags candidate outputs on the leading digit order alone and
+    re-evaluates them exactly from the FP64 operands: on a distribution with a few hundred outputs
+    above the threshold (and many just below it) the candidate count, the top-k indices and their
+    probabilities equal the FP64 kernel's; zero rows, zero 16-column groups and a threshold of the
+    size of the largest output are covered."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rb, cb, kdim = 9, 9, 256
+    rng = np.random.default_rng(5)
+    M, N = 1 << rb, 1 << cb
+    A = rng.random((M, kdim)) * 1e-4
+    Bt = rng.random((N, kdim)) * 1e-4
+    hot_r, hot_c = rng.choice(M, 12, replace=False), rng.choice(N, 20, replace=False)
+    A[hot_r] = rng.random((12, kdim)) * rng.uniform(0.5, 2.0, (12, 1))
+    Bt[hot_c] = rng.random((20, kdim)) * rng.uniform(0.5, 2.0, (20, 1))
+    A[40:60] = 0.0                                         # zero rows
+    Bt[64:96] = 0.0                                        # two all-zero 16-column groups
+    G = __import__("networkx").gnm_random_graph(rb + cb, 20, seed=6)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    A_d, B_d = torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda)
+    want = A @ Bt.T
+    want /= want.sum()
+    hot = np.sort(want[np.ix_(hot_r, hot_c)].reshape(-1))
+    for thr in (float(0.5 * (hot[40] + hot[41])), float(0.5 * (hot[-2] + hot[-1])), float(hot[-1] * 2)):
+        n_want = int((want > thr).sum())
+        ref = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=16).get()
+        for slices in (4, 5, 6, "auto"):
+            got = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=16, method="i8", slices=slices).get()
+            assert got["n_candidates"] == ref["n_candidates"] == n_want
+            assert [x for x, _ in got["top"]] == [x for x, _ in ref["top"]]
+            assert all(abs(p - q) <= 1e-15 + 1e-13 * q for (_, p), (_, q) in zip(got["top"], ref["top"]))
+            assert abs(got["sum_p"] - 1.0) < 1e-12
+
+
+def test_colsum_and_norm_kernels(cuda):
+    """qdc_colsum (full-grid streaming column sums over two row ranges) and qdc_contract_norm against
+    numpy, on even / odd contraction lengths and a misaligned base pointer."""
+    import ctypes as C
+    import torch
+    from qdc_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(9)
+    for rows, kdim in ((5000, 256), (777, 48), (1000, 7), (33, 512)):
+        X = rng.standard_normal((rows, kdim))
+        X_d = torch.as_tensor(X, device=cuda)
+        n_part = lib.qdc_colsum_partials()
+        part = torch.empty(n_part, kdim, dtype=torch.float64, device=cuda)
+        lo, hi = rows // 5, rows // 2
+        _lib.check(lib.qdc_colsum(_lib.ptr(X_d), 0, lo, hi, rows, kdim, _lib.ptr(part), _lib.stream_ptr()))
+        want = X[:lo].sum(0) + X[hi:].sum(0)
+        assert np.abs(part.sum(0).cpu().numpy() - want).max() < 1e-11
+        Y = rng.standard_normal((300, kdim))
+        Y_d = torch.as_tensor(Y, device=cuda)
+        ws = torch.empty(lib.qdc_norm_workspace_doubles(kdim), dtype=torch.float64, device=cuda)
+        norm = torch.empty(1, dtype=torch.float64, device=cuda)
+        _lib.check(lib.qdc_contract_norm(_lib.ptr(X_d), rows, _lib.ptr(Y_d), 300, kdim, 0.25, _lib.ptr(ws),
+                                         _lib.ptr(norm), _lib.stream_ptr()))
+        want_n = 0.25 * float(X.sum(0) @ Y.sum(0))
+        assert abs(float(norm) - want_n) < 1e-9 * max(1.0, abs(want_n))

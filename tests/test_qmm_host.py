@@ -115,9 +115,10 @@ def test_contraction_spec_parsing(monkeypatch):
 
 
 def test_i8_error_bounds_formula():
-    """recombine.i8_error_bounds on the CPU (pure torch): the per-output bound is
-    2^(e_r + f_c) scale / norm kdim (S + 1.1) 2^(-8S) at the largest rows, the cost bound only
-    counts rows / columns that are independent sets themselves, both shrink 256-fold per slice."""
+    """recombine.i8_error_bounds on the CPU (pure torch mirror of the device plan kernel): the
+    per-output bound is 2^(e_r + f_c) scale / norm kdim (S + 1.1) 2^(-8S) at the largest rows, the
+    cost bound only counts rows / columns that are independent sets themselves (plus the rounding
+    of the epilogue's 16-column sums), both shrink 256-fold per slice."""
     from qdc_b200 import recombine as rc
     A = torch.tensor([[0.3, -0.7, 0.0, 0.1], [0.01, 0.02, 0.0, 0.0], [0.0, 0.0, 0.0, 0.0]], dtype=torch.float64)
     Bt = torch.tensor([[1.5, 0.0, 0.0, 0.2], [0.2, 0.1, 0.0, 0.0]], dtype=torch.float64)
@@ -127,8 +128,13 @@ def test_i8_error_bounds_formula():
     norm = torch.tensor([2.0], dtype=torch.float64)
     b = rc.i8_error_bounds(A, Bt, tabs, 0.5, norm)
     g5 = 4 * 6.1 * 2.0 ** -40
-    # power-of-two ceilings with the bump: 0.7 -> 2, 0.02 -> 1/16, 1.5 -> 4, 0.2 -> 1/2
-    assert abs(b[5]["per_output"] - 2 * 4 * 0.25 * g5) < 1e-25
-    assert abs(b[5]["cost"] - 3 * (2 + 0) * (4 + 0.5) * 0.25 * g5) < 1e-25
-    assert abs(b[4]["cost"] / b[5]["cost"] - 256 * 5.1 / 6.1) < 1e-9
+    # exponents the slicing applies (|x| 2^(7 - e) <= 127): 0.7 -> 2^0, 0.02 -> 2^-5, 1.5 -> 2^1, 0.2 -> 2^-2
+    assert abs(b[5]["per_output"] - 1 * 2 * 0.25 * g5) < 1e-25
+    fold = 0.5 * 1 * 2.0 ** -26                                       # one 16-column group
+    assert abs(b[5]["cost"] - 3 * 0.25 * ((1 + 0) * (2 + 0.25) * g5 + 1 * 2 * fold * 2.0 ** -40)) < 1e-25
+    assert abs(b[4]["per_output"] / b[5]["per_output"] - 256 * 5.1 / 6.1) < 1e-9
+    # a column more than 2^20 below the largest of its 16-column group is sliced at that floor
+    Bt2 = torch.tensor([[1.5, 0.0, 0.0, 0.2], [2e-9, 1e-9, 0.0, 0.0]], dtype=torch.float64)
+    b2 = rc.i8_error_bounds(A, Bt2, tabs, 0.5, norm)
+    assert abs(b2[5]["cost"] - 3 * 0.25 * (1 * (2 + 2.0 ** -19) * g5 + 1 * 2 * fold * 2.0 ** -40)) < 1e-25
     assert set(b) == {2, 3, 4, 5, 6}
