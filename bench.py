@@ -348,33 +348,40 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     kernel_events = []
-    chosen = {}                        # slice count and bounds of the last i8 call (slices = auto)
     tol = args.tol / ws                # every rank keeps its share of the cost error below tol / N
-
-    def note(res):
-        if res.slices is not None:
-            chosen["slices"] = res.slices
-            chosen["bounds"] = res.error_bound
-        return res
+    i8 = args.method == "i8"
+    # e2e at N > 1: the column operand crosses PCIe once in total -- every rank copies 1/N of it from
+    # its pinned host buffer and the ranks all-gather the pieces over NVLink
+    c_lo, c_n = qdist.row_shard(N, rank, ws)
+    Bt_pin_shard = Bt_pin[c_lo:c_lo + c_n]
+    even_cols = N % ws == 0
 
     def step_device():
-        # inputs resident in HBM (row-major); packing for the bulk-copy pipeline is part of the step
-        res = note(rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
-                                         row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
-                                         method=args.method, slices=args.slices, tol=tol))
-        return qdist.finish(res.sums, res.top_x, res.top_p, k) if ws > 1 else res
+        # inputs resident in HBM (row-major FP64); slicing / packing is part of the step.  Nothing in
+        # here reads the device back before the finish.
+        res = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k,
+                                    row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
+                                    method=args.method, slices=args.slices, tol=tol)
+        if ws > 1:
+            return (qdist.finish_block(res, k) if i8 else qdist.finish(res.sums, res.top_x, res.top_p, k)), res
+        return res, res
 
     def step_e2e():
         A_stage.copy_(A_pin_slab, non_blocking=True)
-        Bt_stage.copy_(Bt_pin, non_blocking=True)
+        if ws > 1 and even_cols:
+            Bt_stage[c_lo:c_lo + c_n].copy_(Bt_pin_shard, non_blocking=True)
+            dist.all_gather_into_tensor(Bt_stage.view(-1), Bt_stage[c_lo:c_lo + c_n].reshape(-1))
+        else:
+            Bt_stage.copy_(Bt_pin, non_blocking=True)
         norm = qdist.sharded_norm(A_stage, Bt_stage, scale) if ws > 1 else None
         res = rc.contract_and_score(A_stage, Bt_stage, tabs_slab, scale=scale, threshold=1e-5, k=k,
                                     method=args.method, slices=args.slices, norm=norm, tol=tol)
         if ws > 1:
+            if i8:
+                return qdist.finish_block(res, k)
             sums, top = qdist.finish(res.sums, res.top_x, res.top_p, k)
             return sums.cpu().numpy(), top
-        out = res.get()
-        return out
+        return res.get()
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -400,15 +407,19 @@ def run_b200(args):
     t_e2e, last_e2e = timed(step_e2e, args.steps, max(args.warmup, 3))
 
     # correctness spot check of the result that was just timed (cheap, outside timed regions)
+    last_dev, last_res = last_dev
     if ws == 1:
         final = last_dev.get()
         sum_p, cost = final["sum_p"], final["sum_pw_indset"]
         top = final["top"]
     else:
         sums, top = last_dev
-        sum_p, cost = float(sums[0].item()), float(sums[1].item())
+        sum_p, cost = float(sums[0]), float(sums[1])
     assert abs(sum_p - 1.0) < 1e-9, f"distribution does not sum to 1: {sum_p}"
-    # the end-to-end leg (host operands, sharded row operand at N > 1) must land on the same numbers
+    chosen = {}
+    if i8:
+        chosen = {"slices": last_res.slices, "bounds": last_res.error_bound}
+    # the end-to-end leg (host operands, sharded operands at N > 1) must land on the same numbers
     if ws == 1:
         e2e_sum_p, e2e_cost = last_e2e["sum_p"], last_e2e["sum_pw_indset"]
     else:
@@ -441,21 +452,25 @@ def run_b200(args):
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s",
                     "frac": achieved / peak,
                     "traffic": ncu_traffic(rb, cb, KDIM, ws, "i8"),
-                    "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops_sustained (dense int8 = 2 x "
-                                    "dense bf16 on the tcgen05 pipe; the issue-rate probe "
-                                    "profiles/r1_umma_rate_probe.log reaches 4.50 POP/s at N=256 and "
-                                    "2.52 at the N=64 instruction this kernel issues)") if bf16 else
+                    "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops_sustained (MEASURED_PEAKS has no int8 entry; "
+                                    "dense int8 = 2 x dense bf16 on the tcgen05 pipe)") if bf16 else
                                    "nominal 4.5 POP/s dense int8 (MEASURED_PEAKS.json absent)",
+                    # the second denominator, stated once: this repo's own issue-rate probe
+                    # (profiles/r1_umma_rate_probe.log) measures the int8 pipe at 4.50 POP/s (N = 256);
+                    # ncu's sm__pipe_tensor_cycles_active is the fraction of THAT rate
+                    "frac_of_measured_int8_issue_peak": achieved / 4500.0,
+                    "int8_issue_peak_tops": 4500.0,
                     "algorithmic_ops_per_launch": int8_ops,
                     "algorithmic_ops_note": f"2 x outputs x kdim x {pairs} slice pairs (S = {n_sl})",
                     "fp64_equivalent_tflops": flops / ws / t_kernel / 1e12,
                     "fp64_pipe_peak_tflops": dgemm_peak,
-                    "kernel": f"contract_i8_kernel<{n_sl}> (+ slice / column-table / moments kernels)",
+                    "kernel": f"contract_i8_kernel<{n_sl}> (events bracket plan + contraction + finish)",
                     "slices": n_sl, "slices_chosen_by": chosen.get("bounds") if args.slices == "auto" else "command line",
                     "kernel_ms": t_kernel * 1e3}
-        dtype = f"i8 x {n_sl} slices (Ozaki split of FP64 operands, int32 accumulation, FP64 fold)"
-        launches = 12 * args.steps        # colsum x2, norm_finalize, slice x2, coltab, contract_i8, finalize_sums,
-                                          # moments x2, moments_finish, topk (profiles/r1_launches_i8.csv)
+        dtype = f"i8 x {n_sl} slices (Ozaki split of FP64 operands, int32 accumulation, integer fold)"
+        # i8_prep x2, [colsum of the other ranks' rows], i8_plan, contract_i8 (x4 with slices = auto:
+        # the three counts the plan kernel did not choose return at once), finish (sums + top-k)
+        launches = (5 + (3 if args.slices == "auto" else 0) + (1 if ws > 1 else 0)) * args.steps
     else:
         achieved = flops / ws / t_kernel / 1e12
         roofline = {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,
@@ -479,7 +494,7 @@ def run_b200(args):
                    "l2": "operands 0.5 GB > 126 MB L2; no flush needed"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
-                "h2d_bytes_per_step": int(A_pin.numel() * 8 + ws * Bt_pin.numel() * 8),
+                "h2d_bytes_per_step": int(A_pin.numel() * 8 + (1 if even_cols else ws) * Bt_pin.numel() * 8),
                 "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
         "gpu_launches": launches,
         "roofline": roofline,
@@ -504,9 +519,46 @@ def run_b200(args):
             line["cpu_port"] = port
         except Exception as exc:
             line["cpu_port"] = {"value": None, "sample": f"failed: {exc}"}
+            sums = None
+        if sums is not None:
+            try:
+                line["parity_check"] = parity_check(rc, A_d, Bt_d, tabs, scale, k, args, sums, sample_rows,
+                                                    last_res, chosen)
+            except Exception as exc:
+                line["parity_check"] = {"pass": False, "note": f"failed to run: {exc!r}"}
     print(json.dumps(line), flush=True)
     if ws > 1:
         dist.destroy_process_group()
+
+
+def parity_check(rc, A_d, Bt_d, tabs, scale, k, args, cpu_sums, sample_rows, last_res, chosen):
+    """The headline configuration against something that is not this repo's kernels, at its own
+    size: the C/OpenMP port (FP64 dot products, oracle/c/oracle_port.c) evaluated `sample_rows` rows
+    x all 2^col_bits columns of the SAME operands; the GPU evaluates exactly those rows with the
+    normalisation of the full run (`row_lo = 0, n_rows = sample_rows, norm = `), for the headline
+    method and for the FP64 kernel.  The port's sums are unnormalised: divide by the same norm."""
+    norm = last_res.norm.reshape(1).clone()
+    norm_h = float(norm.item())
+    want = [float(v) / norm_h for v in cpu_sums]             # [sum p, sum p w [indset], sum p w]
+    out = {"rows": sample_rows, "cols": int(Bt_d.shape[0]), "cpu_port_sums": want}
+    ok = True
+    for name, kw in (("headline", dict(method=args.method, slices=args.slices, tol=args.tol)),
+                     ("f64", dict(method="f64"))):
+        got = rc.contract_and_score(A_d, Bt_d, tabs, scale=scale, threshold=1e-5, k=k, row_lo=0,
+                                    n_rows=sample_rows, norm=norm, **kw)
+        g = got.get()
+        diff = [g["sum_p"] - want[0], g["sum_pw_indset"] - want[1], g["sum_pw"] - want[2]]
+        # FP64 summation noise of 2^27 outputs in two different orders, plus (int8) the stated bound
+        # on the masked sum, scaled to the slab (the bound of the full run covers all rows)
+        allowed = 1e-12 * max(abs(want[2]), 1e-30)
+        if name == "headline" and got.error_bound is not None:
+            allowed += got.error_bound["cost"]
+        passed = all(abs(d) <= allowed for d in diff)
+        ok = ok and passed
+        out[name] = {"sums": [g["sum_p"], g["sum_pw_indset"], g["sum_pw"]], "minus_cpu_port": diff,
+                     "allowed": allowed, "pass": passed}
+    out["pass"] = ok
+    return out
 
 
 def measured_peaks():

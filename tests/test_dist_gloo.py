@@ -114,3 +114,39 @@ def test_sharded_norm_world_size_2():
         got, want = out[rank]
         assert abs(got - want) < 1e-12 * max(1.0, abs(want))
     assert out[0][0] == out[1][0]
+
+
+def _block_worker(rank, ws, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
+    import importlib, sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import dist as qd, recombine as rc
+    qd.init_from_env(backend="gloo")
+    k = 3
+    # the int8 path's result block: [3 sums | norm | slices | 2 bounds | candidate count | ... | k indices | k probs]
+    h = np.zeros(16 + 2 * k)
+    h[0:3] = [0.25 * (rank + 1), 1.0 * rank, 2.0]
+    h[7:8].view(np.int64)[0] = 2
+    h[16:16 + k].view(np.int64)[:] = [(1 << 40) + rank, 20 + rank, -1]
+    h[16 + k:16 + 2 * k] = [0.5 - 0.1 * rank, 0.3, float("-inf")]
+    block = torch.from_numpy(h)
+    res = rc.ScoreResult(block[0:3], block[16:16 + k].view(torch.int64), block[16 + k:], block[7:8].view(torch.int64),
+                         cand_cap=8, block=block)
+    total, top = qd.finish_block(res, k)
+    out[rank] = (total.tolist(), top)
+    dist.destroy_process_group()
+
+
+def test_finish_block_world_size_2():
+    """dist.finish_block: the whole result block is all-gathered, 64-bit indices survive the trip."""
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_block_worker, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    for rank in range(ws):
+        total, top = out[rank]
+        assert total == [0.75, 1.0, 4.0]
+        assert top == [(1 << 40, 0.5), ((1 << 40) + 1, 0.4), (20, 0.3)]
