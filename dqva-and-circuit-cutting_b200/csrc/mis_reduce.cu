@@ -212,6 +212,9 @@ __global__ void __launch_bounds__(256, 4) mis_reduce_kernel(
 }
 
 // scalar fallback for tiny tables (n_cols < vector width)
+template <typename T> __device__ __forceinline__ double prob_of(const T& v) { return (double)v; }
+template <> __device__ __forceinline__ double prob_of<Amp>(const Amp& v) { return v.re * v.re + v.im * v.im; }
+
 template <typename T>
 __global__ void __launch_bounds__(256) mis_reduce_small_kernel(
     const T* __restrict__ P, long long row_lo, long long n_rows, int col_shift,
@@ -223,7 +226,7 @@ __global__ void __launch_bounds__(256) mis_reduce_small_kernel(
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n;
          e += (long long)gridDim.x * blockDim.x) {
         const long long r = row_lo + (e >> col_shift), c = e & ((1ll << col_shift) - 1);
-        mis_accumulate(acc, (double)P[e] * inv_norm, tab.row_x[r], tab.row_forb[r], tab.row_wok[r],
+        mis_accumulate(acc, prob_of<T>(P[e]) * inv_norm, tab.row_x[r], tab.row_forb[r], tab.row_wok[r],
                        tab.col_x[c], tab.col_wok[c], sink);
     }
     mis_block_store(acc, scratch, partials);
@@ -307,6 +310,9 @@ extern "C" int qdc_mis_reduce(const void* d_P, int dtype, int64_t row_lo, int64_
         if (dtype == 0)
             mis_reduce_small_kernel<double><<<blocks, 256, 0, s>>>(
                 (const double*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
+        else if (dtype == 2)
+            mis_reduce_small_kernel<Amp><<<blocks, 256, 0, s>>>(
+                (const Amp*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);
         else
             mis_reduce_small_kernel<float><<<blocks, 256, 0, s>>>(
                 (const float*)d_P, row_lo, n_rows, col_shift, d_norm, tab, sink, d_partials);

@@ -192,6 +192,35 @@ def test_uncut_cost_batch_matches_oracle(cuda):
         assert abs(got[s] + s_pw) < TOL and abs(got_masked[s] + s_pwok) < TOL
 
 
+def test_uncut_cost_on_a_tiny_graph(cuda):
+    """Graphs of 3-4 nodes give fewer than 64 table columns, where qdc_mis_reduce takes its scalar
+    path: complex128 amplitudes must be scored as |amp|^2 there as well (they were once read as
+    float32)."""
+    import networkx as nx
+    from oracle import mis_oracle as mo
+    from qdc_b200 import mis
+    from qdc_b200.ansatz import dqv_ansatz
+    from qdc_b200.circuit import Parameter
+    for n, edges in ((3, [(0, 1), (1, 2)]), (4, [(0, 1), (1, 2), (2, 3), (3, 0)])):
+        G = nx.Graph()
+        G.add_nodes_from(range(n))
+        G.add_edges_from(edges)
+        syms = [Parameter(f"var_{i}") for i in range(n + 1)]
+        circ = dqv_ansatz.gen_dqva(G, P=1, params=syms, init_state="0" * n, mixer_order=list(range(n)))
+        used = circ.parameters
+        table = np.random.default_rng(n).uniform(0, 2 * np.pi, (3, len(used)))
+        be = _backend(cuda)
+        got = mis.uncut_cost(circ, be, G, params=table, param_order=used)
+        got_masked = mis.uncut_cost(circ, be, G, params=table, param_order=used, masked=True)
+        adj = mo.adjacency_masks(G, n)
+        for s in range(3):
+            bound = circ.bind_parameters(dict(zip(used, table[s])))
+            p = sv.probabilities(sv.simulate(n + 1, bound.to_instructions()))
+            _, s_pw = mo.score_array(p, n, 1, adj, masked=False)
+            _, s_pwok = mo.score_array(p, n, 1, adj, masked=True)
+            assert abs(got[s] + s_pw) < TOL and abs(got_masked[s] + s_pwok) < TOL
+
+
 def test_qaoa_plus_circuit_on_engine(cuda):
     import networkx as nx
     from qdc_b200.ansatz import qaoa_plus
