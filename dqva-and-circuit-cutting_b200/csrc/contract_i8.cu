@@ -129,6 +129,43 @@ __device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uin
         " tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n}\n"
         ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+// The 8 k steps of one slice pair at kdim = 256, issued from ONE asm block.  A k step of 32 advances a
+// descriptor's address field (bits 0-13 of the low word, 16-byte units) by 16; the field cannot carry
+// (shared memory ends below 2^14 units), so a single 32-bit add on the low word makes the next
+// descriptor.  Written this way on purpose: when the adds are visible to the compiler it hoists all
+// S x 8 loop-invariant descriptors out of the tile loop into VECTOR registers and pays two R2UR per
+// descriptor per use -- 19 issue slots per MMA on the one warp that issues them, which held the
+// tensor pipe at 54 % (profiles/r2_i8_issue_bound.md).  Here: 2 adds + 1 MMA per step.
+#define QDC_MMA_SS_STEP(OFF)                                                                   \
+    " add.u32 t, alo, " #OFF ";\n mov.b64 da, {t, ahi};\n"                                     \
+    " add.u32 t, blo, " #OFF ";\n mov.b64 db, {t, bhi};\n"                                     \
+    " tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %3, q;\n"
+__device__ __forceinline__ void umma_i8_ss_x8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n .reg .pred p, q;\n .reg .b32 alo, ahi, blo, bhi, t;\n .reg .b64 da, db;\n"
+        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
+        " mov.b64 {alo, ahi}, %1;\n mov.b64 {blo, bhi}, %2;\n"
+        " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        QDC_MMA_SS_STEP(16) QDC_MMA_SS_STEP(32) QDC_MMA_SS_STEP(48) QDC_MMA_SS_STEP(64)
+        QDC_MMA_SS_STEP(80) QDC_MMA_SS_STEP(96) QDC_MMA_SS_STEP(112)
+        "}\n"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+#define QDC_MMA_TS_STEP(OFFA, OFF)                                                             \
+    " add.u32 ta, %1, " #OFFA ";\n"                                                            \
+    " add.u32 t, blo, " #OFF ";\n mov.b64 db, {t, bhi};\n"                                     \
+    " tcgen05.mma.cta_group::1.kind::i8 [%0], [ta], db, %3, q;\n"
+__device__ __forceinline__ void umma_i8_ts_x8(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n .reg .pred p, q;\n .reg .b32 blo, bhi, t, ta;\n .reg .b64 db;\n"
+        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
+        " mov.b64 {blo, bhi}, %2;\n"
+        " tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n"
+        QDC_MMA_TS_STEP(8, 16) QDC_MMA_TS_STEP(16, 32) QDC_MMA_TS_STEP(24, 48) QDC_MMA_TS_STEP(32, 64)
+        QDC_MMA_TS_STEP(40, 80) QDC_MMA_TS_STEP(48, 96) QDC_MMA_TS_STEP(56, 112)
+        "}\n"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
 // 128 rows x 32 bytes of a K-major core-matrix image (the descriptor the MMA would take) -> 8 TMEM columns
 __device__ __forceinline__ void tmem_cp_128x256b(uint32_t tmem_dst, uint64_t sdesc) {
     asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(tmem_dst), "l"(sdesc) : "memory");
@@ -159,13 +196,36 @@ __device__ __forceinline__ double i64_to_f64(long long y) {
     return __longlong_as_double(y + 0x4338000000000000ll) - 6755399441055744.0;
 }
 
+// signed 128-bit integers as (lo, hi) pairs: everything inline, no helper calls, no local memory
+struct I128 { unsigned long long lo; long long hi; };
+__device__ __forceinline__ void i128_horner256(I128& y, long long a) {            // y = 256 y + a
+    y.hi = (long long)(((unsigned long long)y.hi << 8) | (y.lo >> 56));
+    const unsigned long long l8 = y.lo << 8, l = l8 + (unsigned long long)a;
+    y.hi += (a >> 63) + (l < l8 ? 1 : 0);
+    y.lo = l;
+}
+__device__ __forceinline__ void i128_add(I128& t, const I128& y) {
+    const unsigned long long l = t.lo + y.lo;
+    t.hi += y.hi + (l < t.lo ? 1 : 0);
+    t.lo = l;
+}
+// y = round_half_up(y / 2^sh), 0 <= sh <= 120
+__device__ __forceinline__ void i128_shr_round(I128& y, int sh) {
+    if (sh == 0) return;
+    I128 half;
+    if (sh <= 64) { half.lo = 1ull << (sh - 1); half.hi = 0; } else { half.lo = 0; half.hi = 1ll << (sh - 65); }
+    i128_add(y, half);
+    if (sh >= 64) { y.lo = (unsigned long long)(y.hi >> (sh - 64)); y.hi >>= 63; }
+    else { y.lo = (y.lo >> sh) | ((unsigned long long)y.hi << (64 - sh)); y.hi >>= sh; }
+}
+
 struct I8Args {
     const uint8_t* A8;       // [S stored][rows_pad][kd] core order
     const uint8_t* B8;
     size_t a_slice_stride, b_slice_stride;
     const double* row_scale; // 2^(e_r - 7) per row of the slab (padded rows: 0)
     const double2* colq;     // per padded column: (2^(f_c - 7), 2^(f_c - 7) * weight); padded columns: 0
-    const uint4* coltab;     // per padded column: (x_lo, x_hi | flags, weight | lsh << 8, 0)
+    const uint4* coltab;     // per padded column: (x_lo, x_hi | flags, weight << lsh, 1 << lsh)
     const int* gref;         // per 16 columns: reference exponent
     const double* A_src;     // the FP64 operands themselves (exact re-evaluation of flagged candidates)
     const double* B_src;
@@ -185,22 +245,29 @@ struct I8Args {
     double* partials;
 };
 
-// exact evaluation of the flagged outputs of one thread's 16 columns from the FP64 operands
-__device__ __noinline__ void emit_flagged(const I8Args& a, long long r_loc, long long c0, uint32_t flags, double f) {
-    const uint64_t rx = __ldg(a.tab.row_x + a.row_lo + r_loc);
-    const double* ar = a.A_src + r_loc * a.kdim_src;
+// exact evaluation of the flagged outputs of one thread's 16 columns from the FP64 operands.
+// (Everything by value: a reference to the kernel's parameter struct would force a local-memory
+// copy of it, and the hot loop would read its fields through LDL.)
+struct FlagCtx {
+    const double* A_src; const double* B_src; const uint4* coltab; const uint64_t* row_x;
+    long long n_cols; int kdim_src;
+};
+__device__ __noinline__ void emit_flagged(FlagCtx x, CandSink sink, long long r_tab, long long r_loc, long long c0,
+                                          uint32_t flags, double f) {
+    const uint64_t rx = __ldg(x.row_x + r_tab);
+    const double* ar = x.A_src + r_loc * x.kdim_src;
     while (flags) {
         const int c = __ffs(flags) - 1;
         flags &= flags - 1;
-        if (c0 + c >= a.n_cols) continue;
-        const double* br = a.B_src + (c0 + c) * a.kdim_src;
+        if (c0 + c >= x.n_cols) continue;
+        const double* br = x.B_src + (c0 + c) * x.kdim_src;
         double acc = 0.0;
-        for (int k = 0; k < a.kdim_src; ++k) acc = fma(ar[k], br[k], acc);
+        for (int k = 0; k < x.kdim_src; ++k) acc = fma(ar[k], br[k], acc);
         const double p = acc * f;
-        if (p > a.sink.threshold) {
-            const uint4 ct = __ldg(a.coltab + c0 + c);
+        if (p > sink.threshold) {
+            const uint4 ct = __ldg(x.coltab + c0 + c);
             const uint64_t cx = ((uint64_t)ct.y << 32 | ct.x) & ~(FLAG_ROW_BAD | FLAG_COL_BAD);
-            cand_emit(a.sink, rx | cx, p);
+            cand_emit(sink, rx | cx, p);
         }
     }
 }
@@ -236,7 +303,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = tmem_base_sh;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, tmem_base_sh, 0);     // (lane-0 broadcast: known warp-uniform)
 
     double cta_pwok = 0.0;                                // this thread's share of sum p w [independent]
     const int n_items = a.n_rb * a.n_chunks;
@@ -312,7 +379,10 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
                         const uint32_t tmem_d = tmem + (uint32_t)d * TN;
                         if (leader) {
-                            if (i < n_ta) {
+                            if (ksteps == 8) {                     // kdim = 256: one asm block per slice pair
+                                if (i < n_ta) umma_i8_ts_x8(tmem_d, tmem_a0 + (uint32_t)(i * 64), b_desc, idesc, j > 0 ? 1u : 0u);
+                                else umma_i8_ss_x8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
+                            } else if (i < n_ta) {
                                 const uint32_t ta = tmem_a0 + (uint32_t)(i * ksteps) * 8u;
                                 umma_i8_ts(tmem_d, ta, b_desc, idesc, j > 0 ? 1u : 0u);
 #pragma unroll
@@ -364,11 +434,35 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                     if (fr > 0.0) { tm = (int)(fr * 2147483648.0); tq = ex - 31 - 8 * (S - 1); }
                     else { tm = 0; tq = -(1 << 24); }                                // threshold 0: every output is a candidate
                 }
-                __int128 total = 0;
+                // Per order d one persistent 64-bit sum run[d] += D_d[c] m_c (the IMAD.WIDE chain accumulates
+                // straight into it).  Columns of one 16-group share the unit 2^(gref - 20 - 7); while the
+                // thread's next tile has the same gref nothing else happens.  When it changes (or after 16
+                // tiles: |run| < 16 tiles x 16 columns x 2^25 x 2^29 < 2^63) the orders are folded by a
+                // 128-bit Horner step, shifted to the unit of the largest column exponent and added to the
+                // 128-bit total, which enters FP64 once per work item.
+                I128 total = {0ull, 0ll};
+                long long run[S];
+#pragma unroll
+                for (int d = 0; d < S; ++d) run[d] = 0;
+                int cur_gr = E_ZERO, n_run = 0;
+                auto flush = [&]() {
+                    I128 y = {(unsigned long long)run[0], run[0] >> 63};
+#pragma unroll
+                    for (int d = 1; d < S; ++d) i128_horner256(y, run[d]);
+                    int sh = emax - cur_gr;
+                    sh = sh < 0 ? 0 : (sh > 120 ? 120 : sh);
+                    i128_shr_round(y, sh);
+                    i128_add(total, y);
+#pragma unroll
+                    for (int d = 0; d < S; ++d) run[d] = 0;
+                    n_run = 0;
+                };
                 for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
                     const int c0 = cb * TN + part * CPT;
                     const int gr = __ldg(a.gref + (c0 >> 4));
-                    int tcmp;                               // flag when D_0 >= tcmp
+                    if (gr != cur_gr || n_run == 16) { flush(); cur_gr = gr; }       // warp-uniform
+                    ++n_run;
+                    int tcmp;                               // an output may be a candidate when D_0 >= tcmp
                     {
                         const int sh = gr - tq;             // T 2^-gref = tm >> sh
                         const int tg = (gr == E_ZERO || sh < 0) ? 0x7fffffff : (sh > 31 ? 0 : (tm >> sh));
@@ -377,11 +471,10 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                     int m[CPT];                             // [independent] (w_r + w_c) << lsh_c
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) {
-                        const uint4 ct = __ldg(a.coltab + c0 + c);
+                        const uint4 ct = __ldg(a.coltab + c0 + c);      // (x_lo, x_hi | flags, w_c << lsh_c, 1 << lsh_c)
                         const bool ok = ((ct.x & (uint32_t)rf) | (ct.y & (uint32_t)(rf >> 32))) == 0u;
-                        m[c] = ok ? (w_r + (int)(ct.z & 0xffu)) << (ct.z >> 8) : 0;
+                        m[c] = ok ? w_r * (int)ct.w + (int)ct.z : 0;
                     }
-                    long long acc[S];
                     uint32_t flags = 0;
 #pragma unroll
                     for (int d = 0; d < S; ++d) {
@@ -393,26 +486,29 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&acc_empty[d]);
-                        long long s = 0;
+                        long long r = run[d];
 #pragma unroll
-                        for (int c = 0; c < CPT; ++c) {
-                            s += (long long)(int32_t)v[c] * (long long)m[c];
-                            if (d == 0 && (int32_t)v[c] >= tcmp) flags |= 1u << c;
+                        for (int c = 0; c < CPT; ++c) r += (long long)(int32_t)v[c] * (long long)m[c];
+                        run[d] = r;
+                        if (d == 0) {                       // candidate filter: one max tree, compares only on a hit
+                            int mx = (int32_t)v[0];
+#pragma unroll
+                            for (int c = 1; c < CPT; ++c) mx = max(mx, (int32_t)v[c]);
+                            if (mx >= tcmp) {
+#pragma unroll
+                                for (int c = 0; c < CPT; ++c)
+                                    if ((int32_t)v[c] >= tcmp) flags |= 1u << c;
+                            }
                         }
-                        acc[d] = s;
                     }
-                    // Horner over the orders in 128 bits, to the unit of the largest column exponent
-                    __int128 y = acc[0];
-#pragma unroll
-                    for (int d = 1; d < S; ++d) y = y * 256 + acc[d];
-                    int sh = emax - gr;
-                    sh = sh < 0 ? 0 : (sh > 120 ? 120 : sh);
-                    total += (y + (((__int128)1 << sh) >> 1)) >> sh;
-                    if (flags && row_ok)
-                        emit_flagged(a, r_loc, c0, flags, a.out_scale * inv_norm * ldexp(1.0, 8 * (S - 1)));
+                    if (flags && row_ok) {
+                        const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src};
+                        emit_flagged(fx, a.sink, a.row_lo + r_loc, r_loc, c0, flags, a.out_scale * inv_norm * ldexp(1.0, 8 * (S - 1)));
+                    }
                 }
+                flush();
                 // once per work item: the 128-bit total enters FP64 (unit 2^(emax - lsh_max - 7) rs)
-                const double tot = (double)(long long)(total >> 64) * 18446744073709551616.0 + (double)(unsigned long long)total;
+                const double tot = (double)total.hi * 18446744073709551616.0 + (double)total.lo;
                 cta_pwok += rs * ldexp(tot, emax - I8_LSH_MAX - 7);
             } else {
                 // ---------- per-output FP64 (the slab is stored) ----------

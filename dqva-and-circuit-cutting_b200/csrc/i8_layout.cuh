@@ -7,7 +7,7 @@
 //                                             serves 64-, 96- and 128-row tiles (rows_pad % 384 == 0)
 //   scale    f64   [rows_pad]                 2^(e_r - 7): x = scale * sum_i digit_i 256^-i
 //   colq     f64x2 [rows_pad]                 (scale, scale * weight)               (column role)
-//   coltab   u32x4 [rows_pad]                 (x_lo, x_hi | flags, weight | lsh << 8, 0) (column role)
+//   coltab   u32x4 [rows_pad]                 (x_lo, x_hi | flags, weight << lsh, 1 << lsh) (column role)
 //   gref     i32   [rows_pad / 16]            exponent of the largest row of each 16-row group
 //   part     f64   [PREP_GRID][2 kd + 4]      per-CTA column sums (sum x, sum weight x) and the
 //                                             statistics the error bounds need

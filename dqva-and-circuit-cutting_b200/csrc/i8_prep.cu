@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(PREP_THREADS, 2) i8_prep_kernel(const PrepArgs
                 if (a.coltab) {
                     uint64_t cx = FLAG_ROW_BAD | FLAG_COL_BAD;
                     if (live) cx = (a.xbits ? __ldg(a.xbits + r) : 0ull) | FLAG_ROW_BAD | ((wk >> 8) & 1u ? 0ull : FLAG_COL_BAD);
-                    a.coltab[r] = make_uint4((uint32_t)cx, (uint32_t)(cx >> 32), (wk & 0xffu) | ((uint32_t)lsh << 8), 0u);
+                    a.coltab[r] = make_uint4((uint32_t)cx, (uint32_t)(cx >> 32), (wk & 0xffu) << lsh, 1u << lsh);
                 }
                 if (live && !zero) {
                     const double p2 = pow2(f);

@@ -50,6 +50,36 @@ def chain3():
     return circ, frags, wpm
 
 
+def ckt5():
+    """The circuit of circuit-knitting-toolbox's own wire-cutting test
+    (circuit-knitting-toolbox/test/circuit_cutting/test_circuit_cutting.py:28-47: H, CX, T, RX, RY on 5
+    qubits) with its MANUAL cut `subcircuit_vertices=[[0, 1], [2, 3]]` (:69-72): the two-qubit gates in
+    circuit order are cx(0,1), cx(0,2) | cx(2,4), cx(2,3), so wire 2 is cut between cx(0,2) and
+    cx(2,4).  Known answer held by the reference (:77-82): the reconstruction equals the full
+    statevector distribution (mean squared error 0)."""
+    circ = QuantumCircuit(5, name="q")
+    for i in range(5):
+        circ.h(i)
+    circ.cx(0, 1)
+    for i in range(2, 5):
+        circ.t(i)
+    circ.cx(0, 2)
+    circ.rx(np.pi / 2, 4)
+    circ.rx(np.pi / 2, 0)
+    circ.rx(np.pi / 2, 1)
+    circ.cx(2, 4)
+    circ.t(0)
+    circ.t(1)
+    circ.cx(2, 3)
+    circ.ry(np.pi / 2, 4)
+    for i in range(5):
+        circ.h(i)
+    ops2 = [op for op in circ.data if circ.qubits[2] in op.qargs]
+    cut = next(i for i, op in enumerate(ops2) if op.name == "cx" and op.qargs[1] is circ.qubits[4])
+    frags, wpm = qcc.cut_circuit(circ, [(circ.qubits[2], cut)])
+    return circ, frags, wpm
+
+
 def ghz3():
     circ, cuts = _ghz3()
     frags, wpm = qcc.cut_circuit(circ, cuts)
@@ -63,5 +93,5 @@ def dqva6(max_cuts=2, seed=1, fused=False):
     return circ, frags, wpm, G
 
 
-CASES = {"ghz3": ghz3, "there_and_back": there_and_back, "chain3": chain3,
+CASES = {"ghz3": ghz3, "ckt5": ckt5, "there_and_back": there_and_back, "chain3": chain3,
          "dqva6": lambda: dqva6()[:3], "dqva6_fused": lambda: dqva6(2, 5, True)[:3]}

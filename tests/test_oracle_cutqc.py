@@ -15,7 +15,7 @@ from qdc_b200.cutqc import distributor as dist
 pytestmark = pytest.mark.skipif(not ref_cutqc.available(), reason="oracle/_ref binaries not built")
 
 
-@pytest.mark.parametrize("name,limit", [("ghz3", None), ("there_and_back", None), ("chain3", None),
+@pytest.mark.parametrize("name,limit", [("ghz3", None), ("ckt5", None), ("there_and_back", None), ("chain3", None),
                                         ("dqva6_fused", None), ("chain3", 4), ("dqva6", 5)])
 @pytest.mark.parametrize("et", [0, 1])
 def test_reference_c_pipeline_matches_oracle(tmp_path, name, limit, et):

@@ -162,3 +162,44 @@ def test_top_probs_and_better_strs():
     assert [t[0] for t in top] == ["0101", "1010"]            # stable: insertion order on ties
     assert mo.better_strs(top, G, "0001") == [("0101", 2), ("1010", 2)]
     assert abs(mo.avg_cost(probs, G) + (0.4 * 2 + 0.4 * 2 + 1e-6)) < 1e-15
+
+
+@pytest.mark.parametrize("mode", ["direct", "likely"])
+def test_ckt_manual_cut_known_answer(mode):
+    """Second reference-held known answer (circuit-knitting-toolbox/test/circuit_cutting/
+    test_circuit_cutting.py:28-47, 69-82): CKT's 5-qubit H / CX / T / RX / RY circuit, cut by hand
+    between its first two and last two CX gates, reconstructs the full statevector distribution with
+    mean squared error 0 -- here through the qsplit oracle (SIC preparations, network contraction)
+    and through the cutqc oracle (the path CKT itself wraps), both against oracle/statevector.py,
+    and against a dense 32 x 32 unitary assembled independently of the simulator's gate loop."""
+    import cutqc_cases as cc
+    from oracle import cutqc_oracle as co
+    circ, frags, wpm = cc.ckt5()
+    assert len(frags) == 2 and sum(len(p) - 1 for p in wpm.values()) == 1
+    n = circ.num_qubits
+    full = sv.probabilities(sv.simulate(n, circ.to_instructions()))
+    # independent dense check of the simulator on this gate set: U = product of kron-embedded gates
+    U = np.eye(1 << n, dtype=np.complex128)
+    for name, qubits, params in ((i[0], i[1], i[2]) for i in circ.to_instructions()):
+        if name == "cx":
+            c, t = qubits
+            G = np.zeros((1 << n, 1 << n))
+            for x in range(1 << n):
+                G[x ^ (((x >> c) & 1) << t), x] = 1.0
+        else:
+            (q,) = qubits
+            G = np.kron(np.kron(np.eye(1 << (n - 1 - q)), sv.gate_matrix(name, tuple(params))), np.eye(1 << q))
+        U = G @ U
+    assert np.abs(np.abs(U[:, 0]) ** 2 - full).max() < 1e-12
+    got = qo.sim_with_cutting(frags, wpm, mode=mode)
+    rebuilt = np.zeros(1 << n)
+    for bits, v in got.items():
+        rebuilt[int(bits, 2)] = v
+    assert np.mean((rebuilt - full) ** 2) < 1e-24 and np.abs(rebuilt - full).max() < 1e-10
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    counter, kron, terms, K, _ = co.evaluate(frags, cpm)
+    (schedule, vec, _), = co.post_process(list(circ.qubits), frags, cpm, counter, kron, terms, K)
+    rebuilt2 = np.zeros(1 << n)
+    for bits, v in co.reorder(list(circ.qubits), vec, cpm, frags, schedule).items():
+        rebuilt2[int(bits, 2)] = v
+    assert np.mean((rebuilt2 - full) ** 2) < 1e-24 and np.abs(rebuilt2 - full).max() < 1e-10
