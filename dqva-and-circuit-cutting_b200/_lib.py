@@ -65,6 +65,8 @@ SIGNATURES = {
     "qdc_khatri_rao": (C.c_int, [vp, c_i64, vp, c_i64, C.c_int, vp, vp]),
     "qdc_norm_workspace_doubles": (C.c_int, [C.c_int]),
     "qdc_contract_norm": (C.c_int, [vp, c_i64, vp, c_i64, C.c_int, C.c_double, vp, vp, vp]),
+    "qdc_contract_norm_static_max_kdim": (C.c_int, []),
+    "qdc_contract_norm_static": (C.c_int, [vp, c_i64, vp, c_i64, C.c_int, C.c_double, vp, vp]),
 }
 
 _lib = None

@@ -23,6 +23,7 @@
 // 2^-20 of the group's largest; the statistics below use the exponent actually applied).
 #include "qdc_common.cuh"
 #include "i8_layout.cuh"
+#include <mutex>
 
 namespace {
 
@@ -432,6 +433,57 @@ extern "C" int qdc_contract_norm(const double* d_A, int64_t n_rows_total, const 
     QDC_REQUIRE(kdim >= 1 && n_rows_total >= 0 && n_cols >= 0, "shape");
     double* pa = d_colsums;
     double* pb = d_colsums + (size_t)I8_PREP_GRID * kdim;
+    int rc = qdc_colsum(d_A, 0, n_rows_total, 0, 0, kdim, pa, stream);
+    if (rc != QDC_OK) return rc;
+    rc = qdc_colsum(d_Bt, 0, n_cols, 0, 0, kdim, pb, stream);
+    if (rc != QDC_OK) return rc;
+    norm_finalize_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(pa, pb, I8_PREP_GRID, kdim, scale, d_norm);
+    QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+// ---- the normalisation without any allocation -----------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid it):
+// the column-sum partials live in a file-scope device array instead of a caller workspace.
+// 2 operands x 296 partial rows x 256 columns x 8 B = 1 212 416 bytes, held by every GPU that loads
+// the library until the process exits.  All calls on a device share the array and it keeps the
+// last call's contents: every entry a call reads is written by that call first (each colsum CTA
+// stores its whole row of partials, zeros included), so nothing has to be cleared; two calls that
+// overlap on the GPU (different streams) race on it.
+constexpr int NORM_STATIC_MAX_KDIM = 256;
+static __device__ __align__(256) double g_norm_scratch[2 * I8_PREP_GRID * NORM_STATIC_MAX_KDIM];
+
+extern "C" int qdc_contract_norm_static_max_kdim(void) { return NORM_STATIC_MAX_KDIM; }
+
+extern "C" int qdc_contract_norm_static(const double* d_A, int64_t n_rows_total, const double* d_Bt,
+                                        int64_t n_cols, int kdim, double scale, double* d_norm, void* stream) {
+    QDC_REQUIRE(d_A && d_Bt && d_norm, "null buffer");
+    QDC_REQUIRE(kdim >= 1 && n_rows_total >= 0 && n_cols >= 0, "shape");
+    if (kdim > NORM_STATIC_MAX_KDIM) {
+        qdc_set_error("qdc_contract_norm_static: kdim %d exceeds the static scratch (at most %d columns); "
+                      "use qdc_contract_norm with a caller-owned workspace", kdim, NORM_STATIC_MAX_KDIM);
+        return QDC_ERR_ARG;
+    }
+    // In host code `g_norm_scratch` is only a stand-in for the symbol, not a device address: the
+    // address is looked up once per device, with that device current, and cached.
+    constexpr int MAX_DEVICES = 64;
+    static double* scratch_of[MAX_DEVICES] = {};
+    static std::mutex lock;
+    int dev = -1;
+    QDC_CHECK_CUDA(cudaGetDevice(&dev));
+    QDC_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "device ordinal");
+    double* scratch;
+    {
+        std::lock_guard<std::mutex> guard(lock);
+        if (!scratch_of[dev]) {
+            void* p = nullptr;
+            QDC_CHECK_CUDA(cudaGetSymbolAddress(&p, g_norm_scratch));
+            scratch_of[dev] = (double*)p;
+        }
+        scratch = scratch_of[dev];
+    }
+    double* pa = scratch;
+    double* pb = scratch + (size_t)I8_PREP_GRID * kdim;
     int rc = qdc_colsum(d_A, 0, n_rows_total, 0, 0, kdim, pa, stream);
     if (rc != QDC_OK) return rc;
     rc = qdc_colsum(d_Bt, 0, n_cols, 0, 0, kdim, pb, stream);

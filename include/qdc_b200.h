@@ -290,6 +290,22 @@ int qdc_contract_norm(const double* d_A, int64_t n_rows_total, const double* d_B
                       int64_t n_cols, int kdim, double scale, double* d_colsums,
                       double* d_norm, void* stream);
 
+/* qdc_contract_norm without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  Same inputs, same result (bit for bit) as
+ * qdc_contract_norm, but the column-sum partials live in a file-scope device array of the library
+ * (1 212 416 bytes per GPU that loads it, held until the process exits) instead of a caller
+ * workspace; the call itself performs no cudaMalloc / cudaFree and calls no allocating routine.
+ * Limit: kdim <= qdc_contract_norm_static_max_kdim() = 256; larger kdim returns QDC_ERR_ARG with a
+ * message naming the limit.  All calls on one GPU share the scratch: calls that overlap on the GPU
+ * (different streams) race -- keep them on one stream or order them with events.  The scratch keeps
+ * the previous call's contents; every entry a call reads it has written first, nothing needs
+ * clearing.  The first call on each device looks up the array's address (cudaGetSymbolAddress):
+ * make it outside stream capture. */
+int qdc_contract_norm_static_max_kdim(void);
+int qdc_contract_norm_static(const double* d_A, int64_t n_rows_total, const double* d_Bt,
+                             int64_t n_cols, int kdim, double scale, double* d_norm, void* stream);
+
 /* ---- CutQC-style stages (K3c, K4c, K6, K7) --------------------------------------------------
  * In-memory equivalents of the reference's four C programs (which talk through %e text files;
  * the CLI/file-compatible shims live in the Python package `qdc_b200.cutqc`).  Bit conventions:
