@@ -39,6 +39,8 @@ SIGNATURES = {
     "qdc_sv_pauli_tensor": (C.c_int, [vp, C.c_int, c_i64, C.c_uint64, C.c_int, C.c_int,
                                       C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int,
                                       C.POINTER(c_i64), vp, c_i64, vp]),
+    "qdc_ml_workspace_bytes": (c_i64, [c_i64, C.c_int]),
+    "qdc_ml_project": (C.c_int, [vp, c_i64, C.c_int, c_i64, vp, vp, vp, vp, vp, c_i64, vp, C.c_int, vp]),
     "qdc_reduce_partials": (C.c_int, []),
     "qdc_mis_reduce": (C.c_int, [vp, C.c_int, c_i64, c_i64, c_i64, vp, C.c_double,
                                  vp, vp, vp, vp, vp, vp, vp, vp, vp, c_i64, vp, vp]),

@@ -13,17 +13,21 @@
 //   |err| <= 2^(e_r + f_c) * scale * kdim * (S + 1.1) * 2^(-8S)
 //   S = 5: 1.4e-9, S = 6: 6.5e-12  (x 2^(e_r + f_c) * scale, kdim 256); FP64 itself: 2.8e-14.
 //
-// Structure (one persistent CTA per SM; tile = 128 rows x TN columns; 2 + TN / 4 warps):
+// Structure (one persistent CTA per SM; tile = 128 rows x TN columns; 4 + TN / 4 warps):
 //   warp 0  producer: bulk async copies (cp.async.bulk + mbarrier complete_tx).  The S slices of
 //           a 128-row block of A (S * 128 * kdim bytes) are loaded once and stay resident while
 //           the CTA walks its column blocks; the slices t_j of a TN-column block stream through a
 //           ring whose depth is whatever shared memory is left (2..8 stages).
-//   warp 1  MMA issuer (one lane): for j (ring stage) for i <= S-1-j: 128 x TN x 32 tcgen05.mma steps
-//           into accumulator d = i + j (TMEM columns TN d .. TN d + TN - 1); order d is complete
-//           after the first pair of group j = d and is committed to its own mbarrier, so the
-//           epilogue drains orders while later pairs still run.  Where TMEM columns are left, the
-//           leading resident slices are copied there (tcgen05.cp) and their pairs take A from tensor memory.
-//   warps 2..  epilogue (4 TMEM lane quarters x TN / 16 column groups of 16), two forms:
+//   warps 1-3  MMA issuers (one lane each): for j (ring stage) for i <= S-1-j: the 128 x TN x 32
+//           tcgen05.mma steps of slice pair (i, j) go into accumulator d = i + j (TMEM columns
+//           TN d .. TN d + TN - 1) and are issued by the warp that owns order d (owner_of: S = 5 ->
+//           {4}, {3, 0}, {2, 1}, five pairs each).  Order d is complete after the first pair of group
+//           j = d and is committed to its own mbarrier, so the epilogue drains orders while later
+//           pairs still run.  Where TMEM columns are left, the leading resident slices are copied
+//           there (tcgen05.cp, by issuer 0) and their pairs take A from tensor memory.  Why three
+//           warps: one warp needed ~880 instructions per tile around the 120 MMAs and never waited
+//           on anything -- the tensor pipe waited for it (profiles/r2_i8_issue_bound.md).
+//   warps 4..  epilogue (4 TMEM lane quarters x TN / 16 column groups of 16), two forms:
 //     EPI 0 (nothing stored): ALL-INTEGER.  Scalar FP64 all but stops while the tensor pipe runs
 //           int8 MMAs (profiles/r1_mma_dp_contention_probe.log: DFMA 64 -> 0.6 per clk per SM; IMAD is
 //           unaffected), so the steady state has no FP64 instruction at all.  Per output and order
@@ -41,6 +45,7 @@
 #include "qdc_common.cuh"
 #include "i8_layout.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 int qdc_i8_launch_plan(const void* d_opA, int64_t n_rows, const void* d_opB, int64_t n_cols, int kdim, int n_stored,
                        int n_slices, double tol, int n_nodes, double scale, int norm_mode, const double* d_norm_in,
@@ -56,51 +61,73 @@ constexpr int TM = 128;                       // tile rows
 constexpr int CPT = 16;                       // columns per epilogue thread
 constexpr int MAX_S = 6;
 constexpr int MAX_STAGES = 8;                 // ring of streamed-operand slices
-constexpr int FIRST_EPI_WARP = 2;             // warp 0: producer, warp 1: MMA issuer
+constexpr int N_ISSUERS = 3;                  // MMA-issuing warps; each owns whole accumulator orders (owner_of)
+constexpr int FIRST_EPI_WARP = 1 + N_ISSUERS; // warp 0: producer, warps 1..3: MMA issuers
+// Which issuer warp owns order d (all pairs (i, j) with i + j = d): orders by decreasing pair count to the
+// least loaded warp.  S = 5: {4}, {3, 0}, {2, 1} = 5 / 5 / 5 pairs; S = 6: {5, 0}, {4, 1}, {3, 2} = 7 / 7 / 7.
+constexpr int owner_of(int S, int d) {
+    int load[N_ISSUERS] = {};
+    int own = 0;
+    for (int dd = S - 1; dd >= 0; --dd) {
+        int w = 0;
+        for (int k = 1; k < N_ISSUERS; ++k)
+            if (load[k] < load[w]) w = k;
+        load[w] += dd + 1;
+        if (dd == d) own = w;
+    }
+    return own;
+}
 constexpr int MAX_WARPS = 32;
 constexpr int TMEM_COLS = 512;
 constexpr int E_ZERO = -(1 << 20);            // as in i8_prep.cu
 constexpr int D0_MARGIN = (1 << 15) + (1 << 9);   // |X / 256^(S-1) - D_0| < 2^15.01
+constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = 1, BAR_B_FULL = 2, BAR_B_EMPTY = BAR_B_FULL + 8, BAR_ACC_FULL = BAR_B_EMPTY + 8,
+              BAR_ACC_EMPTY = BAR_ACC_FULL + 6, BAR_TA_FULL = BAR_ACC_EMPTY + 6, BAR_TA_FREE = BAR_TA_FULL + 1,
+              N_BARS = BAR_TA_FREE + 1;                                            // (8 = MAX_STAGES, 6 = MAX_S)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+// All barriers live in ONE shared array and are addressed as base + 8 k, the base computed once per
+// thread: taking the address of a __shared__ variable at every use costs an S2UR SR_CgaCtaId (a
+// ~100-clock special-register read) plus address arithmetic each time -- measured at 11 % of the
+// MMA-issuing warp's time when every commit did it (profiles/r2_i8_issue_bound.md).
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ uint32_t mbar_try(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity) {
     uint32_t done;
     asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
-                 : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     return done;
 }
 // A barrier that never completes is a protocol bug: trap (the launch fails with an error) instead
 // of hanging the device.  try_wait suspends the thread for a while by itself, so the limits below
 // are seconds.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try(bar, parity))
         if (++spins > (1u << 26)) __trap();
 }
 // polling costs shared-memory cycles the tensor core wants for its operands: waiters that are
 // not on the critical path back off between polls
-__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t ns) {
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, uint32_t ns) {
     uint32_t spins = 0;
     while (!mbar_try(bar, parity)) {
         __nanosleep(ns);
         if (++spins > (1u << 25)) __trap();
     }
 }
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
@@ -129,43 +156,52 @@ __device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uin
         " tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n}\n"
         ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
-// The 8 k steps of one slice pair at kdim = 256, issued from ONE asm block.  A k step of 32 advances a
-// descriptor's address field (bits 0-13 of the low word, 16-byte units) by 16; the field cannot carry
-// (shared memory ends below 2^14 units), so a single 32-bit add on the low word makes the next
-// descriptor.  Written this way on purpose: when the adds are visible to the compiler it hoists all
-// S x 8 loop-invariant descriptors out of the tile loop into VECTOR registers and pays two R2UR per
-// descriptor per use -- 19 issue slots per MMA on the one warp that issues them, which held the
-// tensor pipe at 54 % (profiles/r2_i8_issue_bound.md).  Here: 2 adds + 1 MMA per step.
-#define QDC_MMA_SS_STEP(OFF)                                                                   \
-    " add.u32 t, alo, " #OFF ";\n mov.b64 da, {t, ahi};\n"                                     \
-    " add.u32 t, blo, " #OFF ";\n mov.b64 db, {t, bhi};\n"                                     \
-    " tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %3, q;\n"
-__device__ __forceinline__ void umma_i8_ss_x8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+// The 8 k steps of one slice pair at kdim = 256, issued from ONE asm block whose only register
+// inputs are the same for every pair of a tile (TMEM base, descriptor of slice 0, descriptor of the
+// streamed stage, instruction descriptor); slice, order and k step enter as immediates.  A k step of
+// 32 advances a descriptor's address field (16-byte units) by 16, a slice by TM kdim / 16; the
+// field cannot carry out of its 14 bits (shared memory ends below 2^14 units), so plain 64-bit adds
+// on the descriptor make the next one -- one UIADD3.64 each, no high-word copies.  Written this way
+// on purpose: when the adds are visible to the compiler it hoists all S x 8 loop-invariant
+// descriptors out of the tile loop into VECTOR registers and pays two R2UR per descriptor per use
+// (19 issue slots per MMA on the one warp that issues them, profiles/r2_i8_issue_bound.md).
+// (The adds form an in-place chain: only one descriptor pair is live at a time.  With independent
+// adds ptxas computes all 16 descriptors of a block first, runs out of the 63 uniform registers,
+// spills them to vector registers and pays R2UR again.)
+#define QDC_SS_STEP " add.s64 da, da, 16;\n add.s64 db, db, 16;\n tcgen05.mma.cta_group::1.kind::i8 [d], da, db, %3, q;\n"
+template <int A_OFF, int D_OFF, bool ACC>
+__device__ __forceinline__ void umma_pair_ss(uint32_t tmem, uint64_t a_desc0, uint64_t b_desc, uint32_t idesc) {
     asm volatile(
-        "{\n .reg .pred p, q;\n .reg .b32 alo, ahi, blo, bhi, t;\n .reg .b64 da, db;\n"
-        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
-        " mov.b64 {alo, ahi}, %1;\n mov.b64 {blo, bhi}, %2;\n"
-        " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
-        QDC_MMA_SS_STEP(16) QDC_MMA_SS_STEP(32) QDC_MMA_SS_STEP(48) QDC_MMA_SS_STEP(64)
-        QDC_MMA_SS_STEP(80) QDC_MMA_SS_STEP(96) QDC_MMA_SS_STEP(112)
+        "{\n .reg .pred p, q;\n .reg .b32 d;\n .reg .b64 da, db;\n"
+        " setp.ne.b32 p, %5, 0;\n setp.eq.b32 q, %3, %3;\n"
+        " add.u32 d, %0, %4;\n add.s64 da, %1, %6;\n mov.b64 db, %2;\n"
+        " tcgen05.mma.cta_group::1.kind::i8 [d], da, db, %3, p;\n"
+        QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP
         "}\n"
-        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+        ::"r"(tmem), "l"(a_desc0), "l"(b_desc), "r"(idesc), "n"(D_OFF), "n"(ACC ? 1 : 0), "n"(A_OFF) : "memory");
 }
-#define QDC_MMA_TS_STEP(OFFA, OFF)                                                             \
-    " add.u32 ta, %1, " #OFFA ";\n"                                                            \
-    " add.u32 t, blo, " #OFF ";\n mov.b64 db, {t, bhi};\n"                                     \
-    " tcgen05.mma.cta_group::1.kind::i8 [%0], [ta], db, %3, q;\n"
-__device__ __forceinline__ void umma_i8_ts_x8(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+#define QDC_TS_STEP " add.u32 ta, ta, 8;\n add.s64 db, db, 16;\n tcgen05.mma.cta_group::1.kind::i8 [d], [ta], db, %2, q;\n"
+template <int TA_OFF, int D_OFF, bool ACC>
+__device__ __forceinline__ void umma_pair_ts(uint32_t tmem, uint64_t b_desc, uint32_t idesc) {
     asm volatile(
-        "{\n .reg .pred p, q;\n .reg .b32 blo, bhi, t, ta;\n .reg .b64 db;\n"
-        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
-        " mov.b64 {blo, bhi}, %2;\n"
-        " tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n"
-        QDC_MMA_TS_STEP(8, 16) QDC_MMA_TS_STEP(16, 32) QDC_MMA_TS_STEP(24, 48) QDC_MMA_TS_STEP(32, 64)
-        QDC_MMA_TS_STEP(40, 80) QDC_MMA_TS_STEP(48, 96) QDC_MMA_TS_STEP(56, 112)
+        "{\n .reg .pred p, q;\n .reg .b32 d, ta;\n .reg .b64 db;\n"
+        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %2, %2;\n"
+        " add.u32 d, %0, %3;\n add.u32 ta, %0, %5;\n mov.b64 db, %1;\n"
+        " tcgen05.mma.cta_group::1.kind::i8 [d], [ta], db, %2, p;\n"
+        QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP
         "}\n"
-        ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+        ::"r"(tmem), "l"(b_desc), "r"(idesc), "n"(D_OFF), "n"(ACC ? 1 : 0), "n"(TA_OFF) : "memory");
 }
+
+// compile-time loop: f(std::integral_constant<int, I>) for I in [I0, N)
+template <int I0, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (I0 < N) {
+        f(std::integral_constant<int, I0>{});
+        static_for<I0 + 1, N>(f);
+    }
+}
+
 // 128 rows x 32 bytes of a K-major core-matrix image (the descriptor the MMA would take) -> 8 TMEM columns
 __device__ __forceinline__ void tmem_cp_128x256b(uint32_t tmem_dst, uint64_t sdesc) {
     asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(tmem_dst), "l"(sdesc) : "memory");
@@ -232,7 +268,6 @@ struct I8Args {
     int kdim_src;
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
     int n_rb, n_cb, kdim, n_stages;
-    int tmem_a;              // 1: leading resident slices are read from tensor memory (QDC_I8_TMEM_A=0 turns it off)
     int n_chunks, chunk_len;  // work item = (row block, chunk of chunk_len column blocks); item = chunk * n_rb + rb
     int check_slices;        // 1: run only if res[I8_RES_SLICES] == S (the count was chosen on the device)
     double out_scale;        // scale * 256^-(S-1)
@@ -277,8 +312,12 @@ template <int S, int TN, int EPI>
 __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) contract_i8_kernel(const I8Args a) {
     constexpr int N_EPI_WARPS = 4 * (TN / CPT);
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t a_full, a_empty, b_full[MAX_STAGES], b_empty[MAX_STAGES],
-        acc_full[MAX_S], acc_empty[MAX_S];
+    __shared__ __align__(8) uint64_t bars[N_BARS];
+    uint32_t bar0 = smem_u32(bars);
+    asm volatile("" : "+r"(bar0));                     // opaque: never re-derived from the symbol (S2UR + arithmetic per use)
+    const uint32_t a_full = bar0 + 8u * BAR_A_FULL, a_empty = bar0 + 8u * BAR_A_EMPTY;
+    const uint32_t b_full0 = bar0 + 8u * BAR_B_FULL, b_empty0 = bar0 + 8u * BAR_B_EMPTY;
+    const uint32_t acc_full0 = bar0 + 8u * BAR_ACC_FULL, acc_empty0 = bar0 + 8u * BAR_ACC_EMPTY;
     __shared__ uint32_t tmem_base_sh;
     __shared__ double scratch[3 * MAX_WARPS];
 
@@ -287,13 +326,15 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int kdim = a.kdim;
     const uint32_t a_slice_bytes = TM * kdim, b_slice_bytes = TN * kdim;
-    uint8_t* sA = smem;                                   // [S][a_slice_bytes]
-    uint8_t* sB = smem + (size_t)S * a_slice_bytes;       // [n_stages][b_slice_bytes]
+    uint32_t sA_addr = smem_u32(smem);                    // [S][a_slice_bytes], then [n_stages][b_slice_bytes]
+    asm volatile("" : "+r"(sA_addr));
+    const uint32_t sB_addr = sA_addr + (uint32_t)S * a_slice_bytes;
 
     if (tid == 0) {
-        mbar_init(&a_full, 1); mbar_init(&a_empty, 1);
-        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-        for (int d = 0; d < MAX_S; ++d) { mbar_init(&acc_full[d], 1); mbar_init(&acc_empty[d], N_EPI_WARPS); }
+        mbar_init(a_full, 1); mbar_init(a_empty, N_ISSUERS);
+        mbar_init(bar0 + 8u * BAR_TA_FULL, 1); mbar_init(bar0 + 8u * BAR_TA_FREE, N_ISSUERS - 1);
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(b_full0 + 8u * s, 1); mbar_init(b_empty0 + 8u * s, N_ISSUERS); }
+        for (int d = 0; d < MAX_S; ++d) { mbar_init(acc_full0 + 8u * d, 1); mbar_init(acc_empty0 + 8u * d, N_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -315,31 +356,37 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
         for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
             const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
             const int cb1 = min(a.n_cb, cb0 + a.chunk_len);
-            mbar_wait_relaxed(&a_empty, rb_phase ^ 1u, 200);
+            mbar_wait_relaxed(a_empty, rb_phase ^ 1u, 200);
             if (leader) {
-                mbar_expect_tx(&a_full, (uint32_t)S * a_slice_bytes);
+                mbar_expect_tx(a_full, (uint32_t)S * a_slice_bytes);
 #pragma unroll
                 for (int i = 0; i < S; ++i)
-                    bulk_g2s(sA + (size_t)i * a_slice_bytes,
-                             a.A8 + (size_t)i * a.a_slice_stride + (size_t)rb * a_slice_bytes, a_slice_bytes, &a_full);
+                    bulk_g2s(sA_addr + (uint32_t)i * a_slice_bytes,
+                             a.A8 + (size_t)i * a.a_slice_stride + (size_t)rb * a_slice_bytes, a_slice_bytes, a_full);
             }
             for (int cb = cb0; cb < cb1; ++cb) {
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
-                    mbar_wait_relaxed(&b_empty[b_stage], b_phase ^ 1u, 64);
+                    mbar_wait_relaxed(b_empty0 + 8u * b_stage, b_phase ^ 1u, 64);
                     if (leader) {
-                        mbar_expect_tx(&b_full[b_stage], b_slice_bytes);
-                        bulk_g2s(sB + (size_t)b_stage * b_slice_bytes,
-                                 a.B8 + (size_t)j * a.b_slice_stride + (size_t)cb * b_slice_bytes, b_slice_bytes, &b_full[b_stage]);
+                        mbar_expect_tx(b_full0 + 8u * b_stage, b_slice_bytes);
+                        bulk_g2s(sB_addr + (uint32_t)b_stage * b_slice_bytes,
+                                 a.B8 + (size_t)j * a.b_slice_stride + (size_t)cb * b_slice_bytes, b_slice_bytes, b_full0 + 8u * b_stage);
                     }
                     if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
                 }
             }
         }
-    } else if (warp == 1) {
-        // ================= MMA issuer =================
-        // The whole warp walks the loops (so that addresses and descriptors live in uniform
-        // registers); one elected lane issues the MMAs and the commits.
+    } else if (warp < FIRST_EPI_WARP) {
+        // ================= MMA issuers =================
+        // N_ISSUERS warps walk the same loops; issuer `iw` issues the slice pairs of the orders it owns
+        // (MMAs into different accumulators are independent, so the warps need no ordering among
+        // themselves) and EVERY issuer commits every ring stage and the end of every work item, so
+        // those barriers count N_ISSUERS arrivals whatever the pair split.  One issuing warp was the
+        // bottleneck: ~880 instructions per tile around 120 MMAs at ~10 clocks each
+        // (profiles/r2_i8_issue_bound.md).  In each warp all lanes walk the loops (addresses and
+        // descriptors stay warp-uniform); one elected lane issues the MMAs and the commits.
+        const int iw = warp - 1;
         const bool leader = elect_one();
         // D = s32, A = B = signed bytes (bits 7, 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
         const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
@@ -347,61 +394,111 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
         // descriptor of address 0; a slice at byte address x is desc0 + (x >> 4), and a step of
         // 32 k (two 16-byte chunks = 256 bytes in core-matrix order) adds 16
         const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
-        const uint64_t a_desc0 = desc0 + (smem_u32(sA) >> 4), b_desc0 = desc0 + (smem_u32(sB) >> 4);
-        // TMEM columns [S * TN, 512) hold the first n_ta resident slices (kdim / 4 columns each)
-        const uint32_t tmem_a0 = tmem + (uint32_t)(S * TN);
-        const int n_ta = a.tmem_a ? min(S, (TMEM_COLS - S * TN) / (kdim / 4)) : 0;
+        const uint64_t a_desc0 = desc0 + (sA_addr >> 4), b_desc0 = desc0 + (sB_addr >> 4);
+        const uint32_t ta_full = bar0 + 8u * BAR_TA_FULL, ta_free = bar0 + 8u * BAR_TA_FREE;
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
-            const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
-            mbar_wait(&a_full, rb_phase);
-            tc_fence_after();
-            // tcgen05 operations of one thread execute in issue order, so the copies wait for the
-            // previous item's MMAs.
-            if (leader)
-                for (int i = 0; i < n_ta; ++i)
-                    for (int ks = 0; ks < ksteps; ++ks)
-                        tmem_cp_128x256b(tmem_a0 + (uint32_t)(i * ksteps + ks) * 8u,
-                                         a_desc0 + (uint32_t)i * (a_slice_bytes >> 4) + ks * 16);
-            for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) {
-                    mbar_wait(&b_full[b_stage], b_phase);
-                    tc_fence_after();
-                    const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * (b_slice_bytes >> 4);
-#pragma unroll
-                    for (int i = 0; i + j < S; ++i) {
-                        const int d = i + j;
-                        if (j == 0) {                              // first touch of order d in this tile
-                            mbar_wait(&acc_empty[d], tile_phase ^ 1u);
-                            tc_fence_after();
-                        }
-                        const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
-                        const uint32_t tmem_d = tmem + (uint32_t)d * TN;
+        if (ksteps == 8) {
+            // ---- kdim = 256: everything but the ring stage is a compile-time constant ----
+            // TMEM columns [S TN, 512) hold the first NTA resident slices (64 columns each); their pairs
+            // take A from tensor memory and read only the streamed tile from shared memory
+            constexpr int NTA = (TMEM_COLS - S * TN) / 64 < S ? (TMEM_COLS - S * TN) / 64 : S;
+            constexpr uint32_t A_SLICE16 = TM * 256 / 16, B_SLICE16 = TN * 256 / 16;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+                const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
+                mbar_wait(a_full, rb_phase);
+                tc_fence_after();
+                if constexpr (NTA > 0) {
+                    if (iw == 0) {
+                        // issuer 0 copies the slices once the other issuers' MMAs of the previous item are
+                        // done with them (its own tcgen05 operations execute in issue order anyway)
+                        mbar_wait(ta_free, rb_phase ^ 1u);
+                        tc_fence_after();
                         if (leader) {
-                            if (ksteps == 8) {                     // kdim = 256: one asm block per slice pair
-                                if (i < n_ta) umma_i8_ts_x8(tmem_d, tmem_a0 + (uint32_t)(i * 64), b_desc, idesc, j > 0 ? 1u : 0u);
-                                else umma_i8_ss_x8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
-                            } else if (i < n_ta) {
-                                const uint32_t ta = tmem_a0 + (uint32_t)(i * ksteps) * 8u;
-                                umma_i8_ts(tmem_d, ta, b_desc, idesc, j > 0 ? 1u : 0u);
-#pragma unroll
-                                for (int ks = 1; ks < 8; ++ks)
-                                    if (ks < ksteps) umma_i8_ts(tmem_d, ta + ks * 8, b_desc + ks * 16, idesc, 1u);
-                            } else {
-                                umma_i8(tmem_d, a_desc, b_desc, idesc, j > 0 ? 1u : 0u);
-#pragma unroll
-                                for (int ks = 1; ks < 8; ++ks)
-                                    if (ks < ksteps) umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, 1u);
-                            }
-                            if (i == 0) umma_commit(&acc_full[j]);     // order j is complete
+                            for (int i = 0; i < NTA; ++i)
+                                for (int ks = 0; ks < 8; ++ks)
+                                    tmem_cp_128x256b(tmem + (uint32_t)(S * TN + (i * 8 + ks) * 8), a_desc0 + (uint32_t)i * A_SLICE16 + ks * 16);
+                            umma_commit(ta_full);
                         }
+                    } else {
+                        mbar_wait(ta_full, rb_phase);
+                        tc_fence_after();
                     }
-                    if (leader) umma_commit(&b_empty[b_stage]);
-                    if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
+                }
+                for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
+                    static_for<0, S>([&](auto jc) {
+                        constexpr int j = decltype(jc)::value;
+                        mbar_wait(b_full0 + 8u * b_stage, b_phase);
+                        tc_fence_after();
+                        const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * B_SLICE16;
+                        static_for<0, S - j>([&](auto ic) {
+                            constexpr int i = decltype(ic)::value, d = i + j;
+                            if (iw == owner_of(S, d)) {
+                                if (j == 0) {                      // first touch of order d in this tile
+                                    mbar_wait(acc_empty0 + 8u * d, tile_phase ^ 1u);
+                                    tc_fence_after();
+                                }
+                                if (leader) {
+                                    if constexpr (i < NTA) umma_pair_ts<S * TN + i * 64, d * TN, (j > 0)>(tmem, b_desc, idesc);
+                                    else umma_pair_ss<i * (int)A_SLICE16, d * TN, (j > 0)>(tmem, a_desc0, b_desc, idesc);
+                                    if (i == 0) umma_commit(acc_full0 + 8u * j);   // order j is complete
+                                }
+                            }
+                        });
+                        if (leader) umma_commit(b_empty0 + 8u * b_stage);
+                        if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
+                    });
+                }
+                if (leader) {
+                    umma_commit(a_empty);
+                    if (NTA > 0 && iw != 0) umma_commit(ta_free);
                 }
             }
-            if (leader) umma_commit(&a_empty);
+        } else {
+            // ---- any kdim <= 256 (multiple of 32): the same walk with run-time step counts, all pairs
+            // issued by issuer 0 (the others only keep the barrier counts) ----
+            const uint32_t tmem_a0 = tmem + (uint32_t)(S * TN);
+            const int n_ta = min(S, (TMEM_COLS - S * TN) / (kdim / 4));
+            const bool mine = iw == 0;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+                const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
+                mbar_wait(a_full, rb_phase);
+                tc_fence_after();
+                if (leader && mine)
+                    for (int i = 0; i < n_ta; ++i)
+                        for (int ks = 0; ks < ksteps; ++ks)
+                            tmem_cp_128x256b(tmem_a0 + (uint32_t)(i * ksteps + ks) * 8u,
+                                             a_desc0 + (uint32_t)i * (a_slice_bytes >> 4) + ks * 16);
+                for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
+                    for (int j = 0; j < S; ++j) {
+                        mbar_wait(b_full0 + 8u * b_stage, b_phase);
+                        tc_fence_after();
+                        const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * (b_slice_bytes >> 4);
+                        for (int i = 0; mine && i + j < S; ++i) {
+                            const int d = i + j;
+                            if (j == 0) {
+                                mbar_wait(acc_empty0 + 8u * d, tile_phase ^ 1u);
+                                tc_fence_after();
+                            }
+                            const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
+                            const uint32_t tmem_d = tmem + (uint32_t)d * TN;
+                            if (leader) {
+                                if (i < n_ta) {
+                                    const uint32_t ta = tmem_a0 + (uint32_t)(i * ksteps) * 8u;
+                                    for (int ks = 0; ks < ksteps; ++ks)
+                                        umma_i8_ts(tmem_d, ta + ks * 8, b_desc + ks * 16, idesc, (j > 0 || ks > 0) ? 1u : 0u);
+                                } else {
+                                    for (int ks = 0; ks < ksteps; ++ks)
+                                        umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, (j > 0 || ks > 0) ? 1u : 0u);
+                                }
+                                if (i == 0) umma_commit(acc_full0 + 8u * j);
+                            }
+                        }
+                        if (leader) umma_commit(b_empty0 + 8u * b_stage);
+                        if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
+                    }
+                }
+                if (leader) umma_commit(a_empty);
+            }
         }
     } else if (warp >= FIRST_EPI_WARP) {
         // ================= epilogue =================
@@ -478,14 +575,14 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                     uint32_t flags = 0;
 #pragma unroll
                     for (int d = 0; d < S; ++d) {
-                        mbar_wait_relaxed(&acc_full[d], tile_phase, 32);
+                        mbar_wait_relaxed(acc_full0 + 8u * d, tile_phase, 32);
                         tc_fence_after();
                         uint32_t v[CPT];
                         tmem_ld16(lane_base + (uint32_t)(d * TN), v);
                         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                         tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc_empty[d]);
+                        if (lane == 0) mbar_arrive(acc_empty0 + 8u * d);
                         long long r = run[d];
 #pragma unroll
                         for (int c = 0; c < CPT; ++c) r += (long long)(int32_t)v[c] * (long long)m[c];
@@ -526,7 +623,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
 #pragma unroll
                     for (int d = 0; d < S; d += 2) {
                         const bool two = d + 1 < S;
-                        mbar_wait_relaxed(&acc_full[two ? d + 1 : d], tile_phase, 32);
+                        mbar_wait_relaxed(acc_full0 + 8u * (two ? d + 1 : d), tile_phase, 32);
                         tc_fence_after();
                         uint32_t v0[CPT], v1[CPT];
                         tmem_ld16(lane_base + (uint32_t)(d * TN), v0);
@@ -535,8 +632,8 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) {
-                            mbar_arrive(&acc_empty[d]);
-                            if (two) mbar_arrive(&acc_empty[d + 1]);
+                            mbar_arrive(acc_empty0 + 8u * d);
+                            if (two) mbar_arrive(acc_empty0 + 8u * (d + 1));
                         }
 #pragma unroll
                         for (int c = 0; c < CPT; ++c) {
@@ -642,7 +739,6 @@ int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
             if (waste < best - 1e-9) { best = waste; n_chunks = c; }
         }
     }
-    { const char* m = getenv("QDC_I8_TMEM_A"); a.tmem_a = m ? atoi(m) : 1; }
     a.n_chunks = n_chunks;
     a.chunk_len = (int)((n_cb + n_chunks - 1) / n_chunks);
     a.out_scale = ldexp(a.out_scale, -8 * (n_slices - 1));   // the row / column factors carry 2^(e - 7)

@@ -531,43 +531,93 @@ def direct_fragment_model(tomography_data, discard_poor_data=False, rank_cutoff=
     return _model_from_counts(tomography_data, torch.device("cuda"), rank_cutoff)
 
 
-def maximum_likelihood_model(choi_matrix):
-    """Nearest positive-semidefinite model (:320-356): eigen-decompose every block, sort ALL
-    eigenvalues of the fragment together, zero the negative ones while spreading their deficit
-    over the rest, rebuild.  Batched on the model's device; the sequential clipping loop is the
-    closed form  adjusted_j = s_j + (sum_{i<j} s_i) / (dim - j)  (each step preserves the total).
-    The rebuilt block is the complex conjugate of V diag V^+, as in the reference (:45-46,
-    354-356)."""
+_ML_TABLES = {}
+
+
+def _ml_tables(n_prep, n_meas, dev):
+    """Sparse forms of the Pauli <-> Choi-matrix change of basis for `qdc_ml_project`, derived from
+    `_pauli_choi_basis` (so the axis and transposition conventions live in one place): every entry
+    (i, j) of a block touches exactly D = 2^q tensor components and every component D entries.
+      fwd: Lambda[i, j]  = sum_t T[fwd_k[i D + j, t]] * fwd_c[i D + j, t]         (2^-q folded in)
+      inv: T'[kappa]     = Re sum_t inv_c[kappa, t] * L'[j_t, i_t],  inv_ij = (i << 8) | j"""
+    key = (n_prep, n_meas, str(dev))
+    if key not in _ML_TABLES:
+        B = _pauli_choi_basis(n_prep, n_meas)
+        K, D, _ = B.shape
+        q = n_prep + n_meas
+        fwd_k = np.zeros((D * D, D), dtype=np.int32)
+        fwd_c = np.zeros((D * D, D, 2))
+        for i in range(D):
+            for j in range(D):
+                ks = np.nonzero(B[:, i, j])[0]
+                assert len(ks) == D
+                fwd_k[i * D + j] = ks
+                c = B[ks, i, j] / 2 ** q
+                fwd_c[i * D + j, :, 0], fwd_c[i * D + j, :, 1] = c.real, c.imag
+        inv_ij = np.zeros((K, D), dtype=np.int32)
+        inv_c = np.zeros((K, D, 2))
+        for k in range(K):
+            ii, jj = np.nonzero(B[k])
+            assert len(ii) == D
+            inv_ij[k] = (ii << 8) | jj
+            c = B[k, ii, jj]
+            inv_c[k, :, 0], inv_c[k, :, 1] = c.real, c.imag
+        _ML_TABLES[key] = tuple(torch.as_tensor(x, device=dev).contiguous() for x in (fwd_k, fwd_c, inv_ij, inv_c))
+    return _ML_TABLES[key]
+
+
+def maximum_likelihood_model(choi_matrix, force_full=False):
+    """Nearest positive-semidefinite model (:320-356) on the device (`qdc_ml_project`,
+    csrc/ml_project.cu): every Choi block is eigen-decomposed by a one-warp Jacobi, ALL eigenvalues
+    of the fragment are clipped together -- the reference's sequential walk (:333-343) is
+    soft-thresholding lambda' = max(lambda - t0, 0) with t0 the root of sum max(lambda - t, 0) =
+    sum lambda, found by Newton steps over grid-wide reductions -- and the blocks are rebuilt as the
+    complex conjugate of V diag V^+, as the reference's `to_projector` does (:45-46, 354-356).  When a
+    Cholesky test finds every block positive semidefinite to 1e-14 of its trace (exact,
+    infinite-shot data), t0 = 0 and only the conjugate is taken; `force_full=True` skips that test.
+    `model.ml_info[s]` holds (needed the full path, Newton steps, t0) of parameter set s on the
+    device.  No host synchronisation."""
     if type(choi_matrix) is list:
-        return [maximum_likelihood_model(m) for m in choi_matrix]
+        return [maximum_likelihood_model(m, force_full) for m in choi_matrix]
     if not isinstance(choi_matrix, FragmentModel):
         raise _lib.QdcError("maximum_likelihood_model expects the FragmentModel returned by "
                             "direct_fragment_model (device-resident Choi blocks)")
     model = choi_matrix
-    out = []
-    for s in range(model.n_sets):
-        blocks = _choi_from_tensor(model.T[s], model.n_prep, model.n_meas)
-        present = blocks.abs().reshape(blocks.shape[0], -1).amax(dim=1) > 0     # observed outcomes
-        vals, vecs = torch.linalg.eigh(blocks[present])
-        flat = vals.reshape(-1)
-        order = torch.argsort(flat, stable=True)
-        srt = flat[order]
-        dim = srt.numel()
-        prefix = torch.cumsum(srt, 0) - srt
-        adjusted = srt + prefix / (dim - torch.arange(dim, device=srt.device, dtype=srt.dtype))
-        nonneg = torch.nonzero(adjusted >= 0)
-        j = int(nonneg[0]) if nonneg.numel() else dim
-        new = torch.zeros_like(srt)
-        if j < dim:
-            new[j:] = srt[j:] + prefix[j] / (dim - j)
-        clipped = torch.empty_like(flat)
-        clipped[order] = new
-        clipped = clipped.reshape(vals.shape).clamp_min(0.0)
-        rebuilt = torch.einsum("bik,bk,bjk->bij", vecs, clipped.to(vecs.dtype), vecs.conj()).conj()
-        full = torch.zeros_like(blocks)
-        full[present] = rebuilt
-        out.append(_tensor_from_choi(full, model.n_prep, model.n_meas))
-    return FragmentModel(torch.stack(out), model.n_prep, model.n_meas, model.cut_labels, model.scale)
+    if not model.T.is_cuda:
+        raise _lib.QdcError("maximum_likelihood_model runs on the GPU only (qdc_ml_project): the model's "
+                            "tensor is on " + str(model.T.device) + "; there is no CPU fallback")
+    lib = _lib.load()
+    dev = model.T.device
+    q = model.n_prep + model.n_meas
+    if q > 4:
+        raise _lib.QdcError(f"maximum_likelihood_model: {q} cut ends on one fragment (blocks of {2 ** q} x {2 ** q}); "
+                            "the device kernel takes at most 4")
+    D = 2 ** q
+    T = model.T.contiguous()
+    n_sets, n_b, K = T.shape
+    assert K == D * D
+    fwd_k, fwd_c, inv_ij, inv_c = _ml_tables(model.n_prep, model.n_meas, dev)
+    out = torch.empty_like(T)
+    ws_bytes = int(lib.qdc_ml_workspace_bytes(n_b, D))
+    info = []
+    with torch.cuda.device(dev):
+        for s in range(n_sets):
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            _lib.check(lib.qdc_ml_project(_lib.ptr(T[s]), n_b, D, K, _lib.ptr(fwd_k), _lib.ptr(fwd_c),
+                                          _lib.ptr(inv_ij), _lib.ptr(inv_c), _lib.ptr(out[s]), K,
+                                          _lib.ptr(ws), 1 if force_full else 0, _lib.stream_ptr()),
+                       "qdc_ml_project")
+            info.append(ws[:40])                         # MlState: need_full, done, counter, steps, t, total, |total|
+    result = FragmentModel(out, model.n_prep, model.n_meas, model.cut_labels, model.scale)
+    result.ml_info = info
+    return result
+
+
+def ml_info_host(model, set_index=0):
+    """(needed the full path, Newton steps, t0) of `maximum_likelihood_model`'s last run (reads back)."""
+    raw = model.ml_info[set_index].cpu().numpy()
+    ints = raw[:16].view(np.int32)
+    return bool(ints[0]), int(ints[3]), float(raw[16:24].view(np.float64)[0])
 
 
 # ---------------------------------------------------------------------------------------------

@@ -198,6 +198,31 @@ int  qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets, uint
                          const int32_t* h_meas_qubits, int n_meas, const int64_t* h_axis_stride,
                          double* d_T, int64_t ld, void* stream);
 
+/* ---- K4b: nearest positive-semidefinite fragment model ----------------------------------------
+ * Replaces maximum_likelihood_model (qsplit/qsplit_mlrecon_methods.py:320-356): per Choi block
+ * (dim x dim Hermitian, dim = 2^(cut ends of the fragment) in {1, 2, 4, 8, 16}) scipy.linalg.eigh
+ * (:330-331), the global sort-and-clip of ALL the fragment's eigenvalues (:333-343) and the rebuild
+ * through to_projector (:45-46, 354-356: the complex conjugate of V diag V^+).
+ *   d_T    [n_blocks][ld]     Pauli-basis coordinates of the blocks (qdc_sv_pauli_tensor layout)
+ *   d_T_out[n_blocks][ld_out] the projected model, same coordinates
+ * The change of basis is given as two sparse tables (each block entry touches dim components and
+ * vice versa), made by the host from the basis of the direct model:
+ *   Lambda[i][j] = sum_{t < dim} d_T[b][d_fwd_k[(i dim + j) dim + t]] * fwd_c[(i dim + j) dim + t]
+ *   T'[kappa]    = Re sum_{t < dim} inv_c[kappa dim + t] * L'[j_t][i_t],  d_inv_ij = (i_t << 8) | j_t
+ * (coefficients as interleaved (re, im) doubles, 16-byte aligned).
+ * One warp per block: Cholesky test of Lambda + 1e-14 trace I; if every block passes (exact data)
+ * the result is conj(Lambda).  Otherwise parallel-order Jacobi per block, the clipping threshold
+ * t0 (root of sum max(lambda - t, 0) = sum lambda, equal to the reference's sequential walk) by
+ * Newton steps over deterministic grid-wide reductions, and the rebuild.  force_full != 0 skips
+ * the test.  d_workspace: qdc_ml_workspace_bytes(n_blocks, dim) bytes, 16-byte aligned; its first
+ * 40 bytes report {int need_full, done, -, newton_steps; double t0, sum lambda, sum |lambda|}.
+ * Nothing is read back by the host. */
+int64_t qdc_ml_workspace_bytes(int64_t n_blocks, int dim);
+int qdc_ml_project(const double* d_T, int64_t n_blocks, int dim, int64_t ld,
+                   const int32_t* d_fwd_k, const double* d_fwd_c, const int32_t* d_inv_ij,
+                   const double* d_inv_c, double* d_T_out, int64_t ld_out, void* d_workspace,
+                   int force_full, void* stream);
+
 /* ---- K5: two-operand contraction over the cut-basis index ---------------------------------
  * Replaces the itertools.product loop of _recombine_using_networks
  * (qsplit_mlrecon_methods.py:412-461) and cutqc build.c:91-169 for two operands:

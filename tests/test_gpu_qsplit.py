@@ -190,3 +190,84 @@ def test_finite_shot_mode_converges_to_exact(cuda):
         assert abs(float(d.counts.sum()) - 500 * 4 ** p * 3 ** m) < 1e-6      # every draw lands in one cell
         row = next(iter(d.values()))
         assert len(row) == 4 ** p * 6 ** m
+
+
+def _scenario_models(noise, seed):
+    """Fragment Pauli tensors of small cut circuits from the ORACLE (optionally with noise, so that the
+    Choi blocks are not positive semidefinite), as (tensor [n_b, 4^q], n_prep, n_meas)."""
+    import cutqc_cases as cc
+    rng = np.random.default_rng(seed)
+    out = []
+    for name in ("ghz3", "ckt5", "there_and_back", "chain3", "dqva6"):
+        circ, frags, wpm = cc.CASES[name]()
+        ft = qo.identify_frag_targets(wpm)
+        for i, frag in enumerate(frags):
+            R = qo.fragment_pauli_tensor(frag, ft[i]["prep"], ft[i]["meas"])
+            T = R.reshape(R.shape[0], -1)
+            T = T + noise * rng.standard_normal(T.shape) * (np.abs(T).max(axis=1, keepdims=True) > 0)
+            out.append((name, i, T, len(ft[i]["prep"]), len(ft[i]["meas"])))
+    return out
+
+
+@pytest.mark.parametrize("noise,force_full", [(0.0, False), (0.0, True), (0.05, False), (1e-3, False)])
+def test_maximum_likelihood_kernel_matches_oracle(cuda, noise, force_full):
+    """qdc_ml_project against the oracle's line-faithful maximum_likelihood_model
+    (qsplit_mlrecon_methods.py:320-356: scipy eigh per block, sequential clipping walk, rebuild through
+    to_projector) on exact tensors (early-out: every block is PSD), on the same with the early-out
+    switched off (the Jacobi path must reproduce the conjugate), and on noisy, non-PSD tensors; block
+    sizes 2 x 2 to 16 x 16 occur.  Keys (which outcomes survive) and blocks to 1e-10."""
+    from qdc_b200.qsplit import qsplit_mlrecon_methods as qmm
+    seen_dims, seen_full = set(), set()
+    for name, i, T, p, m in _scenario_models(noise, 3):
+        model = qmm.FragmentModel(torch.as_tensor(T, device=cuda).unsqueeze(0), p, m, {"prep": [], "meas": []})
+        direct = {k: v for k, v in model.items()}
+        want = qo.maximum_likelihood_model(direct)
+        got_model = qmm.maximum_likelihood_model(model, force_full=force_full)
+        need_full, steps, t0 = qmm.ml_info_host(got_model)
+        got = dict(got_model.items())
+        seen_dims.add(2 ** (p + m)); seen_full.add(need_full)
+        scale = max(np.abs(b).max() for b in direct.values())
+        for bits, block in want.items():
+            if np.abs(block).max() < 1e-12 * scale:
+                continue
+            assert bits in got, (name, i, bits)
+            assert np.abs(got[bits] - block).max() < 1e-10 * max(scale, 1.0), (name, i, bits)
+        for bits, block in got.items():
+            if bits not in want:
+                assert np.abs(block).max() < 1e-10 * max(scale, 1.0), (name, i, bits)
+        if noise == 0.0 and not force_full:
+            assert not need_full and t0 == 0.0
+        if noise >= 0.05:
+            assert need_full and t0 > 0.0 and 1 <= steps <= 12
+    assert {2, 4} <= seen_dims and max(seen_dims) >= 4
+    assert (True in seen_full) == (force_full or noise > 0)
+
+
+@pytest.mark.parametrize("p,m", [(1, 0), (1, 1), (2, 1), (2, 2), (4, 0), (0, 4)])
+def test_maximum_likelihood_kernel_random_blocks(cuda, p, m):
+    """Random Hermitian blocks of every supported size (2 .. 16), many of them indefinite, some of
+    them exactly rank one or zero: Jacobi eigen-decomposition + global soft threshold + conjugated
+    rebuild against numpy (eigh per block, the oracle's clipping walk over all eigenvalues)."""
+    from qdc_b200.qsplit import qsplit_mlrecon_methods as qmm
+    rng = np.random.default_rng(100 * p + m)
+    D, n_b = 2 ** (p + m), 300
+    L = rng.standard_normal((n_b, D, D)) + 1j * rng.standard_normal((n_b, D, D))
+    L = L @ np.conj(np.swapaxes(L, 1, 2)) / D + 0.3 * (L + np.conj(np.swapaxes(L, 1, 2)))
+    v = rng.standard_normal((n_b, D)) + 1j * rng.standard_normal((n_b, D))
+    L[::7] = v[::7, :, None] * np.conj(v[::7, None, :])            # rank one
+    L[5] = 0.0                                                      # an outcome that never occurs
+    T = qmm._tensor_from_choi(torch.as_tensor(L), p, m)
+    model = qmm.FragmentModel(T.to(cuda).unsqueeze(0), p, m, {"prep": [], "meas": []})
+    got_model = qmm.maximum_likelihood_model(model)
+    need_full, steps, t0 = qmm.ml_info_host(got_model)
+    assert need_full and t0 > 0
+    got = got_model.choi_blocks().cpu().numpy()
+    want_dict = qo.maximum_likelihood_model({format(b, "012b"): L[b] for b in range(n_b) if np.abs(L[b]).max() > 0})
+    want = np.zeros_like(L)
+    for bits, block in want_dict.items():
+        want[int(bits, 2)] = block
+    assert np.abs(got - want).max() < 1e-10 * np.abs(L).max()
+    assert np.abs(got[5]).max() == 0.0
+    # positive semidefinite and trace preserving (the point of the projection)
+    assert np.linalg.eigvalsh(got).min() > -1e-10 * np.abs(L).max()
+    assert abs(np.trace(got, axis1=1, axis2=2).sum().real - np.trace(L, axis1=1, axis2=2).sum().real) < 1e-9 * n_b

@@ -79,25 +79,56 @@ def test_choi_view_of_pauli_tensor_matches_oracle_lstsq():
             assert (T2 - T[0]).abs().max() < 1e-12
 
 
-@pytest.mark.parametrize("noise", [0.0, 0.05])
-def test_maximum_likelihood_matches_oracle(noise):
-    """Closed-form clipping == the reference's sequential loop, including on non-PSD (noisy)
-    blocks; compared through the Choi dict view."""
-    rng = np.random.default_rng(4)
-    frags, wpm = list(_scenarios())[2]
-    ft = qo.identify_frag_targets(wpm)
-    for i, frag in enumerate(frags):
-        R = qo.fragment_pauli_tensor(frag, ft[i]["prep"], ft[i]["meas"])
-        p, m = len(ft[i]["prep"]), len(ft[i]["meas"])
-        T = R.reshape(R.shape[0], -1)
-        T = T + noise * rng.standard_normal(T.shape) * (np.abs(T).max(axis=1, keepdims=True) > 0)
-        model = qmm.FragmentModel(torch.as_tensor(T).unsqueeze(0), p, m, {"prep": [], "meas": []})
-        direct = {k: v for k, v in model.items()}
-        want = qo.maximum_likelihood_model(direct)
-        got = qmm.maximum_likelihood_model(model)
-        assert set(got.keys()) == set(want.keys())
-        for bits in want:
-            assert np.abs(got[bits] - want[bits]).max() < 1e-10
+def test_maximum_likelihood_is_gpu_only():
+    """No CPU fallback: a model on the CPU is refused loudly."""
+    from qdc_b200 import _lib
+    model = qmm.FragmentModel(torch.zeros(1, 2, 4, dtype=torch.float64), 1, 0, {"prep": [], "meas": []})
+    with pytest.raises(_lib.QdcError, match="GPU only"):
+        qmm.maximum_likelihood_model(model)
+
+
+@pytest.mark.parametrize("p,m", [(0, 0), (1, 0), (0, 1), (1, 1), (2, 1), (2, 2), (4, 0), (0, 4)])
+def test_ml_basis_tables_reproduce_the_change_of_basis(p, m):
+    """qmm._ml_tables (what qdc_ml_project is given): the sparse forward table rebuilds every Choi
+    block entry, the sparse inverse table every tensor component, exactly as the dense basis does."""
+    rng = np.random.default_rng(10 * p + m)
+    D = 2 ** (p + m)
+    T = torch.as_tensor(rng.standard_normal((5, D * D)))
+    fwd_k, fwd_c, inv_ij, inv_c = [x.numpy() for x in qmm._ml_tables(p, m, torch.device("cpu"))]
+    want = qmm._choi_from_tensor(T, p, m).numpy()
+    fc = fwd_c[..., 0] + 1j * fwd_c[..., 1]
+    got = (T.numpy()[:, fwd_k] * fc[None]).sum(axis=2).reshape(5, D, D)
+    assert np.abs(got - want).max() < 1e-14
+    L = rng.standard_normal((5, D, D)) + 1j * rng.standard_normal((5, D, D))
+    L = L + np.conj(np.swapaxes(L, 1, 2))
+    want_T = qmm._tensor_from_choi(torch.as_tensor(L), p, m).numpy()
+    ic = inv_c[..., 0] + 1j * inv_c[..., 1]
+    got_T = (ic[None] * L[:, inv_ij & 0xff, inv_ij >> 8]).sum(axis=2).real
+    assert np.abs(got_T - want_T).max() < 1e-13
+
+
+def test_soft_threshold_is_the_reference_clipping_walk():
+    """The reference's sequential walk over the sorted eigenvalues (:333-343, restated line by line in
+    the oracle) equals lambda' = max(lambda - t0, 0) with t0 reached by Newton steps from 0 on
+    h(t) = sum max(lambda - t, 0) - sum lambda -- the form the device kernel uses."""
+    rng = np.random.default_rng(8)
+    for trial in range(200):
+        n = int(rng.integers(2, 80))
+        eigs = rng.standard_normal(n) * rng.uniform(0.01, 1.0) + rng.uniform(0.0, 0.6)
+        if trial % 7 == 0:
+            eigs = np.abs(eigs)                                  # nothing to clip
+        fake = {format(i, "b"): np.diag([v]).astype(complex) for i, v in enumerate(eigs)}
+        want = np.array([qo.maximum_likelihood_model(fake).get(format(i, "b"), np.zeros((1, 1)))[0, 0].real
+                         for i in range(n)])
+        t, total, steps = 0.0, eigs.sum(), 0
+        for steps in range(64):
+            pos = eigs > t
+            h = (eigs[pos] - t).sum() - total
+            if not h > 1e-16 * np.abs(eigs).sum() or pos.sum() == 0:
+                break
+            t += h / pos.sum()
+        got = np.maximum(eigs - t, 0.0)
+        assert np.abs(got - want).max() < 1e-12 and steps < 12
 
 
 def test_contraction_spec_parsing(monkeypatch):
