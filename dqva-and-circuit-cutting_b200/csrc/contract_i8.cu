@@ -58,7 +58,10 @@ int qdc_launch_finish(const double* d_partials, int n_partials, double* d_sums, 
 namespace {
 
 constexpr int TM = 128;                       // tile rows
-constexpr int CPT = 16;                       // columns per epilogue thread
+constexpr int cpt_of(int tn) { return tn == 128 ? 32 : 16; }     // columns per epilogue thread
+// accumulator slots of TN columns: one per order while S TN <= 512 TMEM columns, else 4 that rotate --
+// order 0 is complete after the tile's very first slice pair and drained long before order 4 starts
+constexpr int slots_of(int S, int tn) { return S * tn <= 512 ? S : 4; }
 constexpr int MAX_S = 6;
 constexpr int MAX_STAGES = 8;                 // ring of streamed-operand slices
 constexpr int N_ISSUERS = 3;                  // MMA-issuing warps; each owns whole accumulator orders (owner_of)
@@ -169,28 +172,28 @@ __device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uin
 // adds ptxas computes all 16 descriptors of a block first, runs out of the 63 uniform registers,
 // spills them to vector registers and pays R2UR again.)
 #define QDC_SS_STEP " add.s64 da, da, 16;\n add.s64 db, db, 16;\n tcgen05.mma.cta_group::1.kind::i8 [d], da, db, %3, q;\n"
-template <int A_OFF, int D_OFF, bool ACC>
-__device__ __forceinline__ void umma_pair_ss(uint32_t tmem, uint64_t a_desc0, uint64_t b_desc, uint32_t idesc) {
+template <int A_OFF, bool ACC>
+__device__ __forceinline__ void umma_pair_ss(uint32_t tmem_d, uint64_t a_desc0, uint64_t b_desc, uint32_t idesc) {
     asm volatile(
         "{\n .reg .pred p, q;\n .reg .b32 d;\n .reg .b64 da, db;\n"
-        " setp.ne.b32 p, %5, 0;\n setp.eq.b32 q, %3, %3;\n"
-        " add.u32 d, %0, %4;\n add.s64 da, %1, %6;\n mov.b64 db, %2;\n"
+        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
+        " mov.b32 d, %0;\n add.s64 da, %1, %5;\n mov.b64 db, %2;\n"
         " tcgen05.mma.cta_group::1.kind::i8 [d], da, db, %3, p;\n"
         QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP
         "}\n"
-        ::"r"(tmem), "l"(a_desc0), "l"(b_desc), "r"(idesc), "n"(D_OFF), "n"(ACC ? 1 : 0), "n"(A_OFF) : "memory");
+        ::"r"(tmem_d), "l"(a_desc0), "l"(b_desc), "r"(idesc), "n"(ACC ? 1 : 0), "n"(A_OFF) : "memory");
 }
 #define QDC_TS_STEP " add.u32 ta, ta, 8;\n add.s64 db, db, 16;\n tcgen05.mma.cta_group::1.kind::i8 [d], [ta], db, %2, q;\n"
-template <int TA_OFF, int D_OFF, bool ACC>
-__device__ __forceinline__ void umma_pair_ts(uint32_t tmem, uint64_t b_desc, uint32_t idesc) {
+template <bool ACC>
+__device__ __forceinline__ void umma_pair_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t b_desc, uint32_t idesc) {
     asm volatile(
         "{\n .reg .pred p, q;\n .reg .b32 d, ta;\n .reg .b64 db;\n"
         " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %2, %2;\n"
-        " add.u32 d, %0, %3;\n add.u32 ta, %0, %5;\n mov.b64 db, %1;\n"
+        " mov.b32 d, %0;\n mov.b32 ta, %3;\n mov.b64 db, %1;\n"
         " tcgen05.mma.cta_group::1.kind::i8 [d], [ta], db, %2, p;\n"
         QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP QDC_TS_STEP
         "}\n"
-        ::"r"(tmem), "l"(b_desc), "r"(idesc), "n"(D_OFF), "n"(ACC ? 1 : 0), "n"(TA_OFF) : "memory");
+        ::"r"(tmem_d), "l"(b_desc), "r"(idesc), "r"(tmem_a), "n"(ACC ? 1 : 0) : "memory");
 }
 
 // compile-time loop: f(std::integral_constant<int, I>) for I in [I0, N)
@@ -262,7 +265,7 @@ struct I8Args {
     const double* row_scale; // 2^(e_r - 7) per row of the slab (padded rows: 0)
     const double2* colq;     // per padded column: (2^(f_c - 7), 2^(f_c - 7) * weight); padded columns: 0
     const uint4* coltab;     // per padded column: (x_lo, x_hi | flags, weight << lsh, 1 << lsh)
-    const int* gref;         // per 16 columns: reference exponent
+    const int* gref;         // per I8_GROUP columns: reference exponent
     const double* A_src;     // the FP64 operands themselves (exact re-evaluation of flagged candidates)
     const double* B_src;
     int kdim_src;
@@ -280,7 +283,7 @@ struct I8Args {
     double* partials;
 };
 
-// exact evaluation of the flagged outputs of one thread's 16 columns from the FP64 operands.
+// exact evaluation of the flagged outputs of one thread's columns (bit c of `flags` = column c0 + c) from the FP64 operands.
 // (Everything by value: a reference to the kernel's parameter struct would force a local-memory
 // copy of it, and the hot loop would read its fields through LDL.)
 struct FlagCtx {
@@ -309,8 +312,14 @@ __device__ __noinline__ void emit_flagged(FlagCtx x, CandSink sink, long long r_
 
 // S = number of slices per operand in use (compile time: every loop over slice pairs and orders unrolls)
 template <int S, int TN, int EPI>
-__global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) contract_i8_kernel(const I8Args a) {
-    constexpr int N_EPI_WARPS = 4 * (TN / CPT);
+__global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32, 1) contract_i8_kernel(const I8Args a) {
+    constexpr int CPT = cpt_of(TN), N_EPI_WARPS = 4 * (TN / CPT), NSLOT = slots_of(S, TN);
+    static_assert(NSLOT * TN <= TMEM_COLS && S - NSLOT <= 1, "accumulator slots");
+    static_assert(EPI == 0 || (CPT == 16 && NSLOT == S), "the storing epilogue keeps 16 columns per thread and one slot per order");
+    // order d of this CTA's tile number `seq` is accumulation number g = seq S + d: it lives in slot g % NSLOT
+    // and is that slot's use number g / NSLOT (the parity of its two barriers)
+    auto slot_of = [](uint32_t seq, int d) -> uint32_t { return NSLOT == S ? (uint32_t)d : (seq * S + d) % NSLOT; };
+    auto par_of = [](uint32_t seq, int d) -> uint32_t { return NSLOT == S ? (seq & 1u) : (((seq * S + d) / NSLOT) & 1u); };
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[N_BARS];
     uint32_t bar0 = smem_u32(bars);
@@ -396,12 +405,12 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
         const uint64_t desc0 = smem_desc(0, 128, (uint32_t)(kdim / 16) * 128u);
         const uint64_t a_desc0 = desc0 + (sA_addr >> 4), b_desc0 = desc0 + (sB_addr >> 4);
         const uint32_t ta_full = bar0 + 8u * BAR_TA_FULL, ta_free = bar0 + 8u * BAR_TA_FREE;
-        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, tile_phase = 0;
+        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, seq = 0;          // seq: tiles this CTA has walked
         if (ksteps == 8) {
             // ---- kdim = 256: everything but the ring stage is a compile-time constant ----
             // TMEM columns [S TN, 512) hold the first NTA resident slices (64 columns each); their pairs
             // take A from tensor memory and read only the streamed tile from shared memory
-            constexpr int NTA = (TMEM_COLS - S * TN) / 64 < S ? (TMEM_COLS - S * TN) / 64 : S;
+            constexpr int NTA = (TMEM_COLS - NSLOT * TN) / 64 < S ? (TMEM_COLS - NSLOT * TN) / 64 : S;
             constexpr uint32_t A_SLICE16 = TM * 256 / 16, B_SLICE16 = TN * 256 / 16;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
                 const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
@@ -416,7 +425,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         if (leader) {
                             for (int i = 0; i < NTA; ++i)
                                 for (int ks = 0; ks < 8; ++ks)
-                                    tmem_cp_128x256b(tmem + (uint32_t)(S * TN + (i * 8 + ks) * 8), a_desc0 + (uint32_t)i * A_SLICE16 + ks * 16);
+                                    tmem_cp_128x256b(tmem + (uint32_t)(NSLOT * TN + (i * 8 + ks) * 8), a_desc0 + (uint32_t)i * A_SLICE16 + ks * 16);
                             umma_commit(ta_full);
                         }
                     } else {
@@ -424,7 +433,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         tc_fence_after();
                     }
                 }
-                for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
+                for (int cb = cb0; cb < cb1; ++cb, ++seq) {
                     static_for<0, S>([&](auto jc) {
                         constexpr int j = decltype(jc)::value;
                         mbar_wait(b_full0 + 8u * b_stage, b_phase);
@@ -433,14 +442,15 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         static_for<0, S - j>([&](auto ic) {
                             constexpr int i = decltype(ic)::value, d = i + j;
                             if (iw == owner_of(S, d)) {
+                                const uint32_t slot = slot_of(seq, d);
                                 if (j == 0) {                      // first touch of order d in this tile
-                                    mbar_wait(acc_empty0 + 8u * d, tile_phase ^ 1u);
+                                    mbar_wait(acc_empty0 + 8u * slot, par_of(seq, d) ^ 1u);
                                     tc_fence_after();
                                 }
                                 if (leader) {
-                                    if constexpr (i < NTA) umma_pair_ts<S * TN + i * 64, d * TN, (j > 0)>(tmem, b_desc, idesc);
-                                    else umma_pair_ss<i * (int)A_SLICE16, d * TN, (j > 0)>(tmem, a_desc0, b_desc, idesc);
-                                    if (i == 0) umma_commit(acc_full0 + 8u * j);   // order j is complete
+                                    if constexpr (i < NTA) umma_pair_ts<(j > 0)>(tmem + slot * TN, tmem + (uint32_t)(NSLOT * TN + i * 64), b_desc, idesc);
+                                    else umma_pair_ss<i * (int)A_SLICE16, (j > 0)>(tmem + slot * TN, a_desc0, b_desc, idesc);
+                                    if (i == 0) umma_commit(acc_full0 + 8u * slot);   // order j is complete (d = j here)
                                 }
                             }
                         });
@@ -456,8 +466,8 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
         } else {
             // ---- any kdim <= 256 (multiple of 32): the same walk with run-time step counts, all pairs
             // issued by issuer 0 (the others only keep the barrier counts) ----
-            const uint32_t tmem_a0 = tmem + (uint32_t)(S * TN);
-            const int n_ta = min(S, (TMEM_COLS - S * TN) / (kdim / 4));
+            const uint32_t tmem_a0 = tmem + (uint32_t)(NSLOT * TN);
+            const int n_ta = min(S, (TMEM_COLS - NSLOT * TN) / (kdim / 4));
             const bool mine = iw == 0;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
                 const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
@@ -468,19 +478,20 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                         for (int ks = 0; ks < ksteps; ++ks)
                             tmem_cp_128x256b(tmem_a0 + (uint32_t)(i * ksteps + ks) * 8u,
                                              a_desc0 + (uint32_t)i * (a_slice_bytes >> 4) + ks * 16);
-                for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
+                for (int cb = cb0; cb < cb1; ++cb, ++seq) {
                     for (int j = 0; j < S; ++j) {
                         mbar_wait(b_full0 + 8u * b_stage, b_phase);
                         tc_fence_after();
                         const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * (b_slice_bytes >> 4);
                         for (int i = 0; mine && i + j < S; ++i) {
                             const int d = i + j;
+                            const uint32_t slot = slot_of(seq, d);
                             if (j == 0) {
-                                mbar_wait(acc_empty0 + 8u * d, tile_phase ^ 1u);
+                                mbar_wait(acc_empty0 + 8u * slot, par_of(seq, d) ^ 1u);
                                 tc_fence_after();
                             }
                             const uint64_t a_desc = a_desc0 + (uint32_t)i * (a_slice_bytes >> 4);
-                            const uint32_t tmem_d = tmem + (uint32_t)d * TN;
+                            const uint32_t tmem_d = tmem + slot * TN;
                             if (leader) {
                                 if (i < n_ta) {
                                     const uint32_t ta = tmem_a0 + (uint32_t)(i * ksteps) * 8u;
@@ -490,7 +501,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                                     for (int ks = 0; ks < ksteps; ++ks)
                                         umma_i8(tmem_d, a_desc + ks * 16, b_desc + ks * 16, idesc, (j > 0 || ks > 0) ? 1u : 0u);
                                 }
-                                if (i == 0) umma_commit(acc_full0 + 8u * j);
+                                if (i == 0) umma_commit(acc_full0 + 8u * slot);
                             }
                         }
                         if (leader) umma_commit(b_empty0 + 8u * b_stage);
@@ -504,9 +515,9 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
         // ================= epilogue =================
         const int ew = warp - FIRST_EPI_WARP;
         const int quarter = warp & 3;                      // TMEM lanes 32 * (warp % 4) .. + 31
-        const int part = ew >> 2;                          // which 16 columns of the TN-column accumulator
+        const int part = ew >> 2;                          // which CPT columns of the TN-column accumulator
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(part * CPT);
-        uint32_t tile_phase = 0;
+        uint32_t tile_phase = 0, seq = 0;
         const double inv_norm = a.use_norm ? 1.0 / a.res[I8_RES_NORM] : 1.0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
@@ -533,8 +544,8 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                 }
                 // Per order d one persistent 64-bit sum run[d] += D_d[c] m_c (the IMAD.WIDE chain accumulates
                 // straight into it).  Columns of one 16-group share the unit 2^(gref - 20 - 7); while the
-                // thread's next tile has the same gref nothing else happens.  When it changes (or after 16
-                // tiles: |run| < 16 tiles x 16 columns x 2^25 x 2^29 < 2^63) the orders are folded by a
+                // thread's next tile has the same gref nothing else happens.  When it changes (or after 256
+                // columns: |run| < 256 x 2^25 x 2^29 < 2^63) the orders are folded by a
                 // 128-bit Horner step, shifted to the unit of the largest column exponent and added to the
                 // 128-bit total, which enters FP64 once per work item.
                 I128 total = {0ull, 0ll};
@@ -554,10 +565,17 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                     for (int d = 0; d < S; ++d) run[d] = 0;
                     n_run = 0;
                 };
-                for (int cb = cb0; cb < cb1; ++cb, tile_phase ^= 1u) {
+                for (int cb = cb0; cb < cb1; ++cb, ++seq) {
                     const int c0 = cb * TN + part * CPT;
-                    const int gr = __ldg(a.gref + (c0 >> 4));
-                    if (gr != cur_gr || n_run == 16) { flush(); cur_gr = gr; }       // warp-uniform
+                    // the next tile's column-table lines (CPT x 16 bytes) and group exponent go to L1 now: the
+                    // table is walked once per row block, so every tile would otherwise start with a chain of
+                    // L2 round trips before its first order can be drained
+                    if (cb + 1 < cb1) {
+                        if (lane < CPT / 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.coltab + c0 + TN + lane * 8));
+                        else if (lane == CPT / 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.gref + (c0 + TN) / I8_GROUP));
+                    }
+                    const int gr = __ldg(a.gref + c0 / I8_GROUP);
+                    if (gr != cur_gr || n_run == 256 / CPT) { flush(); cur_gr = gr; } // warp-uniform
                     ++n_run;
                     int tcmp;                               // an output may be a candidate when D_0 >= tcmp
                     {
@@ -575,28 +593,34 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
                     uint32_t flags = 0;
 #pragma unroll
                     for (int d = 0; d < S; ++d) {
-                        mbar_wait_relaxed(acc_full0 + 8u * d, tile_phase, 32);
+                        const uint32_t slot = slot_of(seq, d);
+                        mbar_wait_relaxed(acc_full0 + 8u * slot, par_of(seq, d), 32);
                         tc_fence_after();
-                        uint32_t v[CPT];
-                        tmem_ld16(lane_base + (uint32_t)(d * TN), v);
-                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(acc_empty0 + 8u * d);
                         long long r = run[d];
 #pragma unroll
-                        for (int c = 0; c < CPT; ++c) r += (long long)(int32_t)v[c] * (long long)m[c];
-                        run[d] = r;
-                        if (d == 0) {                       // candidate filter: one max tree, compares only on a hit
-                            int mx = (int32_t)v[0];
+                        for (int h = 0; h < CPT / 16; ++h) {            // 16 columns at a time (registers)
+                            uint32_t v[16];
+                            tmem_ld16(lane_base + slot * TN + (uint32_t)(h * 16), v);
+                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                            if (h == CPT / 16 - 1) {                    // everything of this order is in registers: release the slot
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(acc_empty0 + 8u * slot);
+                            }
 #pragma unroll
-                            for (int c = 1; c < CPT; ++c) mx = max(mx, (int32_t)v[c]);
-                            if (mx >= tcmp) {
+                            for (int c = 0; c < 16; ++c) r += (long long)(int32_t)v[c] * (long long)m[h * 16 + c];
+                            if (d == 0) {                   // candidate filter: one max tree, compares only on a hit
+                                int mx = (int32_t)v[0];
 #pragma unroll
-                                for (int c = 0; c < CPT; ++c)
-                                    if ((int32_t)v[c] >= tcmp) flags |= 1u << c;
+                                for (int c = 1; c < 16; ++c) mx = max(mx, (int32_t)v[c]);
+                                if (mx >= tcmp) {
+#pragma unroll
+                                    for (int c = 0; c < 16; ++c)
+                                        if ((int32_t)v[c] >= tcmp) flags |= 1u << (h * 16 + c);
+                                }
                             }
                         }
+                        run[d] = r;
                     }
                     if (flags && row_ok) {
                         const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src};
@@ -698,24 +722,34 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, 1) con
 template <int S, int TN, int EPI>
 int launch_i8(const I8Args& a, int grid, size_t smem, cudaStream_t s) {
     QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel<S, TN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    contract_i8_kernel<S, TN, EPI><<<grid, (FIRST_EPI_WARP + 4 * (TN / CPT)) * 32, smem, s>>>(a);
+    contract_i8_kernel<S, TN, EPI><<<grid, (FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32, smem, s>>>(a);
     QDC_CHECK_LAUNCH();
     return QDC_OK;
 }
 
-// tile width: 96 columns where the S accumulators of 96 columns fit the 512 of TMEM and two stages of
-// the streamed operand fit beside the resident slices (an N = 96 instruction costs what N = 64 does)
-int i8_tile_n(int n_slices, int kd) {
-    const char* m = getenv("QDC_I8_TN");
-    if (m && atoi(m) == 64) return 64;
-    if (n_slices == 5 && (size_t)n_slices * TM * kd + 2 * (size_t)96 * kd <= 227 * 1024 - 2048) return 96;
+// Tile width.  The M = 128 MMA instruction runs at the tensor pipe's full rate only from N = 128 on
+// (64 clocks; N = 96: 56.8, N = 64: ~47, profiles/r1_umma_rate_probe.log), so 128 columns wherever the
+// accumulators fit tensor memory (S <= 4 directly, S = 5 through 4 rotating slots) and two stages of
+// the streamed operand fit beside the resident slices -- for the scoring-only epilogue; the storing
+// one keeps 16 columns per thread: 96 columns at S = 5, else 64.  QDC_I8_TN overrides (64 / 96 / 128).
+int i8_tile_n(int n_slices, int kd, int store) {
+    const size_t smem_max = 227 * 1024 - 2048, a_res = (size_t)n_slices * TM * kd;
+    auto fits = [&](int tn) { return a_res + 2 * (size_t)tn * kd <= smem_max; };
+    if (const char* m = getenv("QDC_I8_TN")) {
+        const int tn = atoi(m);
+        if (tn == 64) return 64;
+        if (tn == 96 && n_slices == 5 && fits(96)) return 96;
+        if (tn == 128 && !store && n_slices <= 5 && fits(128)) return 128;
+    }
+    if (!store && n_slices <= 5 && fits(128)) return 128;
+    if (n_slices == 5 && fits(96)) return 96;
     return 64;
 }
 
 // one instantiation for one slice count: geometry, work split, launch
 int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
     const int kd = a.kdim;
-    const int TN = i8_tile_n(n_slices, kd);
+    const int TN = i8_tile_n(n_slices, kd, store);
     const long long n_rb = (a.n_rows + TM - 1) / TM, n_cb = (a.n_cols + TN - 1) / TN;
     QDC_REQUIRE(n_rb < (1ll << 31) && n_cb < (1ll << 31), "too many tiles");
     a.n_rb = (int)n_rb; a.n_cb = (int)n_cb;
@@ -750,6 +784,14 @@ int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
         return store ? launch_i8<SS, TT, 1>(a, grid, smem, s) : launch_i8<SS, TT, 0>(a, grid, smem, s);
     QDC_I8_CASE(2, 64) QDC_I8_CASE(3, 64) QDC_I8_CASE(4, 64) QDC_I8_CASE(5, 64) QDC_I8_CASE(5, 96) QDC_I8_CASE(6, 64)
 #undef QDC_I8_CASE
+    if (!store && TN == 128) {
+        switch (n_slices) {
+            case 2: return launch_i8<2, 128, 0>(a, grid, smem, s);
+            case 3: return launch_i8<3, 128, 0>(a, grid, smem, s);
+            case 4: return launch_i8<4, 128, 0>(a, grid, smem, s);
+            case 5: return launch_i8<5, 128, 0>(a, grid, smem, s);
+        }
+    }
     qdc_set_error("no int8 contraction kernel for %d slices, tile width %d", n_slices, TN);
     return QDC_ERR_UNSUPPORTED;
 }

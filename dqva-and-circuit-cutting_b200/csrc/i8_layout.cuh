@@ -8,7 +8,7 @@
 //   scale    f64   [rows_pad]                 2^(e_r - 7): x = scale * sum_i digit_i 256^-i
 //   colq     f64x2 [rows_pad]                 (scale, scale * weight)               (column role)
 //   coltab   u32x4 [rows_pad]                 (x_lo, x_hi | flags, weight << lsh, 1 << lsh) (column role)
-//   gref     i32   [rows_pad / 16]            exponent of the largest row of each 16-row group
+//   gref     i32   [rows_pad / 32]            exponent of the largest row of each 32-row group
 //   part     f64   [PREP_GRID][2 kd + 4]      per-CTA column sums (sum x, sum weight x) and the
 //                                             statistics the error bounds need
 // kd = kdim rounded up to 32 (zero padded).  Nothing here is visible to callers but the byte count.
@@ -18,7 +18,8 @@
 
 constexpr int I8_PREP_GRID = 296;        // CTAs of the preparation pass = partial rows of `part`
 constexpr int I8_ROW_ALIGN = 384;        // lcm of the tile heights / widths in use (128, 96, 64)
-constexpr int I8_GROUP = 16;             // columns that share one epilogue thread per tile
+constexpr int I8_GROUP = 32;             // adjacent columns that share one integer unit (gref): what one epilogue thread sums
+constexpr int I8_FOLD_COLS = 16;         // fewest columns an epilogue thread folds (and rounds) at a time: enters the error bound
 constexpr int I8_LSH_MAX = 20;           // a column keeps its own exponent down to 2^-20 of its group's largest
 constexpr int I8_STAT = 4;               // per-CTA statistics: max 2^e, sum_{ok} 2^e, max e (as a double), spare
 

@@ -15,8 +15,8 @@
 // most 128.5 units of the last kept digit (rounding directly to S' digits: 128), which the stated
 // bound (S' + 1.1) kdim 2^(-8 S') covers, so one 6-slice buffer serves every slice count.
 //
-// Column role (the operand streamed through the tiles): an epilogue thread sums 16 adjacent
-// columns in integers, so those columns need one common unit.  Every 16-row group of the operand
+// Column role (the operand streamed through the tiles): an epilogue thread sums 16 or 32 adjacent
+// columns in integers, so those columns need one common unit.  Every 32-row group of the operand
 // gets the exponent of its largest row as reference; a row keeps its own exponent down to 2^-20 of
 // that (the epilogue shifts its terms left by lsh = 20 - (ref - e_r)), smaller rows are sliced with
 // exponent ref - 20 (they lose relative precision, their absolute error stays that of a row at
@@ -28,7 +28,7 @@
 namespace {
 
 constexpr int PREP_THREADS = 256;
-constexpr int PREP_TILE = 32;                           // rows per CTA pass: 2 groups of 16
+constexpr int PREP_TILE = 32;                           // rows per CTA pass = one column group
 constexpr uint64_t FLAG_ROW_BAD = 1ull << 63, FLAG_COL_BAD = 1ull << 62;
 constexpr int E_ZERO = -(1 << 20);                      // exponent of an all-zero row / group
 
@@ -103,10 +103,10 @@ __global__ void __launch_bounds__(PREP_THREADS, 2) i8_prep_kernel(const PrepArgs
         }
         __syncthreads();
         int gmax = E_ZERO;
-        if (a.grouped) {
-            const int ge = rowE[16 * (warp >> 2) + (lane & 15)];
-            gmax = (int)__reduce_max_sync(0xffffffffu, (unsigned)(ge - E_ZERO)) + E_ZERO;
-            if (a.gref && (warp & 3) == 0 && lane == 0) a.gref[(t * PREP_TILE) / I8_GROUP + (warp >> 2)] = gmax;
+        if (a.grouped) {                                    // one group = the 32 rows of this pass
+            static_assert(PREP_TILE == I8_GROUP, "a preparation pass covers exactly one column group");
+            gmax = (int)__reduce_max_sync(0xffffffffu, (unsigned)(rowE[lane] - E_ZERO)) + E_ZERO;
+            if (a.gref && warp == 0 && lane == 0) a.gref[t] = gmax;
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(1024) i8_plan_kernel(const PlanArgs a) {
         // largest row and column; on the masked sum every output counts at most n_nodes times and
         // only independent rows and columns enter; the integer fold of the epilogue adds at most
         // half a unit of the last order (2^-6 of 2^(e_r + f_max) |f| 2^(-8S)) per 16 columns
-        const double af = fabs(f), fold = ldexp(0.5 * (double)((a.n_cols + I8_GROUP - 1) / I8_GROUP), -6 - I8_LSH_MAX);
+        const double af = fabs(f), fold = ldexp(0.5 * (double)((a.n_cols + I8_FOLD_COLS - 1) / I8_FOLD_COLS), -6 - I8_LSH_MAX);
         int chosen = a.n_slices;
         double b_out = 0.0, b_cost = 0.0;
         for (int S = (a.n_slices ? a.n_slices : 3); S <= (a.n_slices ? a.n_slices : a.n_stored); ++S) {

@@ -190,7 +190,8 @@ def resolve_contraction(spec: Optional[str]):
 
 
 I8_LSH_MAX = 20          # csrc/i8_layout.cuh
-I8_GROUP = 16
+I8_GROUP = 32            # adjacent columns sharing one integer unit
+I8_FOLD_COLS = 16        # columns per rounding of the epilogue's integer fold
 
 
 def _pow2_ceiling_exponents(X: torch.Tensor) -> torch.Tensor:
@@ -211,7 +212,7 @@ def i8_error_bounds(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, scale:
 
     Per output |err| <= 2^(e_r + f_c) * scale / norm * kdim * (S + 1.1) * 2^(-8 S), e_r / f_c the
     exponents the slicing applies: per row of A its own; per column its own down to 2^-20 of the
-    largest of its 16-column group (smaller columns are sliced at that floor).  The MIS cost only
+    largest of its 32-column group (smaller columns are sliced at that floor).  The MIS cost only
     sums outputs whose row and column are themselves independent sets, each weighted by at most
     the number of graph nodes, so
         |cost error| <= n_nodes * (sum_{r ok} 2^e_r) * scale / norm * 2^(-8 S) *
@@ -237,7 +238,7 @@ def i8_error_bounds(A: torch.Tensor, Bt: torch.Tensor, tables: MisTables, scale:
     stats = torch.stack([pa.max() * pb.max() * f, (pa * r_ok).sum() * (pb * c_ok).sum() * f,
                          (pa * r_ok).sum() * pb.max() * f]).cpu().tolist()
     n_nodes = bin(int(tables.node_mask)).count("1")
-    fold = 0.5 * ((n_cols + I8_GROUP - 1) // I8_GROUP) * 2.0 ** (-6 - I8_LSH_MAX)
+    fold = 0.5 * ((n_cols + I8_FOLD_COLS - 1) // I8_FOLD_COLS) * 2.0 ** (-6 - I8_LSH_MAX)
     out = {}
     for S in range(2, 7):
         g = kd * (S + 1.1) * 2.0 ** (-8 * S)

@@ -267,7 +267,7 @@ int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_B
  * (sum_r x, sum_r weight_r x: they give combined_norm, qsplit_mlrecon_methods.py:471-472, sum p and
  * sum p w without touching the outputs) and the statistics of the error bounds.
  * d_wok: weight | ok << 8 per row (qdc_mis_build_tables; NULL: weight 0, ok).  column_role != 0 for
- * the operand of fragment 0 (streamed through the tiles): d_x = its col_x table; every 16 adjacent
+ * the operand of fragment 0 (streamed through the tiles): d_x = its col_x table; every 32 adjacent
  * columns then share an integer unit (a column more than 2^20 below the largest of its group is
  * sliced at that floor; the bounds use the exponent actually applied).
  *

@@ -4,7 +4,7 @@ set -u
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_contract_score.py tests/test_gpu_cutqc.py -x -q -m gpu > gpurun_out/r2_iter_tests.log 2>&1
 echo "tests rc=$?"; tail -3 gpurun_out/r2_iter_tests.log
-for tn in 96 64; do
+for tn in 128 96 64; do
   QDC_I8_TN=$tn timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/r2_iter_tn$tn.json 2> gpurun_out/r2_iter_tn$tn.err
   echo "bench tn=$tn rc=$?"
   python - <<P

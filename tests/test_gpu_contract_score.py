@@ -196,8 +196,8 @@ def test_int8_sliced_contraction_per_output_bound(cuda, slices):
     with np.errstate(divide="ignore"):
         ea = np.where(np.abs(A).max(axis=1) > 0, np.floor(np.log2(np.abs(A).max(axis=1))) + 1, -2000.0)[:, None]
         fb = np.floor(np.log2(np.abs(Bt).max(axis=1))) + 1
-    # a column more than 2^20 below the largest of its 16-column group is sliced at that floor
-    fb = np.maximum(fb, np.repeat(fb.reshape(-1, 16).max(axis=1), 16) - 20)[None, :]
+    # a column more than 2^20 below the largest of its 32-column group is sliced at that floor
+    fb = np.maximum(fb, np.repeat(fb.reshape(-1, 32).max(axis=1), 32) - 20)[None, :]
     # + 1: the exponent is bumped when the scaled maximum would exceed 127 / 128
     bound = 2.0 ** (ea + fb + 2) * scale * kdim * (slices + 1.1) * 2.0 ** (-8 * slices)
     fp64_noise = 4 * kdim * 2.0 ** -53 * scale * (np.abs(A) @ np.abs(Bt).T)

@@ -164,7 +164,7 @@ def test_i8_error_bounds_formula():
     fold = 0.5 * 1 * 2.0 ** -26                                       # one 16-column group
     assert abs(b[5]["cost"] - 3 * 0.25 * ((1 + 0) * (2 + 0.25) * g5 + 1 * 2 * fold * 2.0 ** -40)) < 1e-25
     assert abs(b[4]["per_output"] / b[5]["per_output"] - 256 * 5.1 / 6.1) < 1e-9
-    # a column more than 2^20 below the largest of its 16-column group is sliced at that floor
+    # a column more than 2^20 below the largest of its 32-column group is sliced at that floor
     Bt2 = torch.tensor([[1.5, 0.0, 0.0, 0.2], [2e-9, 1e-9, 0.0, 0.0]], dtype=torch.float64)
     b2 = rc.i8_error_bounds(A, Bt2, tabs, 0.5, norm)
     assert abs(b2[5]["cost"] - 3 * 0.25 * (1 * (2 + 2.0 ** -19) * g5 + 1 * 2 * fold * 2.0 ** -40)) < 1e-25
