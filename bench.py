@@ -60,6 +60,13 @@ def parse_args():
                          "a-posteriori bounds for these operands (per output and on the MIS cost, "
                          "recombine.i8_error_bounds) stay below --tol")
     ap.add_argument("--tol", type=float, default=1e-10)
+    ap.add_argument("--workload", default="c4", choices=["c4", "c4-circuit", "c5"],
+                    help="c4 (default, the headline): contraction + MIS scoring of synthetic fragment tensors at 2^34 "
+                         "outputs (BASELINE.json configs[3]); c4-circuit: one whole avg_cost evaluation (sim_with_cutting "
+                         "on real cut-DQVA fragments of that shape: simulate -> tensors -> ML model -> contraction -> "
+                         "score); c5: uncut 30-qubit DQVA statevector + MIS cost for a batch of parameter sets "
+                         "(configs[4]), parameter sets dealt over the ranks")
+    ap.add_argument("--param-sets", type=int, default=None, help="parameter sets per step (c5: 128, c4-circuit: 4)")
     args = ap.parse_args()
     if args.slices != "auto":
         args.slices = int(args.slices)
@@ -242,7 +249,7 @@ def measure_dgemm_peak(torch, dev):
     return 2.0 * 8192 ** 3 / best / 1e12
 
 
-def variant_sims_leg(torch, dev):
+def variant_sims_leg(torch, dev, cpu=True):
     """Second BASELINE metric, "fragment-variant sims/s": the statevector engine on the C4
     fragment shapes (DQVA-structured fragments on seeded 3-regular graphs): prep side = 17 qubits,
     the reference's 4^4 preparation variants obtained (exact limit, by linearity) from the 2^4
@@ -295,12 +302,155 @@ def variant_sims_leg(torch, dev):
                      "ref_variants": ref, "ms": t * 1e3, "groups": prog.n_groups, "ops": prog.n_ops}
         total_t += t; total_ref += ref; total_states += n_init
         group_bytes += prog.n_groups * 32.0 * (1 << n) * n_init
-    out.update({"value": total_ref / total_t, "unit": "ref-equivalent variants/s",
-                "states_per_s": total_states / total_t, "ms_total": total_t * 1e3,
-                "gate_traffic_gbs": group_bytes / total_t / 1e9,
-                "note": "337 reference variants of C4 per evaluation; launches: "
-                        "sv_matrix + sv_group x groups + sv_pauli_tensor per fragment"})
+    hbm = measured_peaks().get("hbm_gbs") or 6650.0
+    out.update({"value": total_states / total_t, "unit": "statevectors/s",
+                "ref_equivalent_variants_per_s": total_ref / total_t, "ms_total": total_t * 1e3,
+                "roofline": {"bound": "hbm", "achieved": group_bytes / total_t / 1e9, "peak": hbm, "unit": "GB/s",
+                             "frac": group_bytes / total_t / 1e9 / hbm,
+                             "note": "32 B per amplitude per gate group (read + write of a complex128); states of "
+                                     "2-34 MB each live in the 126 MB L2, so this is L2-resident traffic set against "
+                                     "the HBM copy figure"},
+                "note": "value counts the statevectors actually evolved (2^4 + 1 per evaluation); "
+                        "ref_equivalent counts the 4^4 + 3^4 = 337 circuits the reference would run for the same "
+                        "tensors (qsplit_mlrecon_methods.py:689-691). Launches: sv_matrix + sv_group x groups + "
+                        "sv_pauli_tensor per fragment"})
+    if cpu:
+        # the numpy oracle evolving the SAME fragments, one state each, 1 host core
+        from oracle import statevector as osv
+        t_cpu = 0.0
+        for n_nodes, n_states in ((16, 16), (20, 1)):
+            n, insts, pars = fragment(n_nodes, 7)
+            vals = dict(zip(pars, np.random.default_rng(1).uniform(0, 2 * np.pi, len(pars))))
+            bound = [(g, q, tuple(a.bind(vals[a.param]) if hasattr(a, "bind") else float(a) for a in ps), c)
+                     for g, q, ps, c in insts]
+            t0 = time.time()
+            osv.probabilities(osv.simulate(n, bound))
+            t_cpu += (time.time() - t0) * n_states
+        out["cpu_baseline"] = {"value": total_states / t_cpu, "unit": "statevectors/s", "cores": 1, "kind": "port",
+                               "sample": "numpy oracle (oracle/statevector.py; qiskit-Aer is not installable here): one "
+                                         "17-qubit and one 21-qubit fragment state timed, scaled to the 16 + 1 states"}
     return out
+
+
+def c4_circuit_fragments(seed=3):
+    """A cut DQVA circuit of the C4 shape (BASELINE.json configs[3]): 32 graph nodes in two
+    communities of 16 (3-regular inside, 8 edges across) + 2 ancillas = 34 wires = 2^34 outputs,
+    cut by the reference's own node choice (utils/cutting_funcs.py:112-159) with at most 4 cuts."""
+    import random
+    import networkx as nx
+    from qdc_b200.ansatz import dqv_cut_ansatz
+    from qdc_b200.circuit import Parameter
+    from qdc_b200.qsplit import qsplit_circuit_cutter as qcc
+    from qdc_b200.utils import graph_funcs
+    from qdc_b200.utils.cutting_funcs import simple_choose_nodes
+    rng = np.random.default_rng(seed)
+    for attempt in range(50):
+        G = nx.disjoint_union(nx.random_regular_graph(3, 16, seed=seed + attempt),
+                              nx.random_regular_graph(3, 16, seed=seed + 100 + attempt))
+        for a, b in zip(rng.permutation(16)[:8], rng.permutation(16)[:8]):
+            G.add_edge(int(a), 16 + int(b))
+        partition = [list(range(16)), list(range(16, 32))]
+        random.seed(seed + attempt)
+        np.random.seed(seed + attempt)
+        _, cut_edges = graph_funcs.get_subgraphs(G, partition)
+        try:
+            cut_nodes, hot_nodes = simple_choose_nodes(G, partition, cut_edges, 4)
+        except IndexError:
+            continue
+        order = [int(v) for part in partition for v in np.random.permutation(part)]
+        syms = [Parameter(f"var_{i}") for i in range(33)]
+        circ, cuts = dqv_cut_ansatz.gen_dqva(G, partition, cut_nodes, hot_nodes, order, params=syms,
+                                             init_state="0" * 32, fused=False)
+        if len(cuts) != 4:
+            continue
+        frags, wpm = qcc.cut_circuit(circ, cuts)
+        if len(frags) == 2:
+            return G, circ, frags, wpm
+    raise RuntimeError("no 4-cut instance found")
+
+
+def c4_circuit_leg(torch, dev, n_sets=4, steps=3, contraction="i8:auto"):
+    """ONE timed step = what `avg_cost` does per parameter vector in solve_mis_cut_dqva
+    (mis.py:117-134 -> utils/cutting_funcs.py:167-205): every fragment variant simulated, Pauli tensors,
+    maximum-likelihood models, recombination over 2^34 outputs, MIS objective -- through the
+    reference-named API (`mis.cut_cost`), host parameters in, costs out.  DQVA fragments only populate
+    independent sets, so the contraction runs over the occupied rows / columns (exact compaction)."""
+    from qdc_b200 import mis
+    from qdc_b200.engine import B200Backend
+    G, circ, frags, wpm = c4_circuit_fragments()
+    used = circ.parameters
+    be = B200Backend(device=dev, graph=G)
+    table = np.random.default_rng(2).uniform(0, 2 * np.pi, (n_sets, len(used)))
+    os.environ["QDC_CONTRACTION"] = contraction
+    try:
+        costs = mis.cut_cost(frags, wpm, 1, be, params=table, param_order=used, mode="likely")     # warm-up, compile
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            costs = mis.cut_cost(frags, wpm, 1, be, params=table, param_order=used, mode="likely")
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b) * 1e-3)
+        ref = None
+        if contraction != "f64":
+            os.environ["QDC_CONTRACTION"] = "f64"
+            ref = mis.cut_cost(frags, wpm, 1, be, params=table[:1], param_order=used, mode="likely")
+    finally:
+        os.environ.pop("QDC_CONTRACTION", None)
+    t = min(ts) / n_sets
+    widths = [f.num_qubits for f in frags]
+    return {"ms_per_evaluation": t * 1e3, "evaluations_per_s": 1.0 / t, "outputs_per_evaluation": 2.0 ** circ.num_qubits,
+            "probs_per_s": 2.0 ** circ.num_qubits / t, "param_sets_per_step": n_sets, "fragment_qubits": widths,
+            "cuts": 4, "mode": "likely", "contraction": contraction, "cost_first_set": float(costs[0]),
+            "cost_minus_f64": None if ref is None else float(costs[0] - ref[0]),
+            "note": "mis.cut_cost end to end (host parameter table in, costs out); the distribution is never stored; "
+                    "rows / columns of the fragment tensors that are exactly zero (non-independent fragment "
+                    "outcomes) are dropped before the contraction, which is why a whole evaluation is cheaper than "
+                    "the dense-tensor headline step"}
+
+
+def c5_circuit(n_nodes=29, seed=2):
+    import networkx as nx
+    from qdc_b200.ansatz import dqv_ansatz
+    from qdc_b200.circuit import Parameter
+    G = nx.random_regular_graph(4, n_nodes + 1, seed=seed)
+    G.remove_node(n_nodes)                                    # 29 nodes of degree 3-4 (+ 1 ancilla = 30 qubits)
+    syms = [Parameter(f"var_{i}") for i in range(n_nodes + 1)]
+    circ = dqv_ansatz.gen_dqva(G, P=1, params=syms, init_state="0" * n_nodes, mixer_order=list(range(n_nodes)))
+    return G, circ
+
+
+def c5_leg(torch, dev, n_sets, steps=1, shard=False, n_nodes=29):
+    """BASELINE.json configs[4]: the uncut cost f(params) of solve_mis_dqva (mis.py:639-665) on a
+    30-qubit DQVA statevector (29 nodes + ancilla, 17 GB per state), MIS objective reduced straight
+    from the amplitudes, for a batch of parameter sets; under torchrun the sets are dealt over the
+    ranks ("replicas only": a state fits one GPU, nothing but the scalars is exchanged)."""
+    from qdc_b200 import mis
+    from qdc_b200.engine import B200Backend
+    G, circ = c5_circuit(n_nodes)
+    used = circ.parameters
+    be = B200Backend(device=dev, max_state_bytes=40 << 30)
+    table = np.random.default_rng(4).uniform(0, 2 * np.pi, (n_sets, len(used)))
+    mis.uncut_cost(circ, be, G, params=table[:1], param_order=used)          # compile + warm-up
+    torch.cuda.synchronize()
+    ts, costs = [], None
+    for _ in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        costs = mis.uncut_cost(circ, be, G, params=table, param_order=used, shard=shard)
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e-3)
+    prog, _ = be.compile(circ, param_order=used)
+    n = prog.n_qubits
+    t = float(np.mean(ts))
+    return {"t_step": t, "n_sets": n_sets, "n_qubits": n, "groups": prog.n_groups, "ops": prog.n_ops,
+            "costs_head": [float(c) for c in costs[:2]],
+            # compulsory HBM traffic of one state: the first group only writes (16 B per amplitude), every later
+            # group reads and writes (32 B), the scoring pass reads once (16 B)
+            "bytes_per_state": (16.0 + 32.0 * (prog.n_groups - 1) + 16.0) * 2.0 ** n}
 
 
 def run_b200(args):
@@ -504,9 +654,14 @@ def run_b200(args):
         line["other_methods"] = other_methods_leg(torch, rc, A_d, Bt_d, tabs, scale, k, args,
                                                   outputs_total, cost)
         try:
-            line["variant_sims"] = variant_sims_leg(torch, dev)
+            line["variant_sims"] = variant_sims_leg(torch, dev, cpu=not args.no_cpu_baseline)
         except Exception as exc:
             line["variant_sims"] = {"value": None, "note": f"failed: {exc}"}
+        try:
+            line["c4_circuit"] = c4_circuit_leg(torch, dev, n_sets=2, steps=2,
+                                                contraction="i8:auto" if args.method == "i8" else "f64")
+        except Exception as exc:
+            line["c4_circuit"] = {"ms_per_evaluation": None, "note": f"failed: {exc!r}"}
     if not args.no_cpu_baseline and ws == 1:
         try:
             line["cpu_baseline"] = cpu_reference_sample(args.cpu_sample_bits or 20)
@@ -526,6 +681,20 @@ def run_b200(args):
                                                     last_res, chosen)
             except Exception as exc:
                 line["parity_check"] = {"pass": False, "note": f"failed to run: {exc!r}"}
+    if ws == 1:
+        try:
+            del A_d, Bt_d, A_stage, Bt_stage
+            torch.cuda.empty_cache()
+            c5 = c5_leg(torch, dev, 2, steps=1)
+            hbm = measured_peaks().get("hbm_gbs") or 6650.0
+            line["c5_sample"] = {"states_per_s": c5["n_sets"] / c5["t_step"], "ms_per_state": c5["t_step"] / c5["n_sets"] * 1e3,
+                                 "n_qubits": c5["n_qubits"], "groups": c5["groups"],
+                                 "hbm_gbs": c5["bytes_per_state"] * c5["n_sets"] / c5["t_step"] / 1e9,
+                                 "hbm_frac": c5["bytes_per_state"] * c5["n_sets"] / c5["t_step"] / 1e9 / hbm,
+                                 "note": "2 parameter sets of BASELINE.json configs[4] (mis.uncut_cost, 30 qubits); "
+                                         "`--workload c5` runs the 128-set step, sharded over the ranks"}
+        except Exception as exc:
+            line["c5_sample"] = {"states_per_s": None, "note": f"failed: {exc!r}"}
     print(json.dumps(line), flush=True)
     if ws > 1:
         dist.destroy_process_group()
@@ -559,6 +728,121 @@ def parity_check(rc, A_d, Bt_d, tabs, scale, k, args, cpu_sums, sample_rows, las
                      "allowed": allowed, "pass": passed}
     out["pass"] = ok
     return out
+
+
+def _dist_setup():
+    import torch
+    import torch.distributed as dist
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import _lib, dist as qdist
+    rank, ws, local_rank = qdist.init_from_env()
+    if not torch.cuda.is_available():
+        raise _lib.QdcError("bench.py needs a CUDA device: there is no CPU fallback")
+    _lib.load()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    return torch, dist, rank, ws, local_rank, dev
+
+
+def _max_over_ranks(torch, dist, ws, dev, t):
+    x = torch.tensor([t], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(x, op=dist.ReduceOp.MAX)
+    return float(x.item())
+
+
+def cpu_statevector_sample(n_nodes, seed=7):
+    """The numpy oracle (stand-in for qiskit-Aer, which is not installable here) on ONE fused DQVA
+    statevector of n_nodes + 1 qubits, 1 host core: seconds per state."""
+    import networkx as nx
+    from oracle import statevector as sv
+    rng = np.random.default_rng(seed)
+    Gf = nx.random_regular_graph(3, n_nodes + (n_nodes % 2), seed=seed)
+    insts = []
+    for q in rng.permutation(n_nodes):
+        nb = [int(v) for v in Gf.neighbors(int(q)) if v < n_nodes]
+        insts.append(("zcrx", tuple(nb) + (int(q),), (float(rng.uniform(0, 6.28)),), None))
+    insts += [("rz", (q,), (0.3,), None) for q in range(n_nodes)]
+    t0 = time.time()
+    sv.probabilities(sv.simulate(n_nodes + 1, insts))
+    return time.time() - t0
+
+
+def run_c5(args):
+    """--workload c5: value = uncut cost evaluations (30-qubit statevectors simulated and scored) per
+    second, whole job; a step = `--param-sets` parameter sets (default 128), dealt over the ranks."""
+    torch, dist, rank, ws, local_rank, dev = _dist_setup()
+    n_sets = args.param_sets or 128
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    if ws > 1:
+        dist.barrier()
+    out = c5_leg(torch, dev, n_sets, steps=args.steps, shard=ws > 1)
+    clocks = sampler.stop() if rank == 0 else None
+    t = _max_over_ranks(torch, dist, ws, dev, out["t_step"])
+    if rank == 0:
+        peaks = measured_peaks()
+        hbm = peaks.get("hbm_gbs") or 6650.0
+        achieved = out["bytes_per_state"] * n_sets / ws / t / 1e9
+        line = {"metric": "uncut cost evaluations/s (30-qubit DQVA statevector + MIS reduction)", "value": n_sets / t,
+                "unit": "states/s", "n_gpus": ws, "steps": args.steps, "warmup": 1, "ms_per_step": t * 1e3,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "c128", "data": "synthetic",
+                "config": {"workload": f"C5 uncut DQVA statevector, {out['n_qubits']} qubits, {n_sets} parameter sets per step "
+                                       "(BASELINE.json configs[4])", "parallelism": f"parameter sets x{ws} (replicas only)",
+                           "l2": "one state = 17 GB >> 126 MB L2"},
+                "clocks": clocks,
+                "e2e": {"value": n_sets / t, "unit": "states/s", "ms_per_step": t * 1e3,
+                        "h2d_bytes_per_step": int(n_sets * 30 * 8), "d2h_bytes_per_step": int(n_sets * 24),
+                        "note": "the timed call IS the public API (mis.uncut_cost): host parameter table in, costs out"},
+                "gpu_launches": int((out["groups"] + 3) * n_sets / ws) * args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                             "traffic": None, "kernel": "sv_group_kernel (+ mis_reduce on the amplitudes)",
+                             "algorithmic_bytes_per_state": out["bytes_per_state"],
+                             "note": f"{out['groups']} gate groups per state: 16 B/amplitude written by the first, 32 B by "
+                                     "each later one, 16 B read by the scoring pass"},
+                "result": {"costs_head": out["costs_head"]}}
+        if not args.no_cpu_baseline:
+            try:
+                secs = cpu_statevector_sample(23)
+                line["cpu_baseline"] = {"value": 1.0 / secs, "unit": "states/s", "cores": 1, "kind": "port",
+                                        "sample": f"numpy oracle, ONE fused 24-qubit DQVA state in {secs:.1f} s (a 30-qubit "
+                                                  "state is 64x the work and 17 GB; qiskit-Aer: unavailable on this box)"}
+            except Exception as exc:
+                line["cpu_baseline"] = {"value": None, "sample": f"failed: {exc}"}
+        print(json.dumps(line), flush=True)
+    if ws > 1:
+        dist.destroy_process_group()
+
+
+def run_c4_circuit(args):
+    """--workload c4-circuit: value = reconstructed probs/s of whole avg_cost evaluations on real
+    cut-DQVA fragments (every rank evaluates its share of the parameter sets)."""
+    torch, dist, rank, ws, local_rank, dev = _dist_setup()
+    n_sets = args.param_sets or 4
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    out = c4_circuit_leg(torch, dev, n_sets=max(1, n_sets // ws), steps=max(args.steps, 2),
+                         contraction="i8:auto" if args.method == "i8" else "f64")
+    clocks = sampler.stop() if rank == 0 else None
+    t = _max_over_ranks(torch, dist, ws, dev, out["ms_per_evaluation"] * 1e-3)
+    if rank == 0:
+        line = {"metric": METRIC, "value": ws * out["outputs_per_evaluation"] / t, "unit": "probs/s", "n_gpus": ws,
+                "steps": max(args.steps, 2), "warmup": 1, "ms_per_step": t * 1e3 * max(1, n_sets // ws),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "c128 statevectors, " + out["contraction"] + " contraction", "data": "synthetic",
+                "config": {"workload": "C4 as a circuit: sim_with_cutting + MIS score on 2 cut-DQVA fragments, K = 4, 2^34 outputs",
+                           "fragment_qubits": out["fragment_qubits"], "param_sets_per_rank": max(1, n_sets // ws),
+                           "parallelism": f"parameter sets x{ws}"},
+                "clocks": clocks,
+                "e2e": {"value": ws * out["outputs_per_evaluation"] / t, "unit": "probs/s",
+                        "h2d_bytes_per_step": int(n_sets * 33 * 8), "d2h_bytes_per_step": int(n_sets * 8),
+                        "note": "the timed call IS the public API (mis.cut_cost)"},
+                "gpu_launches": None, "roofline": None, "result": out}
+        print(json.dumps(line), flush=True)
+    if ws > 1:
+        dist.destroy_process_group()
 
 
 def measured_peaks():
@@ -596,6 +880,38 @@ def other_methods_leg(torch, rc, A_d, Bt_d, tabs, scale, k, args, outputs_total,
                          "sum_p_minus_1": r["sum_p"] - 1.0}
         except Exception as exc:
             out[name] = {"value": None, "note": f"failed: {exc}"}
+    # the headline operands are flat (every output ~2^-34, nothing above the 1e-5 threshold, `top`
+    # empty): the same step on PEAKED operands - 64 rows x 64 columns scaled by 2^13, so 4096 outputs
+    # sit at ~1e-4 - exercises the candidate path (flag on the leading order, exact FP64
+    # re-evaluation, top-k) inside a timed region, for the headline method and the FP64 kernel
+    try:
+        Ap, Bp = A_d.clone(), Bt_d.clone()
+        g = torch.Generator(device="cpu").manual_seed(11)
+        hr = torch.randperm(Ap.shape[0], generator=g)[:64].to(Ap.device)
+        hc = torch.randperm(Bp.shape[0], generator=g)[:64].to(Ap.device)
+        Ap[hr] *= 8192.0
+        Bp[hc] *= 8192.0
+        peaked = {}
+        for name, kw in (("headline", dict(method=args.method, slices=args.slices, tol=args.tol)),
+                         ("f64", dict(method="f64"))):
+            ts, res = [], None
+            for it in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                res = rc.contract_and_score(Ap, Bp, tabs, threshold=1e-5, k=k, **kw)
+                e1.record()
+                torch.cuda.synchronize()
+                if it:
+                    ts.append(e0.elapsed_time(e1))
+            r = res.get()
+            peaked[name] = {"ms_per_step": min(ts), "n_candidates": r["n_candidates"], "top": r["top"][:4],
+                            "sum_p_minus_1": r["sum_p"] - 1.0, "cost": r["sum_pw_indset"]}
+        peaked["same_top"] = ([x for x, _ in peaked["headline"]["top"]] == [x for x, _ in peaked["f64"]["top"]]
+                              and peaked["headline"]["n_candidates"] == peaked["f64"]["n_candidates"])
+        out["peaked_operands"] = peaked
+        del Ap, Bp
+    except Exception as exc:
+        out["peaked_operands"] = {"note": f"failed: {exc!r}"}
     return out
 
 
@@ -618,6 +934,10 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_c5(args)
+    elif args.workload == "c4-circuit":
+        run_c4_circuit(args)
     else:
         run_b200(args)
 

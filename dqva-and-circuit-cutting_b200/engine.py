@@ -13,6 +13,7 @@ circuit structure at once (the batch dimension the reference never forms: it cal
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
 from dataclasses import dataclass, field
@@ -234,9 +235,12 @@ class B200Backend:
         if prog is None:
             handle = C.c_void_p()
             gates = _pack_gates(recs)
-            _lib.check(lib.qdc_sv_compile(n_qubits, C.cast(gates, C.c_void_p), len(recs),
-                                          C.c_uint64(zero_mask), self.tile_bits, self.coalesce_bits,
-                                          flags, C.byref(handle)), "qdc_sv_compile")
+            # the program's op and matrix tables are uploaded to the CURRENT device: make it this backend's
+            # (host-only planning on a CPU "device" uploads nothing and needs no context)
+            with (torch.cuda.device(self.device) if torch.device(self.device).type == "cuda" else contextlib.nullcontext()):
+                _lib.check(lib.qdc_sv_compile(n_qubits, C.cast(gates, C.c_void_p), len(recs),
+                                              C.c_uint64(zero_mask), self.tile_bits, self.coalesce_bits,
+                                              flags, C.byref(handle)), "qdc_sv_compile")
             nq, ng, no, nm, tb = (C.c_int() for _ in range(5))
             flip = C.c_uint64()
             _lib.check(lib.qdc_sv_info(handle, C.byref(nq), C.byref(ng), C.byref(no), C.byref(nm),
