@@ -905,7 +905,8 @@ def other_methods_leg(torch, rc, A_d, Bt_d, tabs, scale, k, args, outputs_total,
                     ts.append(e0.elapsed_time(e1))
             r = res.get()
             peaked[name] = {"ms_per_step": min(ts), "n_candidates": r["n_candidates"], "top": r["top"][:4],
-                            "sum_p_minus_1": r["sum_p"] - 1.0, "cost": r["sum_pw_indset"]}
+                            "sum_p_minus_1": r["sum_p"] - 1.0, "cost": r["sum_pw_indset"],
+                            "slices": getattr(res, "slices", None)}
         peaked["same_top"] = ([x for x, _ in peaked["headline"]["top"]] == [x for x, _ in peaked["f64"]["top"]]
                               and peaked["headline"]["n_candidates"] == peaked["f64"]["n_candidates"])
         out["peaked_operands"] = peaked

@@ -15,6 +15,8 @@ File-protocol compatible stage executables live in `cutqc/bin/` (see `cutqc/stag
 """
 from __future__ import annotations
 
+import os
+import pickle
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -225,7 +227,15 @@ class CutQC:
         return prob
 
     def post_process(self, early_termination: int = 0, qubit_limit: Optional[int] = None,
-                     recursion_depth: int = 1, out_dtype=torch.float64) -> List[ReconstructedLayer]:
+                     recursion_depth: int = 1, out_dtype=torch.float64,
+                     dest_folder: Optional[str] = None, resume: bool = False) -> List[ReconstructedLayer]:
+        """Dynamic-definition recursion (main.py:86-139 driving distributor.py:186-260).
+
+        `dest_folder` (optional): mirror the recursion state to disk in the reference's layout -
+        `meta_data.pckl` and `dynamic_definition_<layer>/build_output.pckl`
+        (distributor.py:121-141, 212-215; main.py:452-457; names via helper_fun.get_dirname).
+        `resume=True` continues from the state found there, as the reference does when it is
+        re-invoked with the next `recursion_layer`: layers already on disk are loaded, not rebuilt."""
         if early_termination not in self.kron:
             raise _lib.QdcError("call evaluate(early_termination=(%d,)) first" % early_termination)
         if qubit_limit is None:
@@ -233,7 +243,15 @@ class CutQC:
         schedules: Dict[int, dict] = {}
         outputs: Dict[int, dict] = {}
         layers = []
-        for layer in range(recursion_depth):
+        first = 0
+        if resume:
+            if dest_folder is None:
+                raise _lib.QdcError("resume=True needs the dest_folder that holds meta_data.pckl")
+            schedules, outputs = self._load_state(dest_folder)
+            for layer in sorted(outputs):
+                layers.append(self._wrap(outputs[layer]["reconstructed_prob"], schedules[layer]))
+            first = len(outputs)
+        for layer in range(first, recursion_depth):
             if layer == 0:
                 schedules = initialize_dynamic_definition_schedule(self.counter, qubit_limit, self.verbose)
             else:
@@ -245,13 +263,46 @@ class CutQC:
                     src, schedules[src], int(out["max_states"][out["zoomed_ctr"]]), qubit_limit,
                     self.verbose)
                 out["zoomed_ctr"] += 1
+                if dest_folder is not None:
+                    self._dump_build_output(dest_folder, src, out)       # distributor.py:137-138
             prob = self._layer(schedules[layer], early_termination, out_dtype)
             # main.py:452: bins by decreasing probability (stable, like sorted(..., reverse=True))
             order = torch.sort(prob, descending=True, stable=True).indices
             outputs[layer] = {"zoomed_ctr": 0, "max_states": order, "reconstructed_prob": prob}
             layers.append(self._wrap(prob, schedules[layer]))
+            if dest_folder is not None:
+                os.makedirs(dest_folder, exist_ok=True)
+                with open(os.path.join(dest_folder, "meta_data.pckl"), "wb") as f:
+                    pickle.dump({"counter": self.counter, "dynamic_definition_schedule": schedules}, f)
+                self._dump_build_output(dest_folder, layer, outputs[layer])
         self.schedules = schedules
         return layers
+
+    @staticmethod
+    def _dump_build_output(dest_folder, layer, out):
+        folder = os.path.join(dest_folder, "dynamic_definition_%d" % layer)
+        os.makedirs(folder, exist_ok=True)
+        with open(os.path.join(folder, "build_output.pckl"), "wb") as f:
+            pickle.dump({"zoomed_ctr": int(out["zoomed_ctr"]),
+                         "max_states": [int(x) for x in out["max_states"].cpu().tolist()],
+                         "reconstructed_prob": out["reconstructed_prob"].double().cpu().numpy()}, f)
+
+    def _load_state(self, dest_folder):
+        from .helper_fun import read_dict
+        meta = read_dict(os.path.join(dest_folder, "meta_data.pckl"))
+        if not meta:
+            raise _lib.QdcError(f"no meta_data.pckl under {dest_folder}")
+        schedules = dict(meta["dynamic_definition_schedule"])
+        outputs = {}
+        dev = self.backend.device
+        for layer in sorted(schedules):
+            rec = read_dict(os.path.join(dest_folder, "dynamic_definition_%d" % layer, "build_output.pckl"))
+            if not rec:
+                raise _lib.QdcError(f"layer {layer} of {dest_folder} has a schedule but no build_output.pckl")
+            outputs[layer] = {"zoomed_ctr": int(rec["zoomed_ctr"]),
+                              "max_states": torch.as_tensor(np.asarray(rec["max_states"], dtype=np.int64), device=dev),
+                              "reconstructed_prob": torch.as_tensor(np.asarray(rec["reconstructed_prob"]), device=dev)}
+        return schedules, outputs
 
     def _wrap(self, prob, layer_schedule) -> ReconstructedLayer:
         full_qubits = list(self.circuit.qubits)

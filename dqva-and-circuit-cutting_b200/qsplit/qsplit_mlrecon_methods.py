@@ -26,6 +26,7 @@ The reference samples `shots` outcomes per variant; this engine evaluates the in
 from __future__ import annotations
 
 import itertools
+import os
 from collections.abc import Mapping
 from typing import Dict, List, Optional, Sequence
 
@@ -318,8 +319,8 @@ def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=
     parameter vectors of unbound fragments at once; `linear_inputs` (default) simulates the 2^p
     basis inputs instead of the 4^p SIC preparations when a fragment has at most 4 cut ends
     (same Choi blocks by linearity; the dict view still simulates every variant); `sample=True`
-    draws `shots` outcomes per variant circuit on the device instead of taking the infinite-shot
-    limit (one parameter vector), `seed` makes the draws reproducible."""
+    draws `shots` outcomes per variant circuit (x every parameter vector) on the device instead of
+    taking the infinite-shot limit, `seed` makes the draws reproducible."""
     if not isinstance(tomography_backend, B200Backend):
         raise _lib.QdcError("collect_fragment_data needs a qdc_b200.engine.B200Backend as "
                             "tomography_backend; there is no CPU simulator in this package")
@@ -348,8 +349,6 @@ def collect_fragment_data(fragments, wire_path_map, shots=1, tomography_backend=
         zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in prep)
         prog, auto = be.compile_instructions(n, insts, param_order, zero_mask)
         if sample:
-            if params is not None and np.atleast_2d(np.asarray(params)).shape[0] != 1:
-                raise _lib.QdcError("sample=True evaluates one parameter vector at a time")
             data.append(SampledFragmentData(be, fragment, prep, meas, None, prog, auto, 1, shots,
                                             labels, params, param_order, prep_basis,
                                             seed=None if seed is None else seed + idx))
@@ -446,64 +445,65 @@ def _model_from_counts(data: Mapping, device, rank_cutoff) -> FragmentModel:
 
 
 class SampledFragmentData(FragmentData):
-    """Finite-shot tomography data: every one of the 4^p 3^m variant circuits is simulated and
-    `shots` outcomes are drawn from its distribution on the device (what the reference's
-    qasm_simulator run produces, qsplit_mlrecon_methods.py:20-42, 216-232).  `counts` is the
-    organised table [final bits b][label] (:169-213) as a device tensor; the Mapping view is the
-    reference's dict."""
+    """Finite-shot tomography data: every one of the 4^p 3^m variant circuits is simulated (x all
+    parameter sets) and `shots` outcomes are drawn from each on the device by this package's own
+    sampler (`qdc_sv_sample_counts`: tile masses -> scan -> one warp per shot, Philox counters), which
+    files them straight into the organised table - what the reference's qasm_simulator jobs
+    followed by `organize_tomography_data` produce (qsplit_mlrecon_methods.py:20-42, 169-232).
+    `counts` [n_sets, final bits b, label] is that table as a device tensor; the Mapping view is the
+    reference's dict for parameter set 0."""
 
     def __init__(self, *args, seed=None, **kwargs):
         super().__init__(*args, **kwargs)
-        n, m = self.n_qubits, len(self.meas_qubits)
-        p = len(self.prep_qubits)
-        dev = self.backend.device
-        gen = torch.Generator(device=dev)
-        if seed is not None:
-            gen.manual_seed(int(seed))
+        import ctypes as C
+        lib = _lib.load()
+        be = self.backend
+        n, insts = _frag_insts(self.fragment)
+        p, m = len(self.prep_qubits), len(self.meas_qubits)
+        dev = be.device
+        if seed is None:
+            seed = int.from_bytes(os.urandom(8), "little")
         labels, _ = _fit_matrix(p, m)
         col = {lab: i for i, lab in enumerate(labels)}
         prep_labels = list(itertools.product(prep_state_keys["SIC"], repeat=p))
-        x = torch.arange(1 << n, device=dev)
-        keep = [q for q in range(n) if q not in self.meas_qubits]
-        b = torch.zeros_like(x)
-        for j, q in enumerate(keep):
-            b |= ((x >> q) & 1) << j
-        mid = torch.zeros_like(x)
-        for j, q in enumerate(self.meas_qubits):
-            mid |= ((x >> q) & 1) << j
-        counts = torch.zeros(1 << (n - m), len(labels), dtype=torch.float64, device=dev)
-        for (prep_label, meas_label), probs in self._variant_probabilities_device().items():
-            draws = torch.multinomial(probs.clamp_min(0), int(self.shots), replacement=True, generator=gen)
-            hist = torch.bincount(draws, minlength=1 << n).to(torch.float64)
-            # column of (prep_label, outcome state) for every value of the measured bits
-            cols = torch.empty(1 << m, dtype=torch.long, device=dev)
-            for mv in range(1 << m):
-                state = tuple(basis + ("p" if not (mv >> j) & 1 else "m") for j, basis in enumerate(meas_label))
-                cols[mv] = col[(prep_label, state)]
-            counts.index_put_((b, cols[mid]), hist, accumulate=True)
-        self.counts = counts
-        self.labels = labels
-
-    def _variant_probabilities_device(self):
-        n, insts = _frag_insts(self.fragment)
-        p, m = len(self.prep_qubits), len(self.meas_qubits)
-        prep_labels = list(itertools.product(prep_state_keys["SIC"], repeat=p))
+        rank = {q: i for i, q in enumerate(sorted(self.meas_qubits))}   # kernel: measured value in ascending qubit order
+        meas_mask = sum(1 << q for q in self.meas_qubits)
         zero_mask = ((1 << n) - 1) & ~sum(1 << q for q in self.prep_qubits)
-        out = {}
-        for meas_label in itertools.product(["Z", "X", "Y"], repeat=m):
+        table = None if self.params is None else np.atleast_2d(np.asarray(self.params, dtype=np.float64))
+        n_sets = 1 if table is None else table.shape[0]
+        self.n_sets = n_sets
+        n_init = len(prep_labels)
+        counts = torch.zeros(n_sets, 1 << (n - m), len(labels), dtype=torch.float64, device=dev)
+        ws = torch.empty(max(1, int(lib.qdc_sv_sample_workspace_doubles(n, n_init * n_sets))),
+                         dtype=torch.float64, device=dev)
+        if n_init * n_sets > 65535:
+            raise _lib.QdcError("sample=True: at most 65535 (preparation, parameter set) states per basis choice")
+        for k, meas_label in enumerate(itertools.product(["Z", "X", "Y"], repeat=m)):
             suffix = [(g, (q,), (), None) for q, lab in zip(self.meas_qubits, meas_label)
                       for g in _MEAS_SUFFIX[lab]]
-            prog, auto = self.backend.compile_instructions(n, insts + suffix, self.param_order, zero_mask)
-            states = self.backend.run(prog, auto, self.params, prep_qubits=self.prep_qubits)
-            probs = self.backend.probabilities(states, prog).reshape(len(prep_labels), -1, 1 << n)[:, 0]
+            prog, auto = be.compile_instructions(n, insts + suffix, self.param_order, zero_mask)
+            states = be.run(prog, auto, table, prep_qubits=self.prep_qubits)      # [4^p * n_sets, 2^n]
+            cols = np.empty((n_init, 1 << m), dtype=np.int32)
             for i, prep_label in enumerate(prep_labels):
-                out[(prep_label, meas_label)] = probs[i]
-        return out
+                for v in range(1 << m):
+                    state = tuple(basis + ("m" if (v >> rank[q]) & 1 else "p")
+                                  for basis, q in zip(meas_label, self.meas_qubits))
+                    cols[i, v] = col[(prep_label, state)]
+            d_cols = torch.as_tensor(cols, device=dev)
+            with torch.cuda.device(dev):
+                _lib.check(lib.qdc_sv_sample_counts(_lib.ptr(states), n, n_init, n_sets, C.c_uint64(prog.flip_mask),
+                                                    int(self.shots), C.c_uint64(int(seed) & (2 ** 64 - 1)),
+                                                    C.c_uint64(k), C.c_uint64(meas_mask), _lib.ptr(d_cols),
+                                                    _lib.ptr(counts), counts.shape[2], _lib.ptr(ws),
+                                                    _lib.stream_ptr(None)), "qdc_sv_sample_counts")
+            del states
+        self.counts = counts
+        self.labels = labels
 
     def _materialise(self):
         if self._dict is None:
             n, m = self.n_qubits, len(self.meas_qubits)
-            host = self.counts.cpu().numpy()
+            host = self.counts[0].cpu().numpy()
             seen = np.nonzero(host.sum(axis=1) > 0)[0]
             self._dict = {_bits(int(b), n - m): {lab: float(host[b, i]) for i, lab in enumerate(self.labels)}
                           for b in seen}
@@ -520,7 +520,7 @@ def direct_fragment_model(tomography_data, discard_poor_data=False, rank_cutoff=
         _, W = _fit_matrix(p, m, rank_cutoff)
         blocks = (d.counts.to(torch.complex128) @ torch.as_tensor(W, device=d.counts.device).T)
         T = _tensor_from_choi(blocks.reshape(-1, 2 ** (p + m), 2 ** (p + m)), p, m) / d.shots
-        return FragmentModel(T.unsqueeze(0), p, m, d.cut_labels, d.shots)
+        return FragmentModel(T.reshape(d.counts.shape[0], d.counts.shape[1], -1), p, m, d.cut_labels, d.shots)
     if isinstance(tomography_data, FragmentData):
         d = tomography_data
         T = d.backend.pauli_tensor(d.states, d.prog, d.n_sets, len(d.prep_qubits), d.meas_qubits,

@@ -177,6 +177,26 @@ int  qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int6
 int  qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t flip_mask,
                   double* d_probs, void* stream);
 
+/* ---- finite-shot tomography: sample the variants of one measurement-basis choice ------------------
+ * Replaces run_circuits on qasm_simulator (qsplit_mlrecon_methods.py:20-42, jobs of <= 8192 shots)
+ * followed by the regrouping of organize_tomography_data (:169-213): `shots` outcomes are drawn from
+ * |amp|^2 of every state of the batch and counted straight into the organised table
+ *   d_counts[(set * 2^(n - m) + b) * ld + d_columns[init * 2^m + v]] += 1.0
+ * where, for the drawn basis state x (flip frame undone), b = the bits of the qubits outside
+ * meas_mask (ascending qubit order) and v = the bits of the qubits in meas_mask.  d_columns maps
+ * (preparation index, measured value) to the column of the (prep label, measured state) pair in the
+ * caller's label list; d_counts is accumulated into (zero it before the first basis choice).
+ * d_state: [n_init * n_sets][2^n_qubits] complex128, state = init * n_sets + set (qdc_sv_run order).
+ * Draw j of state (init, set) uses the counter-based generator Philox4x32-10 keyed by `seed` and
+ * `stream_id` (pass the index of the basis choice): the table is a function of the arguments, not of
+ * the launch order.  d_workspace: qdc_sv_sample_workspace_doubles(n_qubits, n_init * n_sets) doubles.
+ * At most 65535 states per call.  Launches 3 kernels (mass, scan, draw); allocates nothing. */
+int64_t qdc_sv_sample_workspace_doubles(int n_qubits, int64_t n_states);
+int  qdc_sv_sample_counts(const void* d_state, int n_qubits, int64_t n_init, int64_t n_sets,
+                          uint64_t flip_mask, int64_t shots, uint64_t seed, uint64_t stream_id,
+                          uint64_t meas_mask, const int32_t* d_columns, double* d_counts, int64_t ld,
+                          double* d_workspace, void* stream);
+
 /* ---- K3 + K4: fragment tensor in the Pauli basis straight from the amplitudes ---------------
  * Replaces, in the exact (infinite-shot) limit, the 3^m measurement variants + organize +
  * least-squares inversion + Choi reshaping of qsplit_mlrecon_methods.py:116-317, 428-440 (and

@@ -443,3 +443,78 @@ def ckt_generate_reconstructed_output(full_qubits, subcircuits, unordered, smart
         _, ordered = zip(*sorted(zip(unordered_qubit, bits), reverse=True))
         out[int("".join(ordered), 2)] = p
     return out
+
+
+_CKT_INIT_EXPANSION = {"zero": ["zero"], "I": ["+zero", "+one"], "X": ["2plus", "-zero", "-one"],
+                       "Y": ["2plusI", "-zero", "-one"], "Z": ["+zero", "-one"]}
+_CKT_PHYSICAL = {"zero": (1, "zero"), "+zero": (1, "zero"), "+one": (1, "one"), "2plus": (2, "plus"),
+                 "-zero": (-1, "zero"), "-one": (-1, "one"), "2plusI": (2, "plusI")}
+
+
+def ckt_generate_summation_terms(subcircuits, complete_path_map, num_cuts):   # wire_cutting_post_processing.py:225-337
+    """(summation_terms, subcircuit_entries, subcircuit_instances) with the CKT numbering: entries
+    and instances are numbered in order of first appearance while the 4^num_cuts labels are walked
+    with cut 0 as the LEAST significant base-4 digit (get_label :48-68)."""
+    pairs = get_pairs(complete_path_map)                                       # :23-46, same walk
+    n_sub = len(subcircuits)
+    terms, entries, instances = [], {s: {} for s in range(n_sub)}, {s: {} for s in range(n_sub)}
+    for idx in range(4 ** num_cuts):
+        label = ["IXYZ"[(idx >> (2 * c)) & 3] for c in range(num_cuts)]
+        sub_label = {s: {"init": "", "meas": ""} for s in range(n_sub)}        # attribute_label :71-105
+        for c, (O_q, rho_q) in zip(label, pairs):
+            sub_label[O_q["subcircuit_idx"]]["meas"] += c
+            sub_label[rho_q["subcircuit_idx"]]["init"] += c
+        term = {}
+        for s in range(n_sub):
+            key = (sub_label[s]["init"], sub_label[s]["meas"])
+            if key not in entries[s]:
+                qubits = list(subcircuits[s].qubits)
+                init, meas = ["zero"] * len(qubits), ["comp"] * len(qubits)    # fill_label :108-146
+                i_ctr = m_ctr = 0
+                for O_q, rho_q in pairs:
+                    if O_q["subcircuit_idx"] == s:
+                        meas[qubits.index(O_q["subcircuit_qubit"])] = sub_label[s]["meas"][m_ctr]
+                        m_ctr += 1
+                    if rho_q["subcircuit_idx"] == s:
+                        init[qubits.index(rho_q["subcircuit_qubit"])] = sub_label[s]["init"][i_ctr]
+                        i_ctr += 1
+                kron_term = []
+                for combo in itertools.product(*[_CKT_INIT_EXPANSION[x] for x in init]):   # get_init_meas :149-189
+                    coeff = 1
+                    phys = []
+                    for x in combo:                                            # convert_to_physical_init :192-222
+                        c, name = _CKT_PHYSICAL[x]
+                        coeff *= c
+                        phys.append(name)
+                    inst_key = (tuple(phys), tuple(meas))
+                    if inst_key not in instances[s]:
+                        instances[s][inst_key] = len(instances[s])
+                    kron_term.append((coeff, instances[s][inst_key]))
+                entries[s][key] = (len(entries[s]), kron_term)
+            term[s] = entries[s][key][0]
+        terms.append(term)
+    return terms, entries, instances
+
+
+def ckt_run_subcircuit_instances(subcircuits, subcircuit_instances):   # wire_cutting_evaluation.py:299-380
+    """{subcircuit: {instance index: measured probabilities}}: one exact statevector simulation per
+    unmutated instance (`I` and `Z` share the circuit, :100-124), then `measure_prob` (:249-296)."""
+    out = {}
+    for s, sub in enumerate(subcircuits):
+        out[s] = {}
+        for (init, meas), idx in subcircuit_instances[s].items():
+            if idx in out[s]:
+                continue
+            raw = instance_probabilities(sub, init, meas)                      # raises on a bare 'Z', as :190-193
+            for mutated in mutate_measurement_basis(tuple(meas)):
+                out[s][subcircuit_instances[s][(init, tuple(mutated))]] = measure_instance(raw, mutated)
+    return out
+
+
+def ckt_reconstruct_full_distribution(full_qubits, subcircuit_instance_probs, cuts):   # wire_cutting.py:149-187
+    terms, entries, _ = ckt_generate_summation_terms(cuts["subcircuits"], cuts["complete_path_map"],
+                                                     cuts["num_cuts"])
+    entry_probs = ckt_attribute_shots(entries, subcircuit_instance_probs)
+    unordered, smart_order, _ = ckt_build(terms, entry_probs, cuts["num_cuts"])
+    return ckt_generate_reconstructed_output(full_qubits, cuts["subcircuits"], unordered, smart_order,
+                                             cuts["complete_path_map"])

@@ -135,3 +135,66 @@ def test_ckt_wrappers_match_numpy_twin(cuda, name):
     ordered = ckt.generate_reconstructed_output(circ, frags, got, order_g, cpm).cpu().numpy()
     assert np.abs(ordered - co.ckt_generate_reconstructed_output(list(circ.qubits), frags, want, order_w, cpm)).max() < TOL
     assert np.abs(ordered - full).max() < TOL
+
+
+@pytest.mark.parametrize("name", ["ckt5", "there_and_back", "chain3", "dqva6_fused"])
+def test_ckt_reconstruct_full_distribution(cuda, name):
+    """CKT's two top-level calls (wire_cutting.py:88-187): `evaluate_subcircuits` instance by
+    instance against the oracle's restatement of `_run_subcircuit_batch` + `measure_prob`, and
+    `reconstruct_full_distribution` against the oracle's and against the uncut statevector - the
+    assertion of the reference's own test (test_circuit_cutting.py:69-82, MSE ~ 0) on its own
+    5-qubit circuit and on cases with 2 cuts / 3 subcircuits."""
+    from qdc_b200.cutqc import ckt
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    K = sum(len(p) - 1 for p in cpm.values())
+    cuts = {"subcircuits": frags, "complete_path_map": cpm, "num_cuts": K}
+    assert ckt._generate_metadata(cuts) == co.ckt_generate_summation_terms(frags, cpm, K)
+    want_inst = co.ckt_run_subcircuit_instances(frags, co.ckt_generate_summation_terms(frags, cpm, K)[2])
+    got_inst = ckt.evaluate_subcircuits(cuts, backend=_be(cuda))
+    for s in want_inst:
+        assert sorted(got_inst[s]) == sorted(want_inst[s])
+        for i, v in want_inst[s].items():
+            assert np.abs(got_inst[s][i].cpu().numpy() - v).max() < TOL
+    got = ckt.reconstruct_full_distribution(circ, got_inst, cuts, num_threads=2).cpu().numpy()
+    want = co.ckt_reconstruct_full_distribution(list(circ.qubits), want_inst, cuts)
+    full = sv.probabilities(sv.simulate(circ.num_qubits, circ.to_instructions()))
+    assert np.abs(got - want).max() < TOL
+    assert np.mean((got - full) ** 2) < 1e-24 and np.abs(got - full).max() < TOL
+    # numpy instance probabilities (what a CKT user holds) are accepted as well
+    got_np = ckt.reconstruct_full_distribution(circ, want_inst, cuts).cpu().numpy()
+    assert np.abs(got_np - full).max() < TOL
+
+
+def test_dynamic_definition_state_on_disk_and_resume(cuda, tmp_path):
+    """f4: `post_process(dest_folder=)` writes the reference's recursion state (meta_data.pckl,
+    dynamic_definition_<layer>/build_output.pckl with its three keys, distributor.py:121-141,
+    main.py:452-457); stopping after one layer and resuming from disk gives the same layers as one
+    in-memory run, and the zoomed_ctr of a zoomed layer is advanced on disk as the reference does."""
+    from qdc_b200.cutqc.main import CutQC
+    from qdc_b200.cutqc.helper_fun import get_dirname, read_dict
+    circ, frags, wpm = cc.CASES["chain3"]()
+    job = CutQC.from_fragments(circ, frags, wpm, _be(cuda)).evaluate()
+    want = job.post_process(qubit_limit=2, recursion_depth=4)
+    assert len(want) >= 3
+    dest = str(tmp_path / get_dirname("chain3", 3, 0, "sv", 1, 2, "build"))
+    assert dest.endswith("cutqc_data/chain3/cc_3/sv_0_2_1")
+    first = job.post_process(qubit_limit=2, recursion_depth=1, dest_folder=dest)
+    assert len(first) == 1
+    meta = read_dict(f"{dest}/meta_data.pckl")
+    assert set(meta) == {"counter", "dynamic_definition_schedule"} and list(meta["dynamic_definition_schedule"]) == [0]
+    out0 = read_dict(f"{dest}/dynamic_definition_0/build_output.pckl")
+    assert set(out0) == {"zoomed_ctr", "max_states", "reconstructed_prob"} and out0["zoomed_ctr"] == 0
+    prob0 = want[0].prob.cpu().numpy()
+    assert np.array_equal(out0["reconstructed_prob"], prob0)
+    assert out0["max_states"] == sorted(range(len(prob0)), key=lambda x: prob0[x], reverse=True)   # main.py:455
+    got = job.post_process(qubit_limit=2, recursion_depth=4, dest_folder=dest, resume=True)
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert a.schedule == b.schedule and torch.equal(a.prob, b.prob)
+    meta = read_dict(f"{dest}/meta_data.pckl")
+    assert list(meta["dynamic_definition_schedule"]) == list(range(len(want)))
+    assert sum(read_dict(f"{dest}/dynamic_definition_{l}/build_output.pckl")["zoomed_ctr"]
+               for l in range(len(want))) == len(want) - 1
+    with pytest.raises(Exception):
+        job.post_process(resume=True)

@@ -203,3 +203,28 @@ def test_ckt_manual_cut_known_answer(mode):
     for bits, v in co.reorder(list(circ.qubits), vec, cpm, frags, schedule).items():
         rebuilt2[int(bits, 2)] = v
     assert np.mean((rebuilt2 - full) ** 2) < 1e-24 and np.abs(rebuilt2 - full).max() < 1e-10
+
+
+@pytest.mark.parametrize("name", ["ckt5", "chain3", "there_and_back"])
+def test_ckt_reconstruct_full_distribution_restatement(name):
+    """CKT's top-level entry (wire_cutting.py:149-187: _generate_metadata -> _attribute_shots -> build
+    -> generate_reconstructed_output) restated in the oracle reproduces the uncut distribution, as
+    the reference's own test demands of it (test_circuit_cutting.py:69-82), and its summation-term
+    bookkeeping has the shape the reference documents (4^cuts terms, one entry per distinct
+    (init, meas) label pair, every instance a physical initialisation)."""
+    import cutqc_cases as cc
+    from oracle import cutqc_oracle as co
+    circ, frags, wpm = cc.CASES[name]()
+    cpm = co.complete_path_map_from_wire_path_map(wpm)
+    K = sum(len(p) - 1 for p in cpm.values())
+    cuts = {"subcircuits": frags, "complete_path_map": cpm, "num_cuts": K}
+    terms, entries, instances = co.ckt_generate_summation_terms(frags, cpm, K)
+    assert len(terms) == 4 ** K and all(set(t) == set(range(len(frags))) for t in terms)
+    for s in range(len(frags)):
+        assert sorted(e[0] for e in entries[s].values()) == list(range(len(entries[s])))
+        assert all(lab in ("zero", "one", "plus", "plusI") for init, _ in instances[s] for lab in init)
+    probs = co.ckt_run_subcircuit_instances(frags, instances)
+    assert all(sorted(probs[s]) == list(range(len(instances[s]))) for s in probs)
+    got = co.ckt_reconstruct_full_distribution(list(circ.qubits), probs, cuts)
+    full = sv.probabilities(sv.simulate(circ.num_qubits, circ.to_instructions()))
+    assert np.mean((got - full) ** 2) < 1e-24 and np.abs(got - full).max() < 1e-10

@@ -169,3 +169,34 @@ def test_i8_error_bounds_formula():
     b2 = rc.i8_error_bounds(A, Bt2, tabs, 0.5, norm)
     assert abs(b2[5]["cost"] - 3 * 0.25 * (1 * (2 + 2.0 ** -19) * g5 + 1 * 2 * fold * 2.0 ** -40)) < 1e-25
     assert set(b) == {2, 3, 4, 5, 6}
+
+
+def test_ckt_summation_terms_numbering_matches_restatement():
+    """Host bookkeeping of `cutqc.ckt.generate_summation_terms` (digit-tuple lookup) == the oracle's
+    label-string restatement of wire_cutting_post_processing.py:225-337, dict for dict, including
+    the first-appearance numbering of entries and instances; a wrong num_cuts is refused."""
+    import cutqc_cases as cc
+    from oracle import cutqc_oracle as co
+    from qdc_b200.cutqc import ckt
+    for name in cc.CASES:
+        circ, frags, wpm = cc.CASES[name]()
+        cpm = co.complete_path_map_from_wire_path_map(wpm)
+        K = sum(len(p) - 1 for p in cpm.values())
+        got = ckt.generate_summation_terms(frags, cpm, K)
+        want = co.ckt_generate_summation_terms(frags, cpm, K)
+        assert got == want
+        for s in want[2]:
+            assert list(got[2][s].items()) == list(want[2][s].items())
+        with pytest.raises(ValueError):
+            ckt.generate_summation_terms(frags, cpm, K + 1)
+
+
+def test_get_dirname_spelling():
+    from qdc_b200.cutqc.helper_fun import get_dirname
+    assert get_dirname("bv", 10, None, None, None, None, "cutter") == "./cutqc_data/bv/cc_10"
+    assert get_dirname("bv", 10, None, "sv", None, None, "evaluator") == "./cutqc_data/bv/cc_10/sv"
+    assert get_dirname("bv", 10, 1, "sv", None, None, "vertical_collapse") == "./cutqc_data/bv/cc_10/sv/et_1"
+    assert get_dirname("bv", 10, 1, "sv", 4, 20, "build") == "./cutqc_data/bv/cc_10/sv_1_20_4"
+    assert get_dirname("bv", 10, None, None, 4, 20, "runtime") == "./runtime/bv/cc_10/q_20_4"
+    with pytest.raises(Exception):
+        get_dirname("bv", 10, None, None, None, None, "nope")
