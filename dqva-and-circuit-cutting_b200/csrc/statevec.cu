@@ -68,6 +68,7 @@ struct GroupArgs {
     long long init_lo;
     uint64_t prep_mask, hole_mask;
     int n, t, n_sets, n_mats, op_lo, op_hi, first, n_runs, n_prep, n_codes;
+    int bulk;                 // stage the tile with bulk copies (runs of >= 64 bytes)
     uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
     uint8_t prep_q[MAX_PREP];
     double code[MAX_CODES][4];
@@ -108,6 +109,38 @@ __device__ __forceinline__ uint32_t insert_fixed(uint32_t i, int n_fixed, const 
     return i;
 }
 
+// ---- bulk-copy staging of a tile (cp.async.bulk, one instruction per contiguous run) ------------------
+// A tile is 2^t amplitudes whose full indices differ only in the group's local qubits; its lowest
+// 2^p0 local indices (p0 = position of the lowest non-local qubit >= the coalesce bits) are contiguous
+// in HBM, so the tile is 2^(t - p0) runs of 16 << p0 bytes: each is ONE bulk copy HBM -> shared
+// memory (completion counted in bytes on an mbarrier) and one bulk copy back, instead of a load,
+// a 64-bit index walk and a store per amplitude.
+__device__ __forceinline__ uint32_t sv_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sv_mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sv_smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void sv_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sv_smem_u32(bar)), "r"(bytes) : "memory");
+}
+// bounded wait: a copy that never lands traps instead of hanging the device
+__device__ __forceinline__ void sv_mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(sv_smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void sv_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(sv_smem_u32(dst)), "l"(src), "r"(bytes), "r"(sv_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void sv_bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 ::"l"(dst), "r"(sv_smem_u32(src)), "r"(bytes) : "memory");
+}
+
 constexpr int OPS_CHUNK = 32;          // ops staged in shared memory at a time
 constexpr int TAB_LO_BITS = 6;          // diagonal-run phase table over the low tile bits
 
@@ -118,6 +151,7 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
     __shared__ SvOp sh_ops[OPS_CHUNK];
     __shared__ double sh_mats[OPS_CHUNK][8];
     __shared__ double2 sh_tab[(1 << TAB_LO_BITS) + (1 << (13 - TAB_LO_BITS))];
+    __shared__ __align__(8) uint64_t sh_bar;
 
     const long long blk = blockIdx.x;
     const long long batch = blk / a.n_tiles;
@@ -137,28 +171,48 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
     const uint64_t hole = a.hole_mask;
     const uint64_t x_first = expand_runs(tid, a.n_runs, a.run_pos, a.run_len);
     const uint64_t x_step = expand_runs(nthr, a.n_runs, a.run_pos, a.run_len);
+    // contiguous runs of the tile in HBM (see the bulk-copy note above)
+    const int p0 = a.n_runs ? (a.run_pos[0] < a.t ? a.run_pos[0] : a.t) : a.t;
+    const uint32_t n_chunks = T >> p0, chunk_bytes = 16u << p0;
+    const bool bulk = a.bulk != 0;
 
     if (a.first) {
-        // initial product state: prep qubit j in code[digit_j], every other qubit in |0>
-        long long v = a.init_lo + batch / a.n_sets;
-        int digit[MAX_PREP];
+        // initial product state: prep qubit j in code[digit_j], every other qubit in |0>.  All but
+        // 2^n_prep amplitudes of a state are zero: clear the tile, then place the few that fall in it.
+        for (uint32_t l = tid; l < T; l += nthr) tile[l] = make_double2(0.0, 0.0);
+        __syncthreads();
+        if ((base & ~a.prep_mask) == 0ull) {                       // uniform over the CTA
+            long long v = a.init_lo + batch / a.n_sets;
+            int digit[MAX_PREP];
 #pragma unroll
-        for (int j = MAX_PREP - 1; j >= 0; --j)
-            if (j < a.n_prep) { digit[j] = (int)(v % a.n_codes); v /= a.n_codes; }
-        uint64_t x = x_first;
-        for (uint32_t l = tid; l < T; l += nthr, x = ((x | hole) + x_step) & ~hole) {
-            const uint64_t full = x | base;
-            double2 amp = make_double2(0.0, 0.0);
-            if ((full & ~a.prep_mask) == 0ull) {                   // rare: 2^n_prep basis states per state
-                amp = make_double2(1.0, 0.0);
+            for (int j = MAX_PREP - 1; j >= 0; --j)
+                if (j < a.n_prep) { digit[j] = (int)(v % a.n_codes); v /= a.n_codes; }
+            for (uint32_t k = tid; k < (1u << a.n_prep); k += nthr) {
+                uint64_t full = 0;
+                double2 amp = make_double2(1.0, 0.0);
 #pragma unroll 1
                 for (int j = 0; j < a.n_prep; ++j) {
-                    const int bit = (int)((full >> a.prep_q[j]) & 1ull);
+                    const int bit = (int)((k >> j) & 1u);
+                    full |= (uint64_t)bit << a.prep_q[j];
                     amp = cmul(amp, make_double2(a.code[digit[j]][2 * bit], a.code[digit[j]][2 * bit + 1]));
                 }
+                if ((full & hole) != base) continue;               // another tile's amplitude
+                uint64_t l = full & ~hole;
+                for (int r = a.n_runs - 1; r >= 0; --r) {          // full index -> tile-local index
+                    const int p = a.run_pos[r], w = a.run_len[r];
+                    l = ((l >> (p + w)) << p) | (l & ((1ull << p) - 1ull));
+                }
+                tile[l] = amp;
             }
-            tile[l] = amp;
         }
+    } else if (bulk) {
+        if (tid == 0) sv_mbar_init(&sh_bar, 1);
+        __syncthreads();
+        if (tid == 0) sv_mbar_expect_tx(&sh_bar, T * 16u);
+        for (uint32_t j = tid; j < n_chunks; j += nthr)
+            sv_bulk_g2s(tile + ((size_t)j << p0), st + (expand_runs((uint64_t)j << p0, a.n_runs, a.run_pos, a.run_len) | base),
+                        chunk_bytes, &sh_bar);
+        sv_mbar_wait(&sh_bar, 0);
     } else {
         // all loads of a batch are issued before the first one is consumed (8 in flight per thread)
         constexpr int U = 8;
@@ -262,6 +316,17 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
             }
             __syncthreads();
         }
+    }
+    if (bulk) {
+        // the gate passes wrote the tile through the generic proxy: order them before the bulk reads
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        for (uint32_t j = tid; j < n_chunks; j += nthr)
+            sv_bulk_s2g(st + (expand_runs((uint64_t)j << p0, a.n_runs, a.run_pos, a.run_len) | base),
+                        tile + ((size_t)j << p0), chunk_bytes);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory is released at exit
+        return;
     }
     __syncthreads();
     {
@@ -804,7 +869,7 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
     int t = tile_bits <= 0 ? 12 : tile_bits;
     if (t > n) t = n;
     QDC_REQUIRE(t >= 1 && t <= 13, "tile_bits in [1, 13] (2^13 * 16 B = 128 KB of shared memory)");
-    int c = coalesce_bits < 0 ? 4 : coalesce_bits;
+    int c = coalesce_bits < 0 ? 5 : coalesce_bits;          // 512-byte runs for the bulk copies
     if (c > t) c = t;
     if (t < n && c >= t) c = t - 1;      // leave room for at least one non-local target
     const uint64_t all = n == 64 ? ~0ull : ((1ull << n) - 1ull);
@@ -1076,6 +1141,8 @@ extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t ini
     }
     QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_group_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         cudaSharedmemCarveoutMaxShared));
+    bool use_bulk = true;
+    if (const char* env = getenv("QDC_SV_BULK")) use_bulk = atoi(env) != 0;   // tuning knob: 0 = per-element staging
     for (size_t g = 0; g < prog->groups.size(); ++g) {
         const Group& gr = prog->groups[g];
         a.op_lo = gr.first_op; a.op_hi = gr.first_op + gr.n_ops;
@@ -1083,6 +1150,10 @@ extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t ini
         a.n_runs = gr.n_runs;
         a.hole_mask = ~gr.local_mask;                      // bits above n never receive a carry-out that matters
         for (int r = 0; r < gr.n_runs; ++r) { a.run_pos[r] = gr.run_pos[r]; a.run_len[r] = gr.run_len[r]; }
+        {
+            const int p0 = gr.n_runs ? (gr.run_pos[0] < prog->t ? gr.run_pos[0] : prog->t) : prog->t;
+            a.bulk = use_bulk && p0 >= 2;                  // >= 64-byte runs; shorter ones go element by element
+        }
         sv_group_kernel<<<(unsigned)grid, threads, smem, s>>>(a);
         QDC_CHECK_LAUNCH();
     }

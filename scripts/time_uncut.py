@@ -11,7 +11,11 @@ from qdc_b200.circuit import Parameter
 
 def case(n, n_sets, tile_bits, coalesce, fused=True):
     dev = torch.device("cuda:0")
-    G = nx.random_regular_graph(3, n, seed=2)
+    if n % 2 == 0:
+        G = nx.random_regular_graph(3, n, seed=2)
+    else:                                   # the bench's C5 graph: 4-regular on n + 1 nodes, one removed
+        G = nx.random_regular_graph(4, n + 1, seed=2)
+        G.remove_node(n)
     syms = [Parameter(f"var_{i}") for i in range(n + 1)]
     circ = dqv_ansatz.gen_dqva(G, P=1, params=syms, init_state="0" * n, barriers=0, fused=fused,
                                mixer_order=list(range(n)))

@@ -54,6 +54,7 @@ def test_sampler_counts_match_probabilities(cuda, n, meas_mask, flip):
     psi *= rng.random((n_init * n_sets, 1 << n)) < 0.3                  # many exact zeros
     psi[:, : (1 << n) // 2] *= 3.0                                      # uneven mass over the tiles
     psi[1] *= 0.25                                                      # an unnormalised state is sampled by its own mass
+    psi[2] = 0.0                                                        # a state without norm draws nothing
     states = torch.as_tensor(psi, device=cuda)
     cols = np.arange(n_init * (1 << m)).reshape(n_init, 1 << m)         # one column per (init, measured value)
     counts = _sample(cuda, states, n, n_init, n_sets, flip, shots, 1234, 5, meas_mask, cols).cpu().numpy()
@@ -71,12 +72,16 @@ def test_sampler_counts_match_probabilities(cuda, n, meas_mask, flip):
             stored = np.abs(psi[init * n_sets + s]) ** 2
             p = np.empty_like(stored)
             p[xs] = stored[xs ^ flip]                                   # logical x lives at stored index x ^ flip
-            p /= p.sum()
             hist = counts[s][b, init * (1 << m) + v]                    # histogram of this state over x
+            if p.sum() == 0.0:
+                assert hist.sum() == 0
+                continue
+            p /= p.sum()
             assert hist.sum() == shots
             assert np.all(hist[p == 0] == 0)
             sigma = np.sqrt(shots * p * (1 - p))
-            assert np.all(np.abs(hist - shots * p) <= 6 * sigma + 1)
+            # 6 sigma, plus room for the Poisson tail of the ~10^6 cells whose expectation is << 1
+            assert np.all(np.abs(hist - shots * p) <= 6 * sigma + 6)
             big = shots * p >= 5
             chi2 += (((hist - shots * p) ** 2)[big] / (shots * p)[big]).sum()
             dof += int(big.sum())
