@@ -128,15 +128,41 @@ def qaoa_plus_cost(circuit, backend: B200Backend, graph, Lambda: float, params=N
 
 def top_strings(dist, graph, cutoff=1, threshold=1e-5, best_weight=0, num_anc=None):
     """Bitstrings among the `cutoff` most probable (p > threshold) that are independent sets
-    heavier than `best_weight` (mis.py:232-242), from the fused on-device top-k when present."""
+    heavier than `best_weight` (mis.py:232-242), from the fused on-device top-k when present.
+
+    The reference strips the ancillas FIRST (helper_funcs.py:3-16 sums entries that differ only in
+    ancilla bits) and applies `threshold` and `cutoff` afterwards; the device ranks full-width
+    bitstrings.  The fused candidates are therefore merged by node string before the threshold and
+    the cut-off are applied, and the fused list is only trusted when it cannot have missed a
+    partner: every candidate above the threshold was returned (`n_candidates <= k`), or the merged
+    list holds `cutoff` entries and the last of them beats the runner-up by more than the
+    2^num_anc - 1 partners that may not have been returned could add (each is below the smallest
+    probability returned).  Otherwise, when the distribution was stored, the reference's dict path
+    runs; when it was not, the merged list is the best available answer."""
     from .utils.graph_funcs import is_indset
     from .utils.helper_funcs import hamming_weight
     n = graph.number_of_nodes()
-    if getattr(dist, "score", None) is not None and len(dist.score.top_x) >= cutoff:
-        top = [(format(x & ((1 << n) - 1), f"0{n}b"), p) for x, p in dist.score.get()["top"]]
-    else:
+    top = None
+    score = getattr(dist, "score", None)
+    if score is not None and len(score.top_x) >= cutoff:
+        got = score.get()
+        merged = {}
+        for x, p in got["top"]:
+            key = format(x & ((1 << n) - 1), f"0{n}b")
+            merged[key] = merged.get(key, 0.0) + p               # insertion order = device rank
+        ranked = sorted(((k, v) for k, v in merged.items() if v > threshold), key=lambda t: -t[1])
+        complete = got.get("n_candidates", len(got["top"]) + 1) <= len(got["top"])
+        anc = num_anc if num_anc is not None else max(getattr(dist, "n_wires", n) - n, 0)
+        floor = min((p for _, p in got["top"]), default=0.0)       # nothing that was not returned is above this
+        slack = ((1 << anc) - 1) * floor                           # what unseen partners could add to a string
+        runner_up = ranked[cutoff][1] if len(ranked) > cutoff else floor
+        safe = len(ranked) >= cutoff and (anc == 0 or ranked[cutoff - 1][1] > runner_up + slack)
+        if complete or safe or getattr(dist, "P", None) is None:
+            top = ranked
+    if top is None:
         from .utils.helper_funcs import strip_ancillas
-        probs = strip_ancillas(dict(dist), num_anc if num_anc is not None else dist.n_wires - n)
+        anc = num_anc if num_anc is not None else dist.n_wires - n
+        probs = strip_ancillas(dict(dist), num_anc=anc) if anc else dict(dist)
         top = sorted([(k, v) for k, v in probs.items() if v > threshold], key=lambda t: -t[1])
     top = top[:cutoff]
     return [(s, hamming_weight(s)) for s, _ in top if is_indset(s, graph)

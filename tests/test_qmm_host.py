@@ -200,3 +200,38 @@ def test_get_dirname_spelling():
     assert get_dirname("bv", 10, None, None, 4, 20, "runtime") == "./runtime/bv/cc_10/q_20_4"
     with pytest.raises(Exception):
         get_dirname("bv", 10, None, None, None, None, "nope")
+
+
+def test_top_strings_merges_ancilla_partners_before_threshold_and_cutoff():
+    """mis.py:229-242 applies threshold and cutoff AFTER strip_ancillas (which sums entries that
+    differ only in ancilla bits); the fused device list ranks full-width strings, so equal node
+    strings are merged first - checked against the reference order of operations on a distribution
+    with weight on ancilla = 1."""
+    import networkx as nx
+    from qdc_b200 import mis
+    from oracle import mis_oracle as mo
+    G = nx.path_graph(3)                                  # independent sets: 000 001 010 100 101
+    probs = {"0101": 0.30, "1101": 0.25, "0010": 0.35, "1010": 0.05, "0100": 0.05}   # ancilla = first character
+
+    class Score:
+        def __init__(self, top, n_cand):
+            self.top_x = [x for x, _ in top]
+            self._r = {"top": top, "n_candidates": n_cand}
+
+        def get(self):
+            return self._r
+
+    class Dist(dict):
+        n_wires = 4
+        P = object()
+
+    full = sorted(((int(k, 2), v) for k, v in probs.items()), key=lambda t: -t[1])
+    want = mo.better_strs(mo.top_probs(mo.strip_ancillas(probs, 1), threshold=1e-5, cutoff=1), G, "000")
+    assert want == [("101", 2)]                           # 0.30 + 0.25 beats 0.35 + 0.05 only after merging
+    d = Dist(probs); d.score = Score(full, len(full))     # every candidate returned: merge is complete
+    assert mis.top_strings(d, G, cutoff=1) == want
+    d.score = Score(full[:2], 5)                          # truncated list (0010, 0101): the gap does not cover the
+    assert mis.top_strings(d, G, cutoff=1) == want        # unseen partners -> falls back to the dict path
+    d.score = Score(full[:1], 5)
+    d.P = None                                            # nothing stored: best effort from the fused list
+    assert mis.top_strings(d, G, cutoff=1) == [("010", 1)]
