@@ -55,6 +55,28 @@ int qdc_launch_finish(const double* d_partials, int n_partials, double* d_sums, 
                       double* d_cand_p, const unsigned long long* d_cand_count, long long cand_cap, int k,
                       uint64_t* d_top_x, double* d_top_p, cudaStream_t stream);
 
+// Timeline tracing (diagnostic builds only: make EXTRA=-DQDC_I8_TRACE): CTA 0 records (event, clock64) for a few
+// tiles -- which wait of which warp the tensor pipe's idle time hides behind (scripts/trace_i8.py reads it).
+#ifdef QDC_I8_TRACE
+__device__ unsigned long long g_i8_trace[8][1024];
+__device__ int g_i8_trace_n[8];
+#define QDC_TR(who, tile, cond, code)                                                                   \
+    if (blockIdx.x == 0 && (tile) >= 200u && (tile) < 204u && (cond)) {                                  \
+        const int k_ = g_i8_trace_n[who]++;                                                              \
+        if (k_ < 512) { g_i8_trace[who][2 * k_] = (unsigned long long)(code) | ((unsigned long long)(tile) << 32); g_i8_trace[who][2 * k_ + 1] = clock64(); } \
+    }
+extern "C" int qdc_i8_debug_trace(unsigned long long* h_events, int* h_counts) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(h_events, g_i8_trace, sizeof(g_i8_trace));
+    cudaMemcpyFromSymbol(h_counts, g_i8_trace_n, sizeof(g_i8_trace_n));
+    int zero[8] = {};
+    cudaMemcpyToSymbol(g_i8_trace_n, zero, sizeof(zero));
+    return 0;
+}
+#else
+#define QDC_TR(who, tile, cond, code)
+#endif
+
 namespace {
 
 constexpr int TM = 128;                       // tile rows
@@ -86,7 +108,12 @@ constexpr int E_ZERO = -(1 << 20);            // as in i8_prep.cu
 constexpr int D0_MARGIN = (1 << 15) + (1 << 9);   // |X / 256^(S-1) - D_0| < 2^15.01
 constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = 1, BAR_B_FULL = 2, BAR_B_EMPTY = BAR_B_FULL + 8, BAR_ACC_FULL = BAR_B_EMPTY + 8,
               BAR_ACC_EMPTY = BAR_ACC_FULL + 6, BAR_TA_FULL = BAR_ACC_EMPTY + 6, BAR_TA_FREE = BAR_TA_FULL + 1,
-              N_BARS = BAR_TA_FREE + 1;                                            // (8 = MAX_STAGES, 6 = MAX_S)
+              BAR_CT_FULL = BAR_TA_FREE + 1, BAR_CT_EMPTY = BAR_CT_FULL + 4,
+              N_BARS = BAR_CT_EMPTY + 4;                                           // (8 = MAX_STAGES, 6 = MAX_S, 4 = CT_STAGES)
+// pair form: the column table of a tile (TN entries of 16 bytes + the group exponents) is staged in shared
+// memory by the producer, CT_STAGES tiles ahead (see the epilogue)
+constexpr int CT_STAGES = 4;
+constexpr int ct_stage_bytes(int tn) { return tn * 16 + 16; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 // All barriers live in ONE shared array and are addressed as base + 8 k, the base computed once per
@@ -132,6 +159,36 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// ---- CTA pair (cta_group::2) helpers ------------------------------------------------------------------
+// commit that arrives on the barrier at the same shared-memory offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+// the shared::cluster address of this CTA's shared-memory offset `addr` in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// Waits on barriers that also receive arrivals from the peer CTA use the plain (CTA-scope) try_wait, as
+// the cluster barriers of CUTLASS's 2-SM pipelines do: what the wait guards is read by the tensor core
+// (async proxy) from shared memory that was written before the arrival was sent, never by this thread.
+// A cluster-scope acquire here was measured at ~800 clocks per wait, five of them on the serial chain of
+// the warp that issues the last order (profiles/r2_i8_timeline.md).
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) { mbar_wait(bar, parity); }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
@@ -180,6 +237,20 @@ __device__ __forceinline__ void umma_pair_ss(uint32_t tmem_d, uint64_t a_desc0, 
         " mov.b32 d, %0;\n add.s64 da, %1, %5;\n mov.b64 db, %2;\n"
         " tcgen05.mma.cta_group::1.kind::i8 [d], da, db, %3, p;\n"
         QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP QDC_SS_STEP
+        "}\n"
+        ::"r"(tmem_d), "l"(a_desc0), "l"(b_desc), "r"(idesc), "n"(ACC ? 1 : 0), "n"(A_OFF) : "memory");
+}
+// the same block for a CTA pair: M = 256 (128 rows in each CTA), the streamed tile split between the two
+// CTAs' shared memories (TN / 2 columns each, same offset), issued by the leader CTA only
+#define QDC_SS2_STEP " add.s64 da, da, 16;\n add.s64 db, db, 16;\n tcgen05.mma.cta_group::2.kind::i8 [d], da, db, %3, q;\n"
+template <int A_OFF, bool ACC>
+__device__ __forceinline__ void umma_pair_ss2(uint32_t tmem_d, uint64_t a_desc0, uint64_t b_desc, uint32_t idesc) {
+    asm volatile(
+        "{\n .reg .pred p, q;\n .reg .b32 d;\n .reg .b64 da, db;\n"
+        " setp.ne.b32 p, %4, 0;\n setp.eq.b32 q, %3, %3;\n"
+        " mov.b32 d, %0;\n add.s64 da, %1, %5;\n mov.b64 db, %2;\n"
+        " tcgen05.mma.cta_group::2.kind::i8 [d], da, db, %3, p;\n"
+        QDC_SS2_STEP QDC_SS2_STEP QDC_SS2_STEP QDC_SS2_STEP QDC_SS2_STEP QDC_SS2_STEP QDC_SS2_STEP
         "}\n"
         ::"r"(tmem_d), "l"(a_desc0), "l"(b_desc), "r"(idesc), "n"(ACC ? 1 : 0), "n"(A_OFF) : "memory");
 }
@@ -270,7 +341,8 @@ struct I8Args {
     const double* B_src;
     int kdim_src;
     long long n_rows, n_cols, row_lo;     // row_lo: offset of this slab in the MIS row tables / united index
-    int n_rb, n_cb, kdim, n_stages;
+    int n_rb, n_cb, kdim, n_stages;       // n_rb: work units along the rows (row blocks; pair form: 256-row units)
+    int a_blocks_pad;        // 128-row blocks the prepared row operand holds (pair form: a unit's second half may lie beyond)
     int n_chunks, chunk_len;  // work item = (row block, chunk of chunk_len column blocks); item = chunk * n_rb + rb
     int check_slices;        // 1: run only if res[I8_RES_SLICES] == S (the count was chosen on the device)
     double out_scale;        // scale * 256^-(S-1)
@@ -311,10 +383,20 @@ __device__ __noinline__ void emit_flagged(FlagCtx x, CandSink sink, long long r_
 }
 
 // S = number of slices per operand in use (compile time: every loop over slice pairs and orders unrolls)
-template <int S, int TN, int EPI>
+// PAIR: two CTAs of a cluster form a CTA pair (cta_group::2): the unit of work is 256 rows (128 in each CTA, both
+// resident), every tcgen05.mma is M = 256 issued by the leader CTA (rank 0) for both, and the streamed tile is
+// split -- each CTA loads TN / 2 of its columns and the MMA reads both halves -- so a CTA's shared memory
+// serves 6 KB instead of 8 KB per 64-clock instruction and takes half of the streamed bytes.  Cross-CTA
+// protocol: "full" barriers of the leader count 2 (its own copy's expect_tx + a forwarded arrival from the peer,
+// whose idle issuer warp 0 waits on the peer's own barrier and arrives remotely), "empty" and "accumulator
+// full" barriers are signalled in both CTAs by multicast commits, the leader's "accumulator empty" barriers
+// count the epilogue warps of both CTAs (the peer's arrive remotely).
+template <int S, int TN, int EPI, bool PAIR = false>
 __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32, 1) contract_i8_kernel(const I8Args a) {
     constexpr int CPT = cpt_of(TN), N_EPI_WARPS = 4 * (TN / CPT), NSLOT = slots_of(S, TN);
     static_assert(NSLOT * TN <= TMEM_COLS && S - NSLOT <= 1, "accumulator slots");
+    static_assert(!PAIR || (EPI == 0 && TN % 32 == 0), "the CTA-pair form is the scoring-only kernel");
+    constexpr int TNL = PAIR ? TN / 2 : TN;            // columns of the streamed tile this CTA loads
     static_assert(EPI == 0 || (CPT == 16 && NSLOT == S), "the storing epilogue keeps 16 columns per thread and one slot per order");
     // order d of this CTA's tile number `seq` is accumulation number g = seq S + d: it lives in slot g % NSLOT
     // and is that slot's use number g / NSLOT (the parity of its two barriers)
@@ -334,24 +416,37 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int kdim = a.kdim;
-    const uint32_t a_slice_bytes = TM * kdim, b_slice_bytes = TN * kdim;
+    const uint32_t a_slice_bytes = TM * kdim, b_slice_bytes = TNL * kdim;
+    const uint32_t crank = PAIR ? cluster_rank() : 0u;                        // 0 = leader of the pair
+    const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // first work item of this CTA (pair)
+    const int unit_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     uint32_t sA_addr = smem_u32(smem);                    // [S][a_slice_bytes], then [n_stages][b_slice_bytes]
     asm volatile("" : "+r"(sA_addr));
     const uint32_t sB_addr = sA_addr + (uint32_t)S * a_slice_bytes;
+    const uint32_t sCT_addr = sB_addr + (uint32_t)a.n_stages * b_slice_bytes;   // (pair form) CT_STAGES column-table stages
+    const uint32_t ct_full0 = bar0 + 8u * BAR_CT_FULL, ct_empty0 = bar0 + 8u * BAR_CT_EMPTY;
+    constexpr uint32_t CTB = ct_stage_bytes(TN);
 
     if (tid == 0) {
-        mbar_init(a_full, 1); mbar_init(a_empty, N_ISSUERS);
+        const int full_count = (PAIR && crank == 0) ? 2 : 1;                  // leader: own copy + the peer's forwarded arrival
+        mbar_init(a_full, full_count); mbar_init(a_empty, N_ISSUERS);
         mbar_init(bar0 + 8u * BAR_TA_FULL, 1); mbar_init(bar0 + 8u * BAR_TA_FREE, N_ISSUERS - 1);
-        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(b_full0 + 8u * s, 1); mbar_init(b_empty0 + 8u * s, N_ISSUERS); }
-        for (int d = 0; d < MAX_S; ++d) { mbar_init(acc_full0 + 8u * d, 1); mbar_init(acc_empty0 + 8u * d, N_EPI_WARPS); }
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(b_full0 + 8u * s, full_count); mbar_init(b_empty0 + 8u * s, N_ISSUERS); }
+        for (int d = 0; d < MAX_S; ++d) { mbar_init(acc_full0 + 8u * d, 1); mbar_init(acc_empty0 + 8u * d, (PAIR ? 2 : 1) * N_EPI_WARPS); }
+        for (int c = 0; c < CT_STAGES; ++c) { mbar_init(ct_full0 + 8u * c, 1); mbar_init(ct_empty0 + 8u * c, N_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sh)), "r"(TMEM_COLS));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        if constexpr (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sh)), "r"(TMEM_COLS));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sh)), "r"(TMEM_COLS));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();           // (pair: the peer's barriers are initialised too)
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, tmem_base_sh, 0);     // (lane-0 broadcast: known warp-uniform)
 
@@ -361,26 +456,42 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
     if (warp == 0) {
         // ================= producer =================
         const bool leader = elect_one();
-        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
-            const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
+        int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, p_seq = 0;
+        (void)p_seq;
+        for (int item = unit0; item < n_items; item += unit_step, rb_phase ^= 1u) {
+            const int rb = PAIR ? 2 * (item % a.n_rb) + (int)crank : item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
             const int cb1 = min(a.n_cb, cb0 + a.chunk_len);
             mbar_wait_relaxed(a_empty, rb_phase ^ 1u, 200);
             if (leader) {
-                mbar_expect_tx(a_full, (uint32_t)S * a_slice_bytes);
+                // (pair: the second half of the last unit may lie beyond the padded operand: nothing is loaded,
+                // its MMA rows are garbage that the epilogue never looks at)
+                const bool have = !PAIR || rb < a.a_blocks_pad;
+                mbar_expect_tx(a_full, have ? (uint32_t)S * a_slice_bytes : 0u);
 #pragma unroll
                 for (int i = 0; i < S; ++i)
-                    bulk_g2s(sA_addr + (uint32_t)i * a_slice_bytes,
-                             a.A8 + (size_t)i * a.a_slice_stride + (size_t)rb * a_slice_bytes, a_slice_bytes, a_full);
+                    if (have)
+                        bulk_g2s(sA_addr + (uint32_t)i * a_slice_bytes,
+                                 a.A8 + (size_t)i * a.a_slice_stride + (size_t)rb * a_slice_bytes, a_slice_bytes, a_full);
             }
-            for (int cb = cb0; cb < cb1; ++cb) {
+            for (int cb = cb0; cb < cb1; ++cb, ++p_seq) {
+                if constexpr (PAIR) {
+                    const uint32_t cs = p_seq & (CT_STAGES - 1), cpar = (p_seq / CT_STAGES) & 1u;
+                    mbar_wait_relaxed(ct_empty0 + 8u * cs, cpar ^ 1u, 64);
+                    if (leader) {
+                        mbar_expect_tx(ct_full0 + 8u * cs, CTB);
+                        bulk_g2s(sCT_addr + cs * CTB, a.coltab + (size_t)cb * TN, TN * 16, ct_full0 + 8u * cs);
+                        bulk_g2s(sCT_addr + cs * CTB + TN * 16, a.gref + (size_t)cb * (TN / I8_GROUP), 16, ct_full0 + 8u * cs);
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
                     mbar_wait_relaxed(b_empty0 + 8u * b_stage, b_phase ^ 1u, 64);
+                    QDC_TR(0, p_seq, leader, 0x100 + j);          // stage free, copy of slice j issued now
                     if (leader) {
                         mbar_expect_tx(b_full0 + 8u * b_stage, b_slice_bytes);
                         bulk_g2s(sB_addr + (uint32_t)b_stage * b_slice_bytes,
-                                 a.B8 + (size_t)j * a.b_slice_stride + (size_t)cb * b_slice_bytes, b_slice_bytes, b_full0 + 8u * b_stage);
+                                 a.B8 + (size_t)j * a.b_slice_stride + ((size_t)cb * (PAIR ? 2 : 1) + crank) * b_slice_bytes,
+                                 b_slice_bytes, b_full0 + 8u * b_stage);
                     }
                     if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
                 }
@@ -406,13 +517,68 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
         const uint64_t a_desc0 = desc0 + (sA_addr >> 4), b_desc0 = desc0 + (sB_addr >> 4);
         const uint32_t ta_full = bar0 + 8u * BAR_TA_FULL, ta_free = bar0 + 8u * BAR_TA_FREE;
         int b_stage = 0; uint32_t b_phase = 0, rb_phase = 0, seq = 0;          // seq: tiles this CTA has walked
-        if (ksteps == 8) {
+        if constexpr (PAIR) {
+            // ---- CTA pair, kdim = 256 (the launcher guarantees it) ----
+            constexpr uint32_t A_SLICE16 = TM * 256 / 16, B_SLICE16 = TNL * 256 / 16;
+            if (crank != 0) {
+                // peer CTA: issues nothing.  Its issuer warp 0 forwards "my copy has landed" to the leader's barriers.
+                if (iw == 0) {
+                    const uint32_t r_a_full = mapa(a_full, 0), r_b_full0 = mapa(b_full0, 0);
+                    for (int item = unit0; item < n_items; item += unit_step, rb_phase ^= 1u) {
+                        const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
+                        mbar_wait(a_full, rb_phase);
+                        if (leader) mbar_arrive_remote(r_a_full);
+                        for (int cb = cb0; cb < cb1; ++cb)
+                            for (int j = 0; j < S; ++j) {
+                                mbar_wait(b_full0 + 8u * b_stage, b_phase);
+                                if (leader) mbar_arrive_remote(r_b_full0 + 8u * b_stage);
+                                if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
+                            }
+                    }
+                }
+            } else {
+                const uint32_t idesc2 = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)((2 * TM) >> 4) << 24);
+                for (int item = unit0; item < n_items; item += unit_step, rb_phase ^= 1u) {
+                    const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
+                    mbar_wait_cluster(a_full, rb_phase);
+                    tc_fence_after();
+                    for (int cb = cb0; cb < cb1; ++cb, ++seq) {
+                        static_for<0, S>([&](auto jc) {
+                            constexpr int j = decltype(jc)::value;
+                            mbar_wait_cluster(b_full0 + 8u * b_stage, b_phase);
+                            tc_fence_after();
+                            QDC_TR(1 + iw, seq, leader, 0x200 + j);       // slice j is there
+                            const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * B_SLICE16;
+                            static_for<0, S - j>([&](auto ic) {
+                                constexpr int i = decltype(ic)::value, d = i + j;
+                                if (iw == owner_of(S, d)) {
+                                    const uint32_t slot = slot_of(seq, d);
+                                    if (j == 0) {                      // first touch of order d in this tile: both epilogues are done with the slot
+                                        mbar_wait_cluster(acc_empty0 + 8u * slot, par_of(seq, d) ^ 1u);
+                                        tc_fence_after();
+                                        QDC_TR(1 + iw, seq, leader, 0x300 + d);   // the slot of order d is free
+                                    }
+                                    if (leader) {
+                                        umma_pair_ss2<i * (int)A_SLICE16, (j > 0)>(tmem + slot * TN, a_desc0, b_desc, idesc2);
+                                        QDC_TR(1 + iw, seq, true, 0x400 + i * 16 + j);   // pair (i, j) issued
+                                        if (i == 0) umma_commit_pair(acc_full0 + 8u * slot);
+                                    }
+                                }
+                            });
+                            if (leader) umma_commit_pair(b_empty0 + 8u * b_stage);
+                            if (++b_stage == a.n_stages) { b_stage = 0; b_phase ^= 1u; }
+                        });
+                    }
+                    if (leader) umma_commit_pair(a_empty);
+                }
+            }
+        } else if (ksteps == 8) {
             // ---- kdim = 256: everything but the ring stage is a compile-time constant ----
             // TMEM columns [S TN, 512) hold the first NTA resident slices (64 columns each); their pairs
             // take A from tensor memory and read only the streamed tile from shared memory
             constexpr int NTA = (TMEM_COLS - NSLOT * TN) / 64 < S ? (TMEM_COLS - NSLOT * TN) / 64 : S;
             constexpr uint32_t A_SLICE16 = TM * 256 / 16, B_SLICE16 = TN * 256 / 16;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+            for (int item = unit0; item < n_items; item += unit_step, rb_phase ^= 1u) {
                 const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
                 mbar_wait(a_full, rb_phase);
                 tc_fence_after();
@@ -438,6 +604,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                         constexpr int j = decltype(jc)::value;
                         mbar_wait(b_full0 + 8u * b_stage, b_phase);
                         tc_fence_after();
+                        QDC_TR(1 + iw, seq, leader, 0x200 + j);
                         const uint64_t b_desc = b_desc0 + (uint32_t)b_stage * B_SLICE16;
                         static_for<0, S - j>([&](auto ic) {
                             constexpr int i = decltype(ic)::value, d = i + j;
@@ -446,7 +613,9 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                                 if (j == 0) {                      // first touch of order d in this tile
                                     mbar_wait(acc_empty0 + 8u * slot, par_of(seq, d) ^ 1u);
                                     tc_fence_after();
+                                    QDC_TR(1 + iw, seq, leader, 0x300 + d);
                                 }
+                                QDC_TR(1 + iw, seq, leader, 0x400 + i * 16 + j);
                                 if (leader) {
                                     if constexpr (i < NTA) umma_pair_ts<(j > 0)>(tmem + slot * TN, tmem + (uint32_t)(NSLOT * TN + i * 64), b_desc, idesc);
                                     else umma_pair_ss<i * (int)A_SLICE16, (j > 0)>(tmem + slot * TN, a_desc0, b_desc, idesc);
@@ -469,7 +638,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
             const uint32_t tmem_a0 = tmem + (uint32_t)(NSLOT * TN);
             const int n_ta = min(S, (TMEM_COLS - NSLOT * TN) / (kdim / 4));
             const bool mine = iw == 0;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x, rb_phase ^= 1u) {
+            for (int item = unit0; item < n_items; item += unit_step, rb_phase ^= 1u) {
                 const int cb0 = (item / a.n_rb) * a.chunk_len, cb1 = min(a.n_cb, cb0 + a.chunk_len);
                 mbar_wait(a_full, rb_phase);
                 tc_fence_after();
@@ -519,8 +688,10 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(part * CPT);
         uint32_t tile_phase = 0, seq = 0;
         const double inv_norm = a.use_norm ? 1.0 / a.res[I8_RES_NORM] : 1.0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int rb = item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
+        // (pair: the leader's issuers wait for the epilogues of both CTAs; the peer's release is a remote arrival)
+        const uint32_t acc_empty_rel = (PAIR && crank != 0) ? mapa(acc_empty0, 0) : acc_empty0;
+        for (int item = unit0; item < n_items; item += unit_step) {
+            const int rb = PAIR ? 2 * (item % a.n_rb) + (int)crank : item % a.n_rb, cb0 = (item / a.n_rb) * a.chunk_len;
             const int cb1 = min(a.n_cb, cb0 + a.chunk_len);
             const int r_loc = rb * TM + quarter * 32 + lane;                        // row inside the slab
             const bool row_ok = r_loc < a.n_rows;
@@ -565,16 +736,29 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                     for (int d = 0; d < S; ++d) run[d] = 0;
                     n_run = 0;
                 };
+                int gr_next = __ldg(a.gref + (cb0 * TN + part * CPT) / I8_GROUP);
                 for (int cb = cb0; cb < cb1; ++cb, ++seq) {
                     const int c0 = cb * TN + part * CPT;
+                    QDC_TR(4 + (ew == 0 ? 0 : 1), seq, lane == 0 && (ew == 0 || ew == N_EPI_WARPS - 1), 0x700);   // tile begins (previous one finished)
                     // the next tile's column-table lines (CPT x 16 bytes) and group exponent go to L1 now: the
                     // table is walked once per row block, so every tile would otherwise start with a chain of
                     // L2 round trips before its first order can be drained
-                    if (cb + 1 < cb1) {
-                        if (lane < CPT / 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.coltab + c0 + TN + lane * 8));
-                        else if (lane == CPT / 8) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.gref + (c0 + TN) / I8_GROUP));
+                    // (the group exponent is fetched one tile ahead: a load whose result is needed at once costs an
+                    // L2 round trip per tile on the warp's serial chain -- 1.8 % of all stall samples, r2_i8_timeline.md)
+                    int gr;
+                    uint32_t ct_base = 0;
+                    if constexpr (PAIR) {
+                        // pair form: this tile's column table was staged in shared memory by the producer (the L1 that
+                        // 224 KB of shared memory leave cannot hold it next to the spill stack: every tile began with
+                        // L2 round trips on the serial chain of all 16 epilogue warps)
+                        const uint32_t cs = seq & (CT_STAGES - 1);
+                        mbar_wait(ct_full0 + 8u * cs, (seq / CT_STAGES) & 1u);
+                        ct_base = sCT_addr + cs * CTB;
+                        asm volatile("ld.shared.s32 %0, [%1];" : "=r"(gr) : "r"(ct_base + TN * 16 + (uint32_t)(part * CPT / I8_GROUP) * 4u));
+                    } else {
+                        gr = gr_next;
+                        if (cb + 1 < cb1) gr_next = __ldg(a.gref + (c0 + TN) / I8_GROUP);
                     }
-                    const int gr = __ldg(a.gref + c0 / I8_GROUP);
                     if (gr != cur_gr || n_run == 256 / CPT) { flush(); cur_gr = gr; } // warp-uniform
                     ++n_run;
                     int tcmp;                               // an output may be a candidate when D_0 >= tcmp
@@ -586,16 +770,27 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                     int m[CPT];                             // [independent] (w_r + w_c) << lsh_c
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) {
-                        const uint4 ct = __ldg(a.coltab + c0 + c);      // (x_lo, x_hi | flags, w_c << lsh_c, 1 << lsh_c)
+                        uint4 ct;                                       // (x_lo, x_hi | flags, w_c << lsh_c, 1 << lsh_c)
+                        if constexpr (PAIR)
+                            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ct.x), "=r"(ct.y), "=r"(ct.z), "=r"(ct.w)
+                                         : "r"(ct_base + (uint32_t)(part * CPT + c) * 16u));
+                        else
+                            ct = __ldg(a.coltab + c0 + c);
                         const bool ok = ((ct.x & (uint32_t)rf) | (ct.y & (uint32_t)(rf >> 32))) == 0u;
                         m[c] = ok ? w_r * (int)ct.w + (int)ct.z : 0;
                     }
+                    if constexpr (PAIR) {                               // the stage may be refilled
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(ct_empty0 + 8u * (seq & (CT_STAGES - 1)));
+                    }
                     uint32_t flags = 0;
+                    QDC_TR(4 + (ew == 0 ? 0 : 1), seq, lane == 0 && (ew == 0 || ew == N_EPI_WARPS - 1), 0x701 + (m[0] & 0));   // column factors ready
 #pragma unroll
                     for (int d = 0; d < S; ++d) {
                         const uint32_t slot = slot_of(seq, d);
                         mbar_wait_relaxed(acc_full0 + 8u * slot, par_of(seq, d), 32);
                         tc_fence_after();
+                        QDC_TR(4 + (ew == 0 ? 0 : 1), seq, lane == 0 && (ew == 0 || ew == N_EPI_WARPS - 1), 0x500 + d);   // order d seen complete
                         long long r = run[d];
 #pragma unroll
                         for (int h = 0; h < CPT / 16; ++h) {            // 16 columns at a time (registers)
@@ -605,7 +800,11 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                             if (h == CPT / 16 - 1) {                    // everything of this order is in registers: release the slot
                                 tc_fence_before();
                                 __syncwarp();
-                                if (lane == 0) mbar_arrive(acc_empty0 + 8u * slot);
+                                if (lane == 0) {
+                                    if (PAIR && crank != 0) mbar_arrive_remote(acc_empty_rel + 8u * slot);
+                                    else mbar_arrive(acc_empty0 + 8u * slot);
+                                }
+                                QDC_TR(4 + (ew == 0 ? 0 : 1), seq, lane == 0 && (ew == 0 || ew == N_EPI_WARPS - 1), 0x600 + d);   // slot released
                             }
 #pragma unroll
                             for (int c = 0; c < 16; ++c) r += (long long)(int32_t)v[c] * (long long)m[h * 16 + c];
@@ -621,6 +820,11 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                             }
                         }
                         run[d] = r;
+                        // the next tile's column-table lines (CPT x 16 bytes) go to L1 while the last orders are still
+                        // running: issued a whole tile ahead they were evicted again before use (L1 is what the 224 KB
+                        // of shared memory leave)
+                        if (!PAIR && d == (S > 2 ? S - 3 : 0) && cb + 1 < cb1 && lane < CPT / 8)
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.coltab + c0 + TN + lane * 8));
                     }
                     if (flags && row_ok) {
                         const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src};
@@ -713,8 +917,13 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
     }
     // teardown
     tc_fence_before();
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+    if constexpr (PAIR) {
+        cluster_sync_all();                               // neither CTA's shared / tensor memory is touched by the other any more
+        if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+    } else {
+        __syncthreads();
+        if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+    }
     MisAccum macc = {0.0, cta_pwok, 0.0};
     mis_block_store(macc, scratch, a.partials);
 }
@@ -724,6 +933,24 @@ int launch_i8(const I8Args& a, int grid, size_t smem, cudaStream_t s) {
     QDC_CHECK_CUDA(cudaFuncSetAttribute(contract_i8_kernel<S, TN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     contract_i8_kernel<S, TN, EPI><<<grid, (FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32, smem, s>>>(a);
     QDC_CHECK_LAUNCH();
+    return QDC_OK;
+}
+
+// CTA-pair launch: clusters of 2 (the pair shares a TPC), grid even
+template <int S, int TN>
+int launch_i8_pair(const I8Args& a, int grid, size_t smem, cudaStream_t s) {
+    auto kern = contract_i8_kernel<S, TN, 0, true>;
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    QDC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
     return QDC_OK;
 }
 
@@ -750,17 +977,24 @@ int i8_tile_n(int n_slices, int kd, int store) {
 int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
     const int kd = a.kdim;
     const int TN = i8_tile_n(n_slices, kd, store);
-    const long long n_rb = (a.n_rows + TM - 1) / TM, n_cb = (a.n_cols + TN - 1) / TN;
+    // CTA pairs (cta_group::2): the scoring-only kernel at 128 columns and kdim 256, at least two 256-row units
+    bool pair = !store && TN == 128 && kd == 256 && n_slices >= 3 && n_slices <= 5 && a.n_rows > 2 * TM;
+    if (const char* m = getenv("QDC_I8_PAIR")) pair = pair && atoi(m) != 0;
+    const long long n_blocks = (a.n_rows + TM - 1) / TM;
+    const long long n_rb = pair ? (n_blocks + 1) / 2 : n_blocks, n_cb = (a.n_cols + TN - 1) / TN;
     QDC_REQUIRE(n_rb < (1ll << 31) && n_cb < (1ll << 31), "too many tiles");
     a.n_rb = (int)n_rb; a.n_cb = (int)n_cb;
-    const size_t smem_max = 227 * 1024 - 2048, a_res = (size_t)n_slices * TM * kd, b_slice = (size_t)TN * kd;
+    a.a_blocks_pad = (int)((n_blocks * TM + I8_ROW_ALIGN - 1) / I8_ROW_ALIGN * I8_ROW_ALIGN / TM);
+    const size_t smem_max = 227 * 1024 - 2048, a_res = (size_t)n_slices * TM * kd, b_slice = (size_t)(pair ? TN / 2 : TN) * kd;
     QDC_REQUIRE(a_res + 2 * b_slice <= smem_max, "shared memory");
-    size_t n_stages = (smem_max - a_res) / b_slice;
+    const size_t ct_bytes = pair ? (size_t)CT_STAGES * ct_stage_bytes(TN) : 0;
+    size_t n_stages = (smem_max - a_res - ct_bytes) / b_slice;
     if (n_stages > MAX_STAGES) n_stages = MAX_STAGES;
+    QDC_REQUIRE(n_stages >= 2, "shared memory");
     { const char* m = getenv("QDC_I8_STAGES"); if (m && atoi(m) >= 2 && (size_t)atoi(m) < n_stages) n_stages = atoi(m); }
     a.n_stages = (int)n_stages;
-    const size_t smem = a_res + n_stages * b_slice;
-    const int sms = qdc_sm_count();
+    const size_t smem = a_res + n_stages * b_slice + ct_bytes;
+    const int sms = pair ? qdc_sm_count() / 2 : qdc_sm_count();          // schedulable units: SMs, or SM pairs
     // Work items = row blocks x column chunks, dealt round-robin to one CTA per SM.  Splitting the
     // column walk costs one more load of the resident slices per item, so chunks stay >= 64 tiles;
     // among 1, 2, 4, ... chunks take the split that wastes the least of the last wave.
@@ -778,7 +1012,14 @@ int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
     a.out_scale = ldexp(a.out_scale, -8 * (n_slices - 1));   // the row / column factors carry 2^(e - 7)
     const long long n_items = n_rb * n_chunks;
     QDC_REQUIRE(n_items < (1ll << 31), "too many work items");
-    const int grid = (int)(n_items < sms ? n_items : sms);
+    const int grid = (int)(n_items < sms ? n_items : sms) * (pair ? 2 : 1);
+    if (pair) {
+        switch (n_slices) {
+            case 3: return launch_i8_pair<3, 128>(a, grid, smem, s);
+            case 4: return launch_i8_pair<4, 128>(a, grid, smem, s);
+            case 5: return launch_i8_pair<5, 128>(a, grid, smem, s);
+        }
+    }
 #define QDC_I8_CASE(SS, TT)                                                                         \
     if (n_slices == SS && TN == TT)                                                                 \
         return store ? launch_i8<SS, TT, 1>(a, grid, smem, s) : launch_i8<SS, TT, 0>(a, grid, smem, s);
