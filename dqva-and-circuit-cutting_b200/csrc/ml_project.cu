@@ -47,6 +47,7 @@ struct MlState {                             // head of the workspace (256 bytes
     unsigned int counter;                    // CTAs finished in the current threshold launch
     int newton_steps;
     double t, total, abs_total;
+    int conj_not_diag;                       // set when Lambda -> conj(Lambda) is NOT a sign flip of tensor components
 };
 
 struct MlTables {
@@ -88,16 +89,94 @@ __device__ __forceinline__ void build_lambda(const double* __restrict__ Trow, co
     __syncwarp();
 }
 
+// ---- the change-of-basis tables in shared memory -------------------------------------------------
+// The host tables are generic (index, complex coefficient) lists, 160 KB at D = 16: far more than the
+// L1 that the per-warp blocks leave, so every lookup of every block went to L2 (412 GB of L2 -> SM
+// traffic for the 2^19 blocks of a C4 fragment: 45 ms for what is arithmetically a 3 ms job).  For a
+// Pauli basis every coefficient is s * {1, -1, i, -i, 0} with one magnitude s, so an entry packs
+// into 4 bytes (index, re sign, im sign): 16 KB per table, built once per CTA (components within 1e-12
+// of +-s count as +-s: a relative change of the result below 1e-12).  Tables that do not have that
+// form keep the global-memory path.
+struct PackedTab { const uchar4* e; double s; bool ok; };
+
+template <int D>
+__device__ PackedTab pack_table(const int* __restrict__ idx, const double2* __restrict__ coef, bool inverse,
+                                uchar4* dst, unsigned long long* s_max, int* s_bad) {
+    constexpr int N = D * D * D;
+    __syncthreads();                                   // (a previous call's result has been read by everyone)
+    if (threadIdx.x == 0) { *s_max = 0ull; *s_bad = 0; }
+    __syncthreads();
+    double m = 0.0;
+    for (int e = threadIdx.x; e < N; e += blockDim.x) {
+        const double2 c = __ldg(coef + e);
+        m = fmax(m, fmax(fabs(c.x), fabs(c.y)));
+    }
+    atomicMax(s_max, (unsigned long long)__double_as_longlong(m));     // non-negative doubles order like integers
+    __syncthreads();
+    const double sc = __longlong_as_double((long long)*s_max);
+    bool bad = false;
+    for (int e = threadIdx.x; e < N; e += blockDim.x) {
+        const double2 c = __ldg(coef + e);
+        const int k = __ldg(idx + e);
+        // (the host basis is built from normalised factors: components are +-s up to a few ulp)
+        const double tol = 1e-12 * sc;
+        const int re = fabs(fabs(c.x) - sc) <= tol ? (c.x > 0.0 ? 1 : -1) : 0, im = fabs(fabs(c.y) - sc) <= tol ? (c.y > 0.0 ? 1 : -1) : 0;
+        if ((re == 0 && fabs(c.x) > tol) || (im == 0 && fabs(c.y) > tol)) bad = true;
+#ifdef QDC_ML_DEBUG
+        if (bad && blockIdx.x == 0) printf("bad entry e=%d k=%d c=(%.17g, %.17g) sc=%.17g\n", e, k, c.x, c.y, sc);
+#endif
+        int code = k;
+        if (inverse) { code = ((k >> 8) << 4) | (k & 0xff); if ((k >> 8) >= 16 || (k & 0xff) >= 16) bad = true; }
+        else if (k < 0 || k > 255) bad = true;
+        // stored [t][entry]: the 32 lanes of a warp work on 32 consecutive entries at the same t, so the table
+        // reads are conflict-free ([entry][t] put them 16 words apart: a 16-way bank conflict on every read)
+        dst[(e % D) * (D * D) + e / D] = make_uchar4((unsigned char)code, (unsigned char)(signed char)re, (unsigned char)(signed char)im, 0);
+    }
+    if (bad) atomicOr(s_bad, 1);
+    __syncthreads();
+#ifdef QDC_ML_DEBUG
+    if (blockIdx.x == 0 && threadIdx.x == 0) printf("pack_table D=%d inverse=%d scale=%g bad=%d first=(%d; %g, %g)\n", D, (int)inverse, sc, *s_bad, idx[0], coef[0].x, coef[0].y);
+#endif
+    PackedTab t = {dst, sc, *s_bad == 0};
+    return t;
+}
+
+__device__ __forceinline__ double signed_pick(int sgn, double x) { return sgn > 0 ? x : (sgn < 0 ? -x : 0.0); }
+
+// build_lambda from the packed table
+template <int D>
+__device__ __forceinline__ void build_lambda_packed(const double* __restrict__ Trow, const PackedTab& tab, double* sT, double2* sA, int lane) {
+    for (int e = lane; e < D * D; e += 32) sT[e] = Trow[e];
+    __syncwarp();
+    for (int e = lane; e < D * D; e += 32) {
+        double ax = 0.0, ay = 0.0;
+#pragma unroll 4
+        for (int t = 0; t < D; ++t) {
+            const uchar4 q = tab.e[t * D * D + e];
+            const double x = sT[q.x];
+            ax += signed_pick((signed char)q.y, x);
+            ay += signed_pick((signed char)q.z, x);
+        }
+        sA[e] = make_double2(ax * tab.s, ay * tab.s);
+    }
+    __syncwarp();
+}
+
 template <int D>
 __global__ void __launch_bounds__(ML_WARPS * 32) ml_psd_kernel(const double* __restrict__ T, long long n_blocks, long long ld,
                                                                MlTables tab, MlState* st) {
     __shared__ double sT[ML_WARPS][D * D];
     __shared__ double2 sA[ML_WARPS][D * D];
+    __shared__ uchar4 sFwd[D * D * D];
+    __shared__ unsigned long long s_max;
+    __shared__ int s_bad;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const PackedTab fwd = pack_table<D>(tab.fwd_k, tab.fwd_c, false, sFwd, &s_max, &s_bad);
     bool bad = false;
     for (long long b = (long long)blockIdx.x * ML_WARPS + warp; b < n_blocks; b += (long long)gridDim.x * ML_WARPS) {
         double2* A = sA[warp];
-        build_lambda<D>(T + b * ld, tab, sT[warp], A, lane);
+        if (fwd.ok) build_lambda_packed<D>(T + b * ld, fwd, sT[warp], A, lane);
+        else build_lambda<D>(T + b * ld, tab, sT[warp], A, lane);
         double tr = 0.0;
         for (int i = 0; i < D; ++i) tr += A[i * D + i].x;
         const double eps = 1e-14 * fabs(tr) + 1e-300;
@@ -113,7 +192,10 @@ __global__ void __launch_bounds__(ML_WARPS * 32) ml_psd_kernel(const double* __r
             for (int e = lane; e < D * D; e += 32) {
                 const int i = e / D, j = e % D;
                 if (i > k && j > k) {
-                    const double2 u = cmulc(A[i * D + k], A[j * D + k]);
+                    // A[i][k] conj(A[j][k]) read from ROW k (the trailing block stays Hermitian: both triangles are
+                    // updated): A[k][j] conj(A[k][i]).  Column reads A[j * D + k] put the 16 values of j 256 bytes
+                    // apart -- a 16-way bank conflict that made this kernel 16.7 ms for 2^19 blocks.
+                    const double2 u = cmulc(A[k * D + j], A[k * D + i]);
                     A[e].x -= u.x * inv;
                     A[e].y -= u.y * inv;
                 }
@@ -258,31 +340,54 @@ template <int D>
 __global__ void __launch_bounds__(ML_WARPS * 32) ml_rebuild_kernel(const double* __restrict__ T, long long n_blocks, long long ld,
                                                                    MlTables tab, const MlState* st,
                                                                    const double* __restrict__ evals, const double2* __restrict__ vecs,
-                                                                   double* __restrict__ T_out, long long ld_out) {
-    __shared__ double sT[ML_WARPS][D * D];
-    __shared__ double2 sA[ML_WARPS][D * D];
-    __shared__ double2 sV[ML_WARPS][D * D];
-    __shared__ double sW[ML_WARPS][D];
+                                                                   const double* __restrict__ sgn, double* __restrict__ T_out, long long ld_out) {
+    // dynamic shared memory (rebuild_smem_bytes<D>()): [inverse table][L per warp][V per warp][T per warp][w per warp];
+    // on the exact-data path V is not needed and its space holds the packed forward table
+    extern __shared__ __align__(16) unsigned char ml_dyn[];
+    constexpr int TABB = (D * D * D * 4 + 15) / 16 * 16;
+    uchar4* sInv = reinterpret_cast<uchar4*>(ml_dyn);
+    double2* sA_all = reinterpret_cast<double2*>(ml_dyn + TABB);
+    double2* sV_all = sA_all + ML_WARPS * D * D;
+    double* sT_all = reinterpret_cast<double*>(sV_all + ML_WARPS * D * D);
+    double* sW_all = sT_all + ML_WARPS * D * D;
+    __shared__ unsigned long long s_max;
+    __shared__ int s_bad;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool full = st->need_full != 0;
     const double t0 = st->t;
+    if (!full && !st->conj_not_diag) {
+        // exact data, Pauli basis: the model is the conjugate, i.e. a sign per tensor component (ml_conj_map_kernel)
+        const long long total = n_blocks * (D * D);
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+            const long long b = i / (D * D);
+            const int e = (int)(i - b * (D * D));
+            T_out[b * ld_out + e] = sgn[e] * T[b * ld + e];
+        }
+        return;
+    }
+    const PackedTab inv = pack_table<D>(tab.inv_ij, tab.inv_c, true, sInv, &s_max, &s_bad);
+    PackedTab fwd = {nullptr, 0.0, false};
+    if (!full) fwd = pack_table<D>(tab.fwd_k, tab.fwd_c, false, reinterpret_cast<uchar4*>(sV_all), &s_max, &s_bad);   // (uniform branch)
+    double* sTw = sT_all + warp * D * D;
+    double* sWw = sW_all + warp * D;
     for (long long b = (long long)blockIdx.x * ML_WARPS + warp; b < n_blocks; b += (long long)gridDim.x * ML_WARPS) {
-        double2* L = sA[warp];
+        double2* L = sA_all + warp * D * D;
         if (!full) {
-            build_lambda<D>(T + b * ld, tab, sT[warp], L, lane);
+            if (fwd.ok) build_lambda_packed<D>(T + b * ld, fwd, sTw, L, lane);
+            else build_lambda<D>(T + b * ld, tab, sTw, L, lane);
             for (int e = lane; e < D * D; e += 32) L[e].y = -L[e].y;           // to_projector conjugates (:45-46)
         } else {
-            double2* V = sV[warp];
+            double2* V = sV_all + warp * D * D;
             for (int e = lane; e < D * D; e += 32) V[e] = vecs[b * D * D + e];
-            for (int k = lane; k < D; k += 32) sW[warp][k] = fmax(evals[b * D + k] - t0, 0.0);
+            for (int k = lane; k < D; k += 32) sWw[k] = fmax(evals[b * D + k] - t0, 0.0);
             __syncwarp();
             for (int e = lane; e < D * D; e += 32) {
                 const int i = e / D, j = e % D;
                 double2 acc = make_double2(0.0, 0.0);
                 for (int k = 0; k < D; ++k) {
                     const double2 u = cmulc(V[i * D + k], V[j * D + k]);
-                    acc.x = fma(sW[warp][k], u.x, acc.x);
-                    acc.y = fma(sW[warp][k], u.y, acc.y);
+                    acc.x = fma(sWw[k], u.x, acc.x);
+                    acc.y = fma(sWw[k], u.y, acc.y);
                 }
                 L[e] = make_double2(acc.x, -acc.y);                         // conj(V diag V^+)
             }
@@ -290,12 +395,22 @@ __global__ void __launch_bounds__(ML_WARPS * 32) ml_rebuild_kernel(const double*
         __syncwarp();
         for (int kap = lane; kap < D * D; kap += 32) {
             double acc = 0.0;
+            if (inv.ok) {
 #pragma unroll 4
-            for (int t = 0; t < D; ++t) {
-                const int ij = __ldg(tab.inv_ij + kap * D + t);
-                const double2 c = __ldg(tab.inv_c + kap * D + t);
-                const double2 l = L[(ij & 0xff) * D + (ij >> 8)];           // L'[j][i]
-                acc += c.x * l.x - c.y * l.y;
+                for (int t = 0; t < D; ++t) {
+                    const uchar4 q = inv.e[t * D * D + kap];                    // (i << 4 | j, re sign, im sign)
+                    const double2 l = L[(q.x & 15) * D + (q.x >> 4)];           // L'[j][i]
+                    acc += signed_pick((signed char)q.y, l.x) - signed_pick((signed char)q.z, l.y);
+                }
+                acc *= inv.s;
+            } else {
+#pragma unroll 4
+                for (int t = 0; t < D; ++t) {
+                    const int ij = __ldg(tab.inv_ij + kap * D + t);
+                    const double2 c = __ldg(tab.inv_c + kap * D + t);
+                    const double2 l = L[(ij & 0xff) * D + (ij >> 8)];           // L'[j][i]
+                    acc += c.x * l.x - c.y * l.y;
+                }
             }
             T_out[b * ld_out + kap] = acc;
         }
@@ -305,7 +420,35 @@ __global__ void __launch_bounds__(ML_WARPS * 32) ml_rebuild_kernel(const double*
 
 __global__ void ml_init_kernel(MlState* st, int force_full) {
     st->need_full = force_full ? 1 : 0; st->done = 0; st->counter = 0u; st->newton_steps = 0;
-    st->t = 0.0; st->total = 0.0; st->abs_total = 0.0;
+    st->t = 0.0; st->total = 0.0; st->abs_total = 0.0; st->conj_not_diag = 0;
+}
+
+// What the exact-data path does to a tensor row is the fixed linear map  T -> inv(conj(fwd(T))).  For a
+// basis of Hermitian Pauli products conj(P) = +-P (minus for an odd number of Y), so the map is a sign
+// per component and the "rebuild" of 2^19 blocks is one streaming pass.  This kernel applies the map to
+// the unit vector of component kappa = blockIdx.x through the caller's tables, stores the diagonal
+// entry in sgn[kappa] and raises conj_not_diag if anything else is non-zero or the entry is not +-1
+// (then the table path runs).  D^2 CTAs of D^2 threads, microseconds.
+template <int D>
+__global__ void __launch_bounds__(D * D) ml_conj_map_kernel(MlTables tab, MlState* st, double* __restrict__ sgn) {
+    __shared__ double2 L[D * D];
+    const int kappa = blockIdx.x, e = threadIdx.x;
+    double2 acc = make_double2(0.0, 0.0);
+    for (int t = 0; t < D; ++t)
+        if (tab.fwd_k[e * D + t] == kappa) { const double2 c = tab.fwd_c[e * D + t]; acc.x += c.x; acc.y += c.y; }
+    L[e] = make_double2(acc.x, -acc.y);                                   // conj(Lambda(e_kappa))
+    __syncthreads();
+    double out = 0.0;
+    for (int t = 0; t < D; ++t) {
+        const int ij = tab.inv_ij[e * D + t];
+        const double2 c = tab.inv_c[e * D + t];
+        const double2 l = L[(ij & 0xff) * D + (ij >> 8)];
+        out += c.x * l.x - c.y * l.y;
+    }
+    if (e == kappa) {
+        sgn[kappa] = out;
+        if (fabs(fabs(out) - 1.0) > 1e-12) atomicOr(&st->conj_not_diag, 1);
+    } else if (fabs(out) > 1e-12) atomicOr(&st->conj_not_diag, 1);
 }
 
 template <int D>
@@ -319,7 +462,13 @@ int ml_run(const double* T, long long n, long long ld, MlTables tab, double* T_o
     const int grid = (int)(want < 148ll * 16 ? want : 148ll * 16);
     ml_init_kernel<<<1, 1, 0, s>>>(st, force_full);
     QDC_CHECK_LAUNCH();
-    if (!force_full) { ml_psd_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st); QDC_CHECK_LAUNCH(); }
+    if (!force_full) {
+        // (sgn lives in the Newton partials: they are only touched when the full path runs, the signs only when it does not)
+        ml_conj_map_kernel<D><<<D * D, D * D, 0, s>>>(tab, st, partials);
+        QDC_CHECK_LAUNCH();
+        ml_psd_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st);
+        QDC_CHECK_LAUNCH();
+    }
     ml_jacobi_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st, evals, vecs);
     QDC_CHECK_LAUNCH();
     const long long nv = n * D, tw = (nv + THR_THREADS * 8 - 1) / (THR_THREADS * 8);
@@ -328,7 +477,9 @@ int ml_run(const double* T, long long n, long long ld, MlTables tab, double* T_o
         ml_threshold_kernel<<<tgrid, THR_THREADS, 0, s>>>(evals, nv, st, partials);
         QDC_CHECK_LAUNCH();
     }
-    ml_rebuild_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st, evals, vecs, T_out, ld_out);
+    constexpr size_t rebuild_smem = (size_t)((D * D * D * 4 + 15) / 16 * 16) + (size_t)ML_WARPS * D * D * (16 + 16 + 8) + (size_t)ML_WARPS * D * 8;
+    QDC_CHECK_CUDA(cudaFuncSetAttribute(ml_rebuild_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rebuild_smem));
+    ml_rebuild_kernel<D><<<grid, ML_WARPS * 32, rebuild_smem, s>>>(T, n, ld, tab, st, evals, vecs, partials, T_out, ld_out);
     QDC_CHECK_LAUNCH();
     return QDC_OK;
 }

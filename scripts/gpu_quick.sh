@@ -1,3 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python scripts/time_c4_circuit.py 2>&1 | tail -8 | tee gpurun_out/c4_circuit_stages.log
+timeout 900 python -m pytest tests/test_gpu_qsplit.py -x -q -m gpu 2>&1 | tail -3
+timeout 600 python scripts/time_c4_circuit.py > gpurun_out/c4_stages_plain.log 2>&1; tail -7 gpurun_out/c4_stages_plain.log
