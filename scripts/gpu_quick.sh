@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_cutqc_pipeline.py tests/test_gpu_cutqc_stages.py -x -q -m gpu 2>&1 | tail -3
-timeout 600 python scripts/time_cutqc.py 2>&1 | tee gpurun_out/time_cutqc.log | head -12
+timeout 300 python scripts/probe_marginal.py 2>&1 | tail -2
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:marginal_kernel -o gpurun_out/r2_marginal python scripts/probe_marginal.py > gpurun_out/ncu_marg.log 2>&1; echo rc=$?
