@@ -301,15 +301,17 @@ def variant_sims_leg(torch, dev, cpu=True):
         out[name] = {"n_qubits": n, "prep": len(prep), "meas": len(meas), "states": n_init,
                      "ref_variants": ref, "ms": t * 1e3, "groups": prog.n_groups, "ops": prog.n_ops}
         total_t += t; total_ref += ref; total_states += n_init
-        group_bytes += prog.n_groups * 32.0 * (1 << n) * n_init
+        # compulsory bytes: the gate groups (first writes 16 B / amplitude, later ones read + write) and the
+        # tensor kernel (reads every amplitude once, writes T: 8 B x 2^outputs x 4^cuts -- the larger part)
+        group_bytes += (2 * prog.n_groups - 1) * 16.0 * (1 << n) * n_init + 16.0 * (1 << n) * n_init + 8.0 * T.numel()
     hbm = measured_peaks().get("hbm_gbs") or 6650.0
     out.update({"value": total_states / total_t, "unit": "statevectors/s",
                 "ref_equivalent_variants_per_s": total_ref / total_t, "ms_total": total_t * 1e3,
                 "roofline": {"bound": "hbm", "achieved": group_bytes / total_t / 1e9, "peak": hbm, "unit": "GB/s",
                              "frac": group_bytes / total_t / 1e9 / hbm,
-                             "note": "32 B per amplitude per gate group (read + write of a complex128); states of "
-                                     "2-34 MB each live in the 126 MB L2, so this is L2-resident traffic set against "
-                                     "the HBM copy figure"},
+                             "note": "gate groups (16 B written by the first, 32 B per amplitude by each later one) + the "
+                                     "fragment-tensor kernel (16 B per amplitude read, 268 MB of T written per fragment: "
+                                     "the dominant term); the states themselves (2-34 MB) live in the 126 MB L2"},
                 "note": "value counts the statevectors actually evolved (2^4 + 1 per evaluation); "
                         "ref_equivalent counts the 4^4 + 3^4 = 337 circuits the reference would run for the same "
                         "tensors (qsplit_mlrecon_methods.py:689-691). Launches: sv_matrix + sv_group x groups + "

@@ -699,9 +699,9 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
     extern __shared__ double2 sh_raw[];
     double2* amp = sh_raw;                                         // [bb][N_MU]
     double2* C = sh_raw + (size_t)a.bb * N_MU;                     // [bb][N_HI][PITCH]
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, nthr = blockDim.x;
     const long long set = blockIdx.y, b0 = (long long)blockIdx.x * a.bb;
-    for (int idx = tid; idx < a.bb * N_MU; idx += 256) {
+    for (int idx = tid; idx < a.bb * N_MU; idx += nthr) {
         const int bl = idx % a.bb, mu = idx / a.bb;
         const long long b = b0 + bl;
         double2 v = make_double2(0.0, 0.0);
@@ -724,7 +724,7 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
     // axis j (most significant digit first) <-> measured qubit j <-> bit j of mu.
     // high axes = 0 .. M_HI-1, low axes = M_HI .. M-1.
     if (M_HI == 0) {
-        for (int idx = tid; idx < a.bb; idx += 256) {
+        for (int idx = tid; idx < a.bb; idx += nthr) {
             const double2* am = amp + idx * N_MU;
             double2 v[N_LO];
 #pragma unroll
@@ -758,7 +758,7 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
         return;
     }
     // pass 1: item = (bl, hi digits); products over the low axes, low butterflies
-    for (int idx = tid; idx < a.bb * N_HI; idx += 256) {
+    for (int idx = tid; idx < a.bb * N_HI; idx += nthr) {
         const int h = idx % N_HI, bl = idx / N_HI;
         int row_h = 0, col_h = 0;
 #pragma unroll
@@ -788,7 +788,7 @@ __global__ void __launch_bounds__(256) sv_meas_tensor_kernel(const TensorArgs a)
     }
     __syncthreads();
     // pass 2: item = (bl, lo digits); high butterflies, real parts to T
-    for (int idx = tid; idx < a.bb * N_LO; idx += 256) {
+    for (int idx = tid; idx < a.bb * N_LO; idx += nthr) {
         const int e = idx % N_LO, bl = idx / N_LO;
         const double2* src = C + (size_t)bl * N_LO * (N_HI + 1) + e * (N_HI + 1);
         double2 v[N_HI];
@@ -1243,9 +1243,14 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
         const int n_ax = basis ? n_prep + n_meas : n_meas;        // amplitude-index axes
         const int m_lo = n_ax < 2 ? n_ax : 2, m_hi = n_ax - m_lo;
         const int n_lo = 1 << (2 * m_lo), n_hi = 1 << (2 * m_hi);
-        int bb = n_ax <= 2 ? 256 : (n_ax == 3 ? 64 : 16);
+        // b values per CTA.  With 4 axes the exchange buffer is 4.3 KB per b: 8 of them and 128 threads put six
+        // CTAs on an SM instead of three, in different phases (gather / products / exchange / stores)
+        int bb = n_ax <= 2 ? 256 : (n_ax == 3 ? 64 : 8);
+        if (const char* env = getenv("QDC_SV_TENSOR_BB")) { const int v = atoi(env); if (v >= 1 && v <= 256) bb = v; }
         if (bb > a.n_b) bb = (int)a.n_b;
         a.bb = bb;
+        int mt_threads = bb * (m_hi ? (n_hi > n_lo ? n_hi : n_lo) : 1);
+        mt_threads = mt_threads < 64 ? 64 : (mt_threads > 256 ? 256 : (mt_threads + 31) / 32 * 32);
         const size_t smem = (size_t)bb * ((size_t)(1 << n_ax) + (m_hi ? (size_t)n_lo * (n_hi + 1) : 0)) * 16;
         const long long gx = (a.n_b + bb - 1) / bb;
         QDC_REQUIRE(gx < (1ll << 31) && n_sets <= 65535, "grid");
@@ -1256,7 +1261,7 @@ extern "C" int qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_
         {                                                                                                   \
             QDC_CHECK_CUDA(cudaFuncSetAttribute(sv_meas_tensor_kernel<HI, LO>,                              \
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
-            sv_meas_tensor_kernel<HI, LO><<<grid, 256, smem, st>>>(a);                                      \
+            sv_meas_tensor_kernel<HI, LO><<<grid, mt_threads, smem, st>>>(a);                               \
         }
         if (n_meas_axes == 1) QDC_MEAS_CASE(0, 1)
         else if (n_meas_axes == 2) QDC_MEAS_CASE(0, 2)
