@@ -625,7 +625,8 @@ def run_b200(args):
         dtype = f"i8 x {n_sl} slices (Ozaki split of FP64 operands, int32 accumulation, integer fold)"
         # i8_prep x2, [colsum of the other ranks' rows], i8_plan, contract_i8 (x4 with slices = auto:
         # the three counts the plan kernel did not choose return at once), finish (sums + top-k)
-        launches = (5 + (3 if args.slices == "auto" else 0) + (1 if ws > 1 else 0)) * args.steps
+        # ... and i8_reeval (exact re-evaluation of the outputs the integer filter flagged)
+        launches = (6 + (3 if args.slices == "auto" else 0) + (1 if ws > 1 else 0)) * args.steps
     else:
         achieved = flops / ws / t_kernel / 1e12
         roofline = {"bound": "tensor", "achieved": achieved, "peak": dgemm_peak,

@@ -361,23 +361,66 @@ struct I8Args {
 struct FlagCtx {
     const double* A_src; const double* B_src; const uint4* coltab; const uint64_t* row_x;
     long long n_cols; int kdim_src;
+    unsigned long long* flagged;     // counter of the deferred list (result block, I8_RES_FLAGGED)
+    unsigned long long* lost;        // accepted candidates without a slot (I8_RES_LOST)
 };
 __device__ __noinline__ void emit_flagged(FlagCtx x, CandSink sink, long long r_tab, long long r_loc, long long c0,
                                           uint32_t flags, double f) {
+    // Flagged outputs are NOT evaluated here: scalar FP64 all but stops while the tensor pipe runs (a 256-term
+    // dot product took ~18 us, on a warp the next tile's accumulators were waiting for: 4096 candidates cost
+    // 75 ms, profiles/r2_peaked_probe.log).  They are appended as (local row, column) to the candidate arrays and
+    // evaluated by i8_reeval_kernel after the contraction; only when the arrays are full does the exact test run
+    // here, and what passes it then is counted as lost.
     const uint64_t rx = __ldg(x.row_x + r_tab);
     const double* ar = x.A_src + r_loc * x.kdim_src;
     while (flags) {
         const int c = __ffs(flags) - 1;
         flags &= flags - 1;
         if (c0 + c >= x.n_cols) continue;
+        {
+            const unsigned long long slot = atomicAdd(x.flagged, 1ull);
+            if ((long long)slot < sink.cap) {
+                sink.x[slot] = ((uint64_t)r_loc << 32) | (uint64_t)(c0 + c);
+                continue;
+            }
+        }
         const double* br = x.B_src + (c0 + c) * x.kdim_src;
         double acc = 0.0;
         for (int k = 0; k < x.kdim_src; ++k) acc = fma(ar[k], br[k], acc);
         const double p = acc * f;
-        if (p > sink.threshold) {
-            const uint4 ct = __ldg(x.coltab + c0 + c);
-            const uint64_t cx = ((uint64_t)ct.y << 32 | ct.x) & ~(FLAG_ROW_BAD | FLAG_COL_BAD);
-            cand_emit(sink, rx | cx, p);
+        if (p > sink.threshold) { atomicAdd(sink.count, 1ull); atomicAdd(x.lost, 1ull); }
+    }
+    (void)rx;
+}
+
+// exact evaluation of the deferred list, one warp per entry: p = scale / norm * <A[r], B[c]> in FP64 from the operands
+// themselves; entries above the threshold become (united index, p), the others are marked consumed for the top-k
+__global__ void __launch_bounds__(256) i8_reeval_kernel(FlagCtx x, CandSink sink, const double* __restrict__ res, int use_norm,
+                                                        double scale, long long row_lo) {
+    const unsigned long long n_flag = *x.flagged;
+    const long long n = (long long)n_flag < sink.cap ? (long long)n_flag : sink.cap;
+    const double f = use_norm ? scale / res[I8_RES_NORM] : scale;
+    const int lane = threadIdx.x & 31;
+    for (long long e = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); e < n; e += (long long)gridDim.x * 8) {
+        const uint64_t code = sink.x[e];
+        const long long r_loc = (long long)(code >> 32), c = (long long)(code & 0xffffffffull);
+        const double* ar = x.A_src + r_loc * x.kdim_src;
+        const double* br = x.B_src + c * x.kdim_src;
+        double acc = 0.0;
+        for (int k = lane; k < x.kdim_src; k += 32) acc = fma(ar[k], br[k], acc);
+        acc = warp_sum(acc);
+        const double p = acc * f;
+        if (lane == 0) {
+            if (p > sink.threshold) {
+                const uint4 ct = __ldg(x.coltab + c);
+                const uint64_t cx = ((uint64_t)ct.y << 32 | ct.x) & ~(FLAG_ROW_BAD | FLAG_COL_BAD);
+                sink.x[e] = __ldg(x.row_x + row_lo + r_loc) | cx;
+                sink.p[e] = p;
+                atomicAdd(sink.count, 1ull);
+            } else {
+                sink.x[e] = ~0ull;
+                sink.p[e] = -1.0 / 0.0;
+            }
         }
     }
 }
@@ -827,7 +870,9 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.coltab + c0 + TN + lane * 8));
                     }
                     if (flags && row_ok) {
-                        const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src};
+                        const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src,
+                                            reinterpret_cast<unsigned long long*>(const_cast<double*>(a.res)) + I8_RES_FLAGGED,
+                                            reinterpret_cast<unsigned long long*>(const_cast<double*>(a.res)) + I8_RES_LOST};
                         emit_flagged(fx, a.sink, a.row_lo + r_loc, r_loc, c0, flags, a.out_scale * inv_norm * ldexp(1.0, 8 * (S - 1)));
                     }
                 }
@@ -1094,7 +1139,19 @@ extern "C" int qdc_contract_i8_prepared(const void* d_opA, int64_t n_rows, const
             if (rc != QDC_OK) return rc;
         }
     }
+    unsigned long long* d_list_count = d_cand_count;           // entries of the candidate arrays the top-k walks
+    if (store_mode == 0) {
+        // the scoring-only kernels only flagged outputs: evaluate them exactly now that no MMA runs
+        unsigned long long* d_flagged = reinterpret_cast<unsigned long long*>(d_result) + I8_RES_FLAGGED;
+        const FlagCtx fx = {d_A_src, d_Bt_src, (const uint4*)((const uint8_t*)d_opB + i8_layout(n_cols, kdim, n_stored).off_coltab),
+                            d_row_x, (long long)n_cols, kdim, d_flagged,
+                            reinterpret_cast<unsigned long long*>(d_result) + I8_RES_LOST};
+        const CandSink sink = {d_cand_x, d_cand_p, d_cand_count, (long long)cand_cap, threshold};
+        i8_reeval_kernel<<<sms * 4, 256, 0, s>>>(fx, sink, d_result, norm_mode != 0, scale, (long long)row_lo);
+        QDC_CHECK_LAUNCH();
+        d_list_count = d_flagged;
+    }
     // the masked sum (slots 0 and 2 of the partials are zero) and the top-k, one launch
-    return qdc_launch_finish(d_partials, sms, d_result + I8_RES_SUMS, d_cand_x, d_cand_p, d_cand_count, cand_cap, k,
+    return qdc_launch_finish(d_partials, sms, d_result + I8_RES_SUMS, d_cand_x, d_cand_p, d_list_count, cand_cap, k,
                              d_top_x, d_top_p, s);
 }

@@ -58,4 +58,6 @@ constexpr int I8_RES_BOUND_OUT = 5;      // a-posteriori bound per output for th
 constexpr int I8_RES_BOUND_COST = 6;     // ... and on the masked sum
 constexpr int I8_RES_CAND = 7;           // candidate counter (unsigned 64-bit integer in the same slot size)
 constexpr int I8_RES_EMAX = 8;           // largest column exponent (integer valued)
+constexpr int I8_RES_FLAGGED = 9;        // outputs the integer filter flagged (uint64): entries of the candidate arrays before re-evaluation
+constexpr int I8_RES_LOST = 10;          // candidates above the threshold that found no room in the arrays (uint64)
 constexpr int I8_RES_DOUBLES = 16;

@@ -113,6 +113,11 @@ class ScoreResult:
             h = self._block_host()
             k = self.top_x.numel()
             sums, n_cand = h[0:3], int(h[7:8].view(np.int64)[0])
+            # h[9]: outputs the integer filter flagged (a superset, re-evaluated exactly on the device);
+            # h[10]: candidates above the threshold that found no room because the flagged list was full
+            if int(h[10:11].view(np.int64)[0]) > 0:
+                raise _lib.QdcError(f"top-k candidate buffer overflow: {int(h[9:10].view(np.int64)[0])} outputs were flagged "
+                                    f"for exact re-evaluation and did not fit the candidate arrays; raise the threshold or pass a larger cand_cap")
             xs, ps = h[16:16 + k].view(np.int64), h[16 + k:16 + 2 * k]
         else:
             sums = self.sums.cpu().numpy()
@@ -425,7 +430,11 @@ def _contract_i8(A, Bt, tables, scale, threshold, k, normalize, row_lo, n_rows, 
     assert store_mode == 0 or N == 1 << tables.col_bits
     if cand_cap is None:
         cand_cap = _default_cap(n_rows * N, threshold)
-    ws = _Workspace.get(dev, kdim, cand_cap, k)
+    # the scoring-only kernels file every output their integer filter FLAGS (a superset of the candidates) in
+    # the candidate arrays and a follow-up kernel evaluates those exactly: the arrays get room for the
+    # superset (64 MB at most), `cand_cap` stays the limit on true candidates
+    list_cap = cand_cap if store_mode else max(cand_cap, min(n_rows * N, 1 << 22))
+    ws = _Workspace.get(dev, kdim, list_cap, k)
     if store_mode and out is None:
         out = torch.empty(n_rows, N, dtype=out_dtype, device=dev)
     block = torch.empty(16 + 2 * max(k, 1), dtype=torch.float64, device=dev)
@@ -469,7 +478,7 @@ def _contract_i8(A, Bt, tables, scale, threshold, k, normalize, row_lo, n_rows, 
             float(threshold), _lib.ptr(a_prep.src), _lib.ptr(b_prep.src), row_lo,
             _lib.ptr(tables.row_x), _lib.ptr(tables.row_forb), _lib.ptr(tables.row_wok),
             _lib.ptr(out), store_mode, _lib.ptr(block), _lib.ptr(ws["cand_x"]), _lib.ptr(ws["cand_p"]),
-            cand_cap, k, _lib.ptr(top_x), _lib.ptr(top_p), _lib.ptr(ws["partials"]), sp),
+            list_cap, k, _lib.ptr(top_x), _lib.ptr(top_p), _lib.ptr(ws["partials"]), sp),
             "qdc_contract_i8_prepared")
         if kernel_events is not None:
             ev1.record(stream)

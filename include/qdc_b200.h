@@ -303,9 +303,14 @@ int qdc_contract_f64(const double* d_Ap, int64_t a_rows_total, const double* d_B
  *   integer candidate filter flags are re-evaluated exactly from them).
  *   row tables: indexed row_lo + local row.  store_mode 0, 1 = united slab float64, 2 = float32.
  *   d_result: 16 doubles [sum p, sum p w [indset], sum p w, norm, slices used, bound per output,
- *   bound on the masked sum, candidate count (uint64), largest column exponent, ...] -- written,
- *   not accumulated.  d_cand_*: candidate sink as qdc_mis_reduce; k, d_top_*: as qdc_topk_select
- *   (k = 0: no selection).  d_partials: 3 * qdc_reduce_partials() doubles. */
+ *   bound on the masked sum, candidate count (uint64), largest column exponent, flagged outputs
+ *   (uint64), lost candidates (uint64), ...] -- written, not accumulated.  d_cand_*: candidate sink as
+ *   qdc_mis_reduce; k, d_top_*: as qdc_topk_select (k = 0: no selection).  With store_mode 0 the
+ *   contraction only FLAGS outputs (an integer test on the leading digit order: a superset of the
+ *   candidates) into the candidate arrays and a follow-up kernel evaluates them exactly from the FP64
+ *   operands, so cand_cap should leave room for the superset (the Python side passes up to 2^22
+ *   entries); entry [10] counts candidates that found no room (0 = the result is complete).
+ *   d_partials: 3 * qdc_reduce_partials() doubles. */
 int64_t qdc_i8_operand_bytes(int64_t n_rows, int kdim, int n_slices);
 int qdc_i8_prepare(const double* d_X, int64_t n_rows, int kdim, int n_slices, int column_role,
                    const uint32_t* d_wok, const uint64_t* d_x, void* d_operand, void* stream);
