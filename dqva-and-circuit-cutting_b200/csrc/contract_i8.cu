@@ -439,6 +439,9 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
     constexpr int CPT = cpt_of(TN), N_EPI_WARPS = 4 * (TN / CPT), NSLOT = slots_of(S, TN);
     static_assert(NSLOT * TN <= TMEM_COLS && S - NSLOT <= 1, "accumulator slots");
     static_assert(!PAIR || (EPI == 0 && TN % 32 == 0), "the CTA-pair form is the scoring-only kernel");
+    // EPI 2: the all-integer scoring of EPI 0 plus the outputs themselves as float32 (CutQC's build): the orders of an
+    // output are folded in FP32 (FFMA keeps its rate beside the tensor pipe, scalar FP64 does not) and each thread
+    // stores its 16 consecutive floats as four 16-byte vectors
     constexpr int TNL = PAIR ? TN / 2 : TN;            // columns of the streamed tile this CTA loads
     static_assert(EPI == 0 || (CPT == 16 && NSLOT == S), "the storing epilogue keeps 16 columns per thread and one slot per order");
     // order d of this CTA's tile number `seq` is accumulation number g = seq S + d: it lives in slot g % NSLOT
@@ -742,7 +745,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
             const uint64_t rf = (row_ok ? __ldg(a.tab.row_forb + a.row_lo + r_loc) : 0ull) | FLAG_COL_BAD |
                                 ((rwok >> 8) & 1u ? 0ull : FLAG_ROW_BAD);
             const double rs = row_ok ? a.row_scale[r_loc] * a.out_scale * inv_norm : 0.0;   // row factor
-            if constexpr (EPI == 0) {
+            if constexpr (EPI != 1) {
                 // ---------- all-integer masked sums ----------
                 const int w_r = (int)(rwok & 0xffu);
                 const int emax = (int)a.res[I8_RES_EMAX];
@@ -750,7 +753,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                 // D_0 >= T 2^-f_c - margin with T = threshold 2^7 / (256^(S-1) rs) = tm 2^tq, tm in [2^30, 2^31);
                 // f_c <= gref of the column group
                 int tm = 0x7fffffff, tq = 1 << 24;
-                if (rs > 0.0) {
+                if (rs > 0.0 && a.sink.threshold * 128.0 / rs < 1e300) {               // (an infinite threshold: nothing is ever a candidate)
                     int ex;
                     const double fr = frexp(a.sink.threshold * 128.0 / rs, &ex);      // (rs carries 256^-(S-1): T = this / 256^(S-1))
                     if (fr > 0.0) { tm = (int)(fr * 2147483648.0); tq = ex - 31 - 8 * (S - 1); }
@@ -811,6 +814,8 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                         tcmp = max(tg, (int)0x80000000 + D0_MARGIN) - D0_MARGIN;
                     }
                     int m[CPT];                             // [independent] (w_r + w_c) << lsh_c
+                    float fo[EPI == 2 ? CPT : 1];           // EPI 2: the output itself, folded over the orders in FP32
+                    float fsc[EPI == 2 ? CPT : 1];          //        and its column factor 2^(f_c - 7) = 2^(gref - 27) (1 << lsh_c)
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) {
                         uint4 ct;                                       // (x_lo, x_hi | flags, w_c << lsh_c, 1 << lsh_c)
@@ -821,6 +826,7 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                             ct = __ldg(a.coltab + c0 + c);
                         const bool ok = ((ct.x & (uint32_t)rf) | (ct.y & (uint32_t)(rf >> 32))) == 0u;
                         m[c] = ok ? w_r * (int)ct.w + (int)ct.z : 0;
+                        if constexpr (EPI == 2) fsc[c] = gr == E_ZERO ? 0.0f : ldexpf((float)ct.w, gr - I8_LSH_MAX - 7);
                     }
                     if constexpr (PAIR) {                               // the stage may be refilled
                         __syncwarp();
@@ -851,6 +857,11 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                             }
 #pragma unroll
                             for (int c = 0; c < 16; ++c) r += (long long)(int32_t)v[c] * (long long)m[h * 16 + c];
+                            if constexpr (EPI == 2) {
+#pragma unroll
+                                for (int c = 0; c < 16; ++c)
+                                    fo[h * 16 + c] = d == 0 ? (float)(int32_t)v[c] : fmaf(fo[h * 16 + c], 256.0f, (float)(int32_t)v[c]);
+                            }
                             if (d == 0) {                   // candidate filter: one max tree, compares only on a hit
                                 int mx = (int32_t)v[0];
 #pragma unroll
@@ -868,6 +879,24 @@ __global__ void __launch_bounds__((FIRST_EPI_WARP + 4 * (TN / cpt_of(TN))) * 32,
                         // of shared memory leave)
                         if (!PAIR && d == (S > 2 ? S - 3 : 0) && cb + 1 < cb1 && lane < CPT / 8)
                             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.coltab + c0 + TN + lane * 8));
+                    }
+                    if constexpr (EPI == 2) {
+                        // P~[r, c] = (sum_d D_d 256^(S-1-d)) * 2^(f_c - 7) * rs, as float32
+                        if (row_ok) {
+                            const float rsf = (float)rs;
+                            float* out = reinterpret_cast<float*>(a.P_out) + (long long)r_loc * a.n_cols + c0;
+                            if ((a.n_cols & 3) == 0 && c0 + CPT <= a.n_cols) {
+#pragma unroll
+                                for (int c = 0; c < CPT; c += 4)
+                                    __stcs(reinterpret_cast<float4*>(out + c),
+                                           make_float4(fo[c] * rsf * fsc[c], fo[c + 1] * rsf * fsc[c + 1],
+                                                       fo[c + 2] * rsf * fsc[c + 2], fo[c + 3] * rsf * fsc[c + 3]));
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < CPT; ++c)
+                                    if (c0 + c < a.n_cols) out[c] = fo[c] * rsf * fsc[c];
+                            }
+                        }
                     }
                     if (flags && row_ok) {
                         const FlagCtx fx = {a.A_src, a.B_src, a.coltab, a.tab.row_x, a.n_cols, a.kdim_src,
@@ -1010,10 +1039,11 @@ int i8_tile_n(int n_slices, int kd, int store) {
     if (const char* m = getenv("QDC_I8_TN")) {
         const int tn = atoi(m);
         if (tn == 64) return 64;
-        if (tn == 96 && n_slices == 5 && fits(96)) return 96;
+        if (tn == 96 && n_slices == 5 && fits(96) && store != 2) return 96;
         if (tn == 128 && !store && n_slices <= 5 && fits(128)) return 128;
     }
     if (!store && n_slices <= 5 && fits(128)) return 128;
+    if (store == 2) return 64;                           // float32 outputs (EPI 2): 16 more live registers per thread than 72 leave
     if (n_slices == 5 && fits(96)) return 96;
     return 64;
 }
@@ -1021,7 +1051,7 @@ int i8_tile_n(int n_slices, int kd, int store) {
 // one instantiation for one slice count: geometry, work split, launch
 int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
     const int kd = a.kdim;
-    const int TN = i8_tile_n(n_slices, kd, store);
+    const int TN = i8_tile_n(n_slices, kd, store ? (a.out32 ? 2 : 1) : 0);
     // CTA pairs (cta_group::2): the scoring-only kernel at 128 columns and kdim 256, at least two 256-row units
     bool pair = !store && TN == 128 && kd == 256 && n_slices >= 3 && n_slices <= 5 && a.n_rows > 2 * TM;
     if (const char* m = getenv("QDC_I8_PAIR")) pair = pair && atoi(m) != 0;
@@ -1066,8 +1096,8 @@ int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
         }
     }
 #define QDC_I8_CASE(SS, TT)                                                                         \
-    if (n_slices == SS && TN == TT)                                                                 \
-        return store ? launch_i8<SS, TT, 1>(a, grid, smem, s) : launch_i8<SS, TT, 0>(a, grid, smem, s);
+    if (n_slices == SS && TN == TT && !(TT == 96 && store && a.out32))                               \
+        return !store ? launch_i8<SS, TT, 0>(a, grid, smem, s) : (a.out32 ? launch_i8<SS, TT, 2>(a, grid, smem, s) : launch_i8<SS, TT, 1>(a, grid, smem, s));
     QDC_I8_CASE(2, 64) QDC_I8_CASE(3, 64) QDC_I8_CASE(4, 64) QDC_I8_CASE(5, 64) QDC_I8_CASE(5, 96) QDC_I8_CASE(6, 64)
 #undef QDC_I8_CASE
     if (!store && TN == 128) {
@@ -1105,7 +1135,7 @@ extern "C" int qdc_contract_i8_prepared(const void* d_opA, int64_t n_rows, const
     QDC_REQUIRE(norm_mode >= 0 && norm_mode <= 2 && (norm_mode != 2 || d_norm_in), "norm_mode 0 (none), 1 (from the operands), 2 (given)");
     QDC_REQUIRE(store_mode == 0 || ((store_mode == 1 || store_mode == 2) && d_P_out),
                 "store_mode 0 (none), 1 (united slab, float64) or 2 (united slab, float32)");
-    QDC_REQUIRE(store_mode != 0 || (d_A_src && d_Bt_src), "the FP64 operands are needed to re-evaluate flagged candidates");
+    QDC_REQUIRE(store_mode == 1 || (d_A_src && d_Bt_src), "the FP64 operands are needed to re-evaluate flagged candidates");
     QDC_REQUIRE(k >= 0 && k <= 1024 && (k == 0 || (d_top_x && d_top_p)), "k");
     cudaStream_t s = (cudaStream_t)stream;
     const int sms = qdc_sm_count();
@@ -1140,8 +1170,8 @@ extern "C" int qdc_contract_i8_prepared(const void* d_opA, int64_t n_rows, const
         }
     }
     unsigned long long* d_list_count = d_cand_count;           // entries of the candidate arrays the top-k walks
-    if (store_mode == 0) {
-        // the scoring-only kernels only flagged outputs: evaluate them exactly now that no MMA runs
+    if (store_mode != 1) {
+        // the integer-scoring kernels only flagged outputs: evaluate them exactly now that no MMA runs
         unsigned long long* d_flagged = reinterpret_cast<unsigned long long*>(d_result) + I8_RES_FLAGGED;
         const FlagCtx fx = {d_A_src, d_Bt_src, (const uint4*)((const uint8_t*)d_opB + i8_layout(n_cols, kdim, n_stored).off_coltab),
                             d_row_x, (long long)n_cols, kdim, d_flagged,

@@ -5,6 +5,7 @@ owns the buffers, every number comes from the C-ABI (`qdc_cutqc_*`, `qdc_khatri_
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -136,6 +137,13 @@ def build(kron: Sequence[torch.Tensor], term_index: Sequence[Sequence[int]], num
         rb = int(A.shape[0]).bit_length() - 1
         cb = int(Bt.shape[0]).bit_length() - 1
         tabs = _rc.build_tables(rb, cb, list(range(rb + cb)), [0] * (rb + cb), 0, device=dev)
+        if (contraction is None and "QDC_CONTRACTION" not in os.environ and out_dtype == torch.float32 and 128 <= kdim <= 256
+                and A.shape[0] * Bt.shape[0] >= 1 << 26):
+            # float32 outputs (the reference's build.c is float32): 5 exact int8 slices bound the error at 1e-9 of the
+            # largest product, far below float32 rounding, and the integer-scoring / FP32-fold epilogue is 2x the
+            # FP64 DMMA kernel at 2^28 outputs and 256 terms (profiles/r2_time_build.log); below 2^26 outputs the
+            # fixed cost of slicing the operands outweighs it, and with few terms the FP64 kernel is as fast
+            contraction = "i8:5"
         method, slices = _rc.resolve_contraction(contraction)
         if method == "i8" and kdim > 256:
             if contraction is not None:

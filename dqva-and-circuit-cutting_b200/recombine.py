@@ -433,7 +433,7 @@ def _contract_i8(A, Bt, tables, scale, threshold, k, normalize, row_lo, n_rows, 
     # the scoring-only kernels file every output their integer filter FLAGS (a superset of the candidates) in
     # the candidate arrays and a follow-up kernel evaluates those exactly: the arrays get room for the
     # superset (64 MB at most), `cand_cap` stays the limit on true candidates
-    list_cap = cand_cap if store_mode else max(cand_cap, min(n_rows * N, 1 << 22))
+    list_cap = cand_cap if store_mode == 1 else max(cand_cap, min(n_rows * N, 1 << 22))
     ws = _Workspace.get(dev, kdim, list_cap, k)
     if store_mode and out is None:
         out = torch.empty(n_rows, N, dtype=out_dtype, device=dev)

@@ -205,6 +205,19 @@ def test_int8_sliced_contraction_per_output_bound(cuda, slices):
     assert np.all(got[3] == 0.0)
     s = res.get()
     assert abs(s["sum_p"] - want.sum()) <= bound.sum() + 1e-12 * np.abs(want).sum()
+    # float32 outputs (what CutQC's build stores): integer scoring + FP32 fold of the orders + vector stores; the
+    # same bound plus float32 rounding of the result (5 roundings of the fold, 2 of the scaling), same sums
+    res32 = rc.contract_and_score(torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda), tabs,
+                                  scale=scale, threshold=float("inf"), k=1, normalize=False,
+                                  store="united", out_dtype=torch.float32, method="i8", slices=slices)
+    assert res32.P.dtype == torch.float32
+    got32 = res32.P.cpu().numpy().astype(np.float64)
+    ulp = 2.0 ** -23 * (2.0 ** (ea + fb) * scale * kdim)          # float32 rounding relative to the largest possible |output|
+    assert np.all(np.abs(got32 - want) <= bound + fp64_noise + 8 * ulp + 1e-45), float(np.max(np.abs(got32 - want) / (bound + 8 * ulp + 1e-300)))
+    assert np.all(got32[3] == 0.0)
+    s32 = res32.get()
+    for key in ("sum_p", "sum_pw", "sum_pw_indset"):
+        assert abs(s32[key] - s[key]) <= 2 * bound.sum() * (rb + cb) + 1e-12 * abs(s[key])
 
 
 def test_int8_contraction_row_slabs_and_given_norm(cuda):
