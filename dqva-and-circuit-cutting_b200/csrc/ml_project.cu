@@ -122,9 +122,6 @@ __device__ PackedTab pack_table(const int* __restrict__ idx, const double2* __re
         const double tol = 1e-12 * sc;
         const int re = fabs(fabs(c.x) - sc) <= tol ? (c.x > 0.0 ? 1 : -1) : 0, im = fabs(fabs(c.y) - sc) <= tol ? (c.y > 0.0 ? 1 : -1) : 0;
         if ((re == 0 && fabs(c.x) > tol) || (im == 0 && fabs(c.y) > tol)) bad = true;
-#ifdef QDC_ML_DEBUG
-        if (bad && blockIdx.x == 0) printf("bad entry e=%d k=%d c=(%.17g, %.17g) sc=%.17g\n", e, k, c.x, c.y, sc);
-#endif
         int code = k;
         if (inverse) { code = ((k >> 8) << 4) | (k & 0xff); if ((k >> 8) >= 16 || (k & 0xff) >= 16) bad = true; }
         else if (k < 0 || k > 255) bad = true;
@@ -134,9 +131,6 @@ __device__ PackedTab pack_table(const int* __restrict__ idx, const double2* __re
     }
     if (bad) atomicOr(s_bad, 1);
     __syncthreads();
-#ifdef QDC_ML_DEBUG
-    if (blockIdx.x == 0 && threadIdx.x == 0) printf("pack_table D=%d inverse=%d scale=%g bad=%d first=(%d; %g, %g)\n", D, (int)inverse, sc, *s_bad, idx[0], coef[0].x, coef[0].y);
-#endif
     PackedTab t = {dst, sc, *s_bad == 0};
     return t;
 }
