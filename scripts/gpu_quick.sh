@@ -1,4 +1,2 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_contract_score.py tests/test_gpu_cutqc.py tests/test_gpu_cutqc_pipeline.py -x -q -m gpu 2>&1 | tail -12
-timeout 600 python scripts/time_cutqc.py 2>&1 | grep build | tee gpurun_out/time_build.log
+timeout 900 python -m pytest tests/test_gpu_contract_score.py -x -q -m gpu -k "flagged_list" 2>&1 | tail -15

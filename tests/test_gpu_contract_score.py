@@ -435,3 +435,32 @@ def test_colsum_and_norm_kernels(cuda):
                                          _lib.ptr(norm), _lib.stream_ptr()))
         want_n = 0.25 * float(X.sum(0) @ Y.sum(0))
         assert abs(float(norm) - want_n) < 1e-9 * max(1.0, abs(want_n))
+
+
+def test_int8_flagged_list_overflow_is_reported(cuda):
+    """The scoring-only int8 kernels file every output their integer filter flags and a follow-up kernel
+    evaluates those exactly (i8_reeval_kernel).  With threshold 0 every output is flagged: 2^23 of them do
+    not fit the 2^22-entry list, the exact test then runs inline, and because true candidates found no room
+    the result says so instead of silently dropping them; with a threshold that leaves a handful of candidates
+    the same operands give the FP64 kernel's candidates, and an infinite threshold flags nothing."""
+    import torch
+    from qdc_b200 import recombine as rc
+    from qdc_b200._lib import QdcError
+    rb, cb, kdim = 12, 11, 32
+    rng = np.random.default_rng(3)
+    A = rng.random((1 << rb, kdim)); Bt = rng.random((1 << cb, kdim))
+    A[17] *= 50.0; Bt[5] *= 50.0
+    tabs = rc.build_tables(rb, cb, list(range(rb + cb)), [0] * (rb + cb), (1 << (rb + cb)) - 1, device=cuda)
+    A_d, B_d = torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda)
+    res = rc.contract_and_score(A_d, B_d, tabs, threshold=0.0, k=1, method="i8", slices=4)
+    with pytest.raises(QdcError, match="flagged"):
+        res.get()
+    want = A @ Bt.T
+    want /= want.sum()
+    thr = float(0.5 * (np.sort(want.reshape(-1))[-6] + np.sort(want.reshape(-1))[-7]))
+    got = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=6, method="i8", slices=4).get()
+    ref = rc.contract_and_score(rc.pad_kdim(A_d), rc.pad_kdim(B_d), tabs, threshold=thr, k=6).get()
+    assert got["n_candidates"] == ref["n_candidates"] == 6
+    assert [x for x, _ in got["top"]] == [x for x, _ in ref["top"]]
+    none = rc.contract_and_score(A_d, B_d, tabs, threshold=float("inf"), k=1, method="i8", slices=4)
+    assert none.get()["n_candidates"] == 0 and float(none.block[9:10].view(torch.int64).item()) == 0
