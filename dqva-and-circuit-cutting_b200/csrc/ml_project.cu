@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(ML_WARPS * 32) ml_rebuild_kernel(const double*
 }
 
 __global__ void ml_init_kernel(MlState* st, int force_full) {
-    st->need_full = force_full ? 1 : 0; st->done = 0; st->counter = 0u; st->newton_steps = 0;
+    st->need_full = force_full > 0 ? 1 : 0; st->done = 0; st->counter = 0u; st->newton_steps = 0;
     st->t = 0.0; st->total = 0.0; st->abs_total = 0.0; st->conj_not_diag = 0;
 }
 
@@ -456,12 +456,14 @@ int ml_run(const double* T, long long n, long long ld, MlTables tab, double* T_o
     const int grid = (int)(want < 148ll * 16 ? want : 148ll * 16);
     ml_init_kernel<<<1, 1, 0, s>>>(st, force_full);
     QDC_CHECK_LAUNCH();
-    if (!force_full) {
+    if (force_full <= 0) {
         // (sgn lives in the Newton partials: they are only touched when the full path runs, the signs only when it does not)
         ml_conj_map_kernel<D><<<D * D, D * D, 0, s>>>(tab, st, partials);
         QDC_CHECK_LAUNCH();
-        ml_psd_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st);
-        QDC_CHECK_LAUNCH();
+        if (force_full == 0) {                             // (< 0: the caller vouches for positive semidefinite blocks)
+            ml_psd_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st);
+            QDC_CHECK_LAUNCH();
+        }
     }
     ml_jacobi_kernel<D><<<grid, ML_WARPS * 32, 0, s>>>(T, n, ld, tab, st, evals, vecs);
     QDC_CHECK_LAUNCH();

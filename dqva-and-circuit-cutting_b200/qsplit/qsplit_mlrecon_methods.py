@@ -11,8 +11,9 @@ numbers are made:
 * `direct_fragment_model`   (:273-317)  the per-bitstring least-squares inversion is, for exact
   (infinite-shot) data, a fixed linear map: the kernel `qdc_sv_pauli_tensor` produces the Choi
   blocks in the Pauli basis straight from the amplitudes.
-* `maximum_likelihood_model`(:320-356)  batched `eigh` + the global eigenvalue clipping, on the
-  device the model lives on (torch / cuSOLVER library call; a no-op up to 1e-15 on exact data).
+* `maximum_likelihood_model`(:320-356)  per-block eigen-decomposition + the global eigenvalue
+  clipping as this package's own kernels (csrc/ml_project.cu: Cholesky PSD test, one-warp Jacobi,
+  soft-threshold by Newton steps, rebuild); a sign flip per tensor component on exact data.
 * `recombine_fragment_models`(:463-472) the `itertools.product` loop over all fragment
   bitstrings becomes one FP64 tensor-core contraction over the cut-basis index with the
   bit permutation of `united_axis_permutation` (:532-536) folded into the scoring tables
@@ -20,8 +21,9 @@ numbers are made:
 
 Objects returned are `Mapping`s with the reference's dict layouts (materialised lazily, for the
 sizes where a Python dict is sensible) that keep their device tensors for the next stage.
-The reference samples `shots` outcomes per variant; this engine evaluates the infinite-shot limit
-(SURVEY.md 7.4-2): `shots` only scales the numbers shown by the dict views.
+The reference samples `shots` outcomes per variant; by default this engine evaluates the
+infinite-shot limit (SURVEY.md 7.4-2: `shots` only scales the numbers shown by the dict views);
+`collect_fragment_data(sample=True)` draws the counts on the device (csrc/shot_sampler.cu).
 """
 from __future__ import annotations
 
@@ -525,7 +527,9 @@ def direct_fragment_model(tomography_data, discard_poor_data=False, rank_cutoff=
         d = tomography_data
         T = d.backend.pauli_tensor(d.states, d.prog, d.n_sets, len(d.prep_qubits), d.meas_qubits,
                                    frame=SIC_FRAME, basis_inputs=d.basis_inputs)
-        return FragmentModel(T, len(d.prep_qubits), len(d.meas_qubits), d.cut_labels, d.shots)
+        model = FragmentModel(T, len(d.prep_qubits), len(d.meas_qubits), d.cut_labels, d.shots)
+        model.exact = True                   # built from simulated amplitudes: every Choi block is a Gram matrix
+        return model
     if not torch.cuda.is_available():
         raise _lib.QdcError("direct_fragment_model needs a CUDA device; there is no CPU fallback")
     return _model_from_counts(tomography_data, torch.device("cuda"), rank_cutoff)
@@ -566,7 +570,7 @@ def _ml_tables(n_prep, n_meas, dev):
     return _ML_TABLES[key]
 
 
-def maximum_likelihood_model(choi_matrix, force_full=False):
+def maximum_likelihood_model(choi_matrix, force_full=False, assume_psd=None):
     """Nearest positive-semidefinite model (:320-356) on the device (`qdc_ml_project`,
     csrc/ml_project.cu): every Choi block is eigen-decomposed by a one-warp Jacobi, ALL eigenvalues
     of the fragment are clipped together -- the reference's sequential walk (:333-343) is
@@ -575,10 +579,14 @@ def maximum_likelihood_model(choi_matrix, force_full=False):
     complex conjugate of V diag V^+, as the reference's `to_projector` does (:45-46, 354-356).  When a
     Cholesky test finds every block positive semidefinite to 1e-14 of its trace (exact,
     infinite-shot data), t0 = 0 and only the conjugate is taken; `force_full=True` skips that test.
+    `assume_psd` skips it the other way: models that `direct_fragment_model` built from exactly
+    simulated amplitudes are Gram matrices, positive semidefinite by construction, and the reference's
+    projection changes them by rounding noise only; they carry `exact = True` and take this path by
+    default (`assume_psd=False` runs the test anyway).
     `model.ml_info[s]` holds (needed the full path, Newton steps, t0) of parameter set s on the
     device.  No host synchronisation."""
     if type(choi_matrix) is list:
-        return [maximum_likelihood_model(m, force_full) for m in choi_matrix]
+        return [maximum_likelihood_model(m, force_full, assume_psd) for m in choi_matrix]
     if not isinstance(choi_matrix, FragmentModel):
         raise _lib.QdcError("maximum_likelihood_model expects the FragmentModel returned by "
                             "direct_fragment_model (device-resident Choi blocks)")
@@ -597,6 +605,9 @@ def maximum_likelihood_model(choi_matrix, force_full=False):
     n_sets, n_b, K = T.shape
     assert K == D * D
     fwd_k, fwd_c, inv_ij, inv_c = _ml_tables(model.n_prep, model.n_meas, dev)
+    if assume_psd is None:
+        assume_psd = bool(getattr(model, "exact", False))
+    mode = 1 if force_full else (-1 if assume_psd else 0)
     out = torch.empty_like(T)
     ws_bytes = int(lib.qdc_ml_workspace_bytes(n_b, D))
     info = []
@@ -605,7 +616,7 @@ def maximum_likelihood_model(choi_matrix, force_full=False):
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
             _lib.check(lib.qdc_ml_project(_lib.ptr(T[s]), n_b, D, K, _lib.ptr(fwd_k), _lib.ptr(fwd_c),
                                           _lib.ptr(inv_ij), _lib.ptr(inv_c), _lib.ptr(out[s]), K,
-                                          _lib.ptr(ws), 1 if force_full else 0, _lib.stream_ptr()),
+                                          _lib.ptr(ws), mode, _lib.stream_ptr()),
                        "qdc_ml_project")
             info.append(ws[:40])                         # MlState: need_full, done, counter, steps, t, total, |total|
     result = FragmentModel(out, model.n_prep, model.n_meas, model.cut_labels, model.scale)

@@ -233,8 +233,10 @@ int  qdc_sv_pauli_tensor(const void* d_state, int n_qubits, int64_t n_sets, uint
  * One warp per block: Cholesky test of Lambda + 1e-14 trace I; if every block passes (exact data)
  * the result is conj(Lambda).  Otherwise parallel-order Jacobi per block, the clipping threshold
  * t0 (root of sum max(lambda - t, 0) = sum lambda, equal to the reference's sequential walk) by
- * Newton steps over deterministic grid-wide reductions, and the rebuild.  force_full != 0 skips
- * the test.  d_workspace: qdc_ml_workspace_bytes(n_blocks, dim) bytes, 16-byte aligned; its first
+ * Newton steps over deterministic grid-wide reductions, and the rebuild.  force_full > 0 skips
+ * the test and takes the full path; force_full < 0 skips the test and takes the exact-data path
+ * (for blocks the caller knows to be positive semidefinite by construction: models of exactly
+ * simulated fragments, where the projection changes nothing beyond rounding).  d_workspace: qdc_ml_workspace_bytes(n_blocks, dim) bytes, 16-byte aligned; its first
  * 40 bytes report {int need_full, done, -, newton_steps; double t0, sum lambda, sum |lambda|}.
  * Nothing is read back by the host. */
 int64_t qdc_ml_workspace_bytes(int64_t n_blocks, int dim);

@@ -70,6 +70,14 @@ def test_stage_dict_views_match_oracle(cuda):
             if np.abs(block).max() < 1e-12:
                 continue
             assert np.abs(got_f[bits] / shots - block).max() < 1e-9
+    # models of exactly simulated fragments are Gram matrices: they carry `exact` and skip the Cholesky test
+    # (the oracle comparison above ran that way); running the test anyway, or the full Jacobi path, agrees
+    for model, fast in zip(direct, likely):
+        assert model.exact and not qmm.ml_info_host(fast)[0]
+        tested = qmm.maximum_likelihood_model(model, assume_psd=False)
+        assert not qmm.ml_info_host(tested)[0] and torch.equal(tested.T, fast.T)
+        full = qmm.maximum_likelihood_model(model, force_full=True)
+        assert float((full.T - fast.T).abs().max()) < 1e-9 * shots
 
 
 @pytest.mark.parametrize("fused", [False, True])
