@@ -664,7 +664,7 @@ def run_b200(args):
         except Exception as exc:
             line["variant_sims"] = {"value": None, "note": f"failed: {exc}"}
         try:
-            line["c4_circuit"] = c4_circuit_leg(torch, dev, n_sets=2, steps=2,
+            line["c4_circuit"] = c4_circuit_leg(torch, dev, n_sets=4, steps=4,
                                                 contraction="i8:auto" if args.method == "i8" else "f64")
         except Exception as exc:
             line["c4_circuit"] = {"ms_per_evaluation": None, "note": f"failed: {exc!r}"}

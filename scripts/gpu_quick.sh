@@ -1,4 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_qsplit.py tests/test_gpu_configs.py -x -q -m gpu 2>&1 | tail -5
-timeout 600 python scripts/time_c4_circuit.py > gpurun_out/c4_stages_plain.log 2>&1; tail -7 gpurun_out/c4_stages_plain.log
+timeout 600 python scripts/probe_cut_cost.py 2>&1 | tail -45 | tee gpurun_out/cut_cost_profile.log
