@@ -35,6 +35,8 @@ SIGNATURES = {
     "qdc_sv_dump": (C.c_int, [vp] * 9),
     "qdc_sv_run": (C.c_int, [vp, vp, c_i64, c_i64, c_i64, vp, C.c_int, C.POINTER(C.c_int32),
                              C.c_int, C.POINTER(C.c_double), C.c_int, vp, vp]),
+    "qdc_sv_score_workspace_bytes": (c_i64, [vp, c_i64]),
+    "qdc_sv_run_score": (C.c_int, [vp, vp, c_i64, vp, C.c_int, vp, vp, C.c_uint64, C.c_int, vp, vp, vp]),
     "qdc_sv_probs": (C.c_int, [vp, C.c_int, c_i64, C.c_uint64, vp, vp]),
     "qdc_sv_sample_workspace_doubles": (c_i64, [C.c_int, c_i64]),
     "qdc_sv_sample_counts": (C.c_int, [vp, C.c_int, c_i64, c_i64, C.c_uint64, c_i64, C.c_uint64, C.c_uint64,

@@ -69,6 +69,13 @@ struct GroupArgs {
     uint64_t prep_mask, hole_mask;
     int n, t, n_sets, n_mats, op_lo, op_hi, first, n_runs, n_prep, n_codes;
     int bulk;                 // stage the tile with bulk copies (runs of >= 64 bytes)
+    // fused MIS scoring of the final state (last group of qdc_sv_run_score): sum p, sum p w [independent], sum p w
+    // per CTA into score_partials[3 blockIdx.x + .], w = popcount of the node bits, straight from the tile
+    const uint64_t* score_tab;    // per tile-local index: logical node bits | w << 48 | [independent among themselves] << 63
+    const uint64_t* score_adj;    // adjacency masks of the graph nodes (bit i of adj[j] <=> edge (i, j))
+    double* score_partials;
+    uint64_t score_flip, score_nodes;
+    int score, store;         // store = 0: the state is not written back (only its score is wanted)
     uint8_t run_pos[MAX_RUNS], run_len[MAX_RUNS];
     uint8_t prep_q[MAX_PREP];
     double code[MAX_CODES][4];
@@ -317,6 +324,48 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
             __syncthreads();
         }
     }
+    if (a.score) {
+        // ---- MIS objective of this tile, from shared memory: no second pass over the state ----
+        __shared__ uint64_t sh_forb;
+        __shared__ int sh_bw;
+        __shared__ double sh_red[3][16];
+        __syncthreads();
+        if (tid < 32) {
+            // the tile's fixed (non-local) bits: their weight, whether they are independent among themselves,
+            // and the union of their neighbourhoods (a local node conflicts with them iff it lies in it)
+            const uint64_t xb = (base ^ (a.score_flip & hole)) & a.score_nodes;
+            uint64_t f = 0;
+            bool bad = false;
+            for (int i = (int)tid; i < a.n; i += 32)
+                if ((xb >> i) & 1ull) { const uint64_t ai = a.score_adj[i]; f |= ai; bad |= (ai & xb) != 0ull; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) f |= __shfl_xor_sync(0xffffffffu, f, o);
+            bad = __any_sync(0xffffffffu, bad);
+            if (tid == 0) { sh_forb = f; sh_bw = __popcll(xb) | (bad ? 0 : 256); }
+        }
+        __syncthreads();
+        const uint64_t forb_b = sh_forb;
+        const int wb = sh_bw & 255;
+        const bool okb = (sh_bw >> 8) != 0;
+        double s_p = 0.0, s_pwok = 0.0, s_pw = 0.0;
+        for (uint32_t l = tid; l < T; l += nthr) {
+            const uint64_t e = __ldg(a.score_tab + l);
+            const double2 v = tile[l];
+            const double p = v.x * v.x + v.y * v.y;
+            const double pw = p * (double)((int)((e >> 48) & 0x7full) + wb);
+            s_p += p; s_pw += pw;
+            if (okb && (e >> 63) && ((e & 0xffffffffffffull) & forb_b) == 0ull) s_pwok += pw;
+        }
+        s_p = warp_sum(s_p); s_pwok = warp_sum(s_pwok); s_pw = warp_sum(s_pw);
+        if ((tid & 31) == 0) { sh_red[0][tid >> 5] = s_p; sh_red[1][tid >> 5] = s_pwok; sh_red[2][tid >> 5] = s_pw; }
+        __syncthreads();
+        if (tid < 3) {
+            double t = 0.0;
+            for (uint32_t w = 0; w < (nthr >> 5); ++w) t += sh_red[tid][w];
+            a.score_partials[3 * (size_t)blk + tid] = t;
+        }
+        if (!a.store) return;
+    }
     if (bulk) {
         // the gate passes wrote the tile through the generic proxy: order them before the bulk reads
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -332,6 +381,37 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
     {
         uint64_t x = x_first;
         for (uint32_t l = tid; l < T; l += nthr, x = ((x | hole) + x_step) & ~hole) st[x | base] = tile[l];
+    }
+}
+
+// score table of a group: entry l = logical node bits of tile-local index l | popcount << 48 | [no edge inside] << 63
+__global__ void sv_score_table_kernel(uint64_t* __restrict__ tab, int t, int n_runs, GroupArgs a) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= (1u << t)) return;
+    const uint64_t local_mask = expand_runs((1ull << t) - 1ull, n_runs, a.run_pos, a.run_len);
+    const uint64_t x = (expand_runs(l, n_runs, a.run_pos, a.run_len) ^ (a.score_flip & local_mask)) & a.score_nodes;
+    bool ok = true;
+    for (uint64_t m = x; m; m &= m - 1) {
+        const int i = __ffsll((long long)m) - 1;
+        if (a.score_adj[i] & x) { ok = false; break; }
+    }
+    tab[l] = x | ((uint64_t)__popcll(x) << 48) | ((uint64_t)(ok ? 1 : 0) << 63);
+}
+
+// sums[set][j] = sum over the tiles of a state of partials[3 tile + j], fixed order (deterministic)
+__global__ void __launch_bounds__(1024) sv_score_finish_kernel(const double* __restrict__ partials, long long n_tiles,
+                                                               double* __restrict__ sums) {
+    __shared__ double red[3][32];
+    const double* p = partials + 3 * (size_t)blockIdx.x * n_tiles;
+    double a = 0.0, b = 0.0, c = 0.0;
+    for (long long i = threadIdx.x; i < n_tiles; i += blockDim.x) { a += p[3 * i]; b += p[3 * i + 1]; c += p[3 * i + 2]; }
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = b; red[2][threadIdx.x >> 5] = c; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        double t = 0.0;
+        for (int w = 0; w < 32; ++w) t += red[threadIdx.x][w];
+        sums[3 * blockIdx.x + threadIdx.x] = t;
     }
 }
 
@@ -1084,10 +1164,14 @@ extern "C" int qdc_sv_dump(const qdc_sv_program* prog, int32_t* group_first_op,
     return QDC_OK;
 }
 
-extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int64_t n_init,
-                          int64_t n_sets, const double* d_params, int n_params,
-                          const int32_t* h_prep_qubits, int n_prep, const double* h_code_table,
-                          int n_codes, double* d_matrices, void* stream) {
+struct ScoreReq {                 // fused scoring of the final state (qdc_sv_run_score); tab == nullptr: none
+    uint64_t* tab; const uint64_t* adj; double* partials; double* sums; uint64_t nodes; int keep_state;
+};
+
+static int sv_run_impl(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int64_t n_init,
+                       int64_t n_sets, const double* d_params, int n_params,
+                       const int32_t* h_prep_qubits, int n_prep, const double* h_code_table,
+                       int n_codes, double* d_matrices, const ScoreReq& score, void* stream) {
     QDC_REQUIRE(prog != nullptr && d_state != nullptr, "program / state");
     QDC_REQUIRE(n_init >= 1 && n_sets >= 1 && init_lo >= 0, "batch");
     QDC_REQUIRE(n_prep >= 0 && n_prep <= MAX_PREP, "n_prep");
@@ -1154,10 +1238,52 @@ extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t ini
             const int p0 = gr.n_runs ? (gr.run_pos[0] < prog->t ? gr.run_pos[0] : prog->t) : prog->t;
             a.bulk = use_bulk && p0 >= 2;                  // >= 64-byte runs; shorter ones go element by element
         }
+        a.score = 0; a.store = 1;
+        if (score.tab && g + 1 == prog->groups.size()) {
+            // the last group also scores its tiles (and may skip writing the state back)
+            a.score = 1; a.store = score.keep_state;
+            a.score_tab = score.tab; a.score_adj = score.adj; a.score_partials = score.partials;
+            a.score_flip = prog->flip; a.score_nodes = score.nodes;
+            sv_score_table_kernel<<<((1u << prog->t) + 255) / 256, 256, 0, s>>>(score.tab, prog->t, gr.n_runs, a);
+            QDC_CHECK_LAUNCH();
+        }
         sv_group_kernel<<<(unsigned)grid, threads, smem, s>>>(a);
         QDC_CHECK_LAUNCH();
     }
+    if (score.tab) {
+        sv_score_finish_kernel<<<(unsigned)n_batch, 1024, 0, s>>>(score.partials, a.n_tiles, score.sums);
+        QDC_CHECK_LAUNCH();
+    }
     return QDC_OK;
+}
+
+extern "C" int qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int64_t n_init,
+                          int64_t n_sets, const double* d_params, int n_params,
+                          const int32_t* h_prep_qubits, int n_prep, const double* h_code_table,
+                          int n_codes, double* d_matrices, void* stream) {
+    const ScoreReq none = {nullptr, nullptr, nullptr, nullptr, 0ull, 1};
+    return sv_run_impl(prog, d_state, init_lo, n_init, n_sets, d_params, n_params, h_prep_qubits, n_prep,
+                       h_code_table, n_codes, d_matrices, none, stream);
+}
+
+extern "C" int64_t qdc_sv_score_workspace_bytes(const qdc_sv_program* prog, int64_t n_sets) {
+    if (!prog || n_sets < 1) return -1;
+    const long long n_tiles = 1ll << (prog->n - prog->t);
+    return (int64_t)(8ll << prog->t) + 3 * 8 * n_sets * n_tiles;
+}
+
+extern "C" int qdc_sv_run_score(const qdc_sv_program* prog, void* d_state, int64_t n_sets, const double* d_params,
+                                int n_params, double* d_matrices, const uint64_t* d_adj, uint64_t node_mask,
+                                int keep_state, void* d_workspace, double* d_sums, void* stream) {
+    QDC_REQUIRE(prog != nullptr && d_adj && d_workspace && d_sums, "null buffer");
+    QDC_REQUIRE((((uintptr_t)d_workspace) & 7) == 0, "workspace alignment");
+    QDC_REQUIRE(prog->n <= 48 && (prog->n >= 64 || (node_mask >> prog->n) == 0), "node_mask");
+    QDC_REQUIRE(!prog->groups.empty(), "a program without gate groups has no final group to score in");
+    ScoreReq score;
+    score.tab = (uint64_t*)d_workspace;
+    score.partials = (double*)((uint8_t*)d_workspace + (8ll << prog->t));
+    score.adj = d_adj; score.sums = d_sums; score.nodes = node_mask; score.keep_state = keep_state ? 1 : 0;
+    return sv_run_impl(prog, d_state, 0, 1, n_sets, d_params, n_params, nullptr, 0, nullptr, 1, d_matrices, score, stream);
 }
 
 extern "C" int qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t flip_mask,

@@ -306,6 +306,32 @@ class B200Backend:
                                       _lib.ptr(mats), _lib.stream_ptr(stream)), "qdc_sv_run")
         return out
 
+    def run_scored(self, prog: CompiledCircuit, auto: Sequence[float], params, adj: Sequence[int], node_mask: int,
+                   scratch: Optional[torch.Tensor] = None, keep_state: bool = False, stream=None) -> torch.Tensor:
+        """The uncut cost in one pass (`qdc_sv_run_score`): simulate every parameter row and reduce
+        [sum p, sum p |x| [x independent], sum p |x|] inside the last gate group, so the final state is
+        never re-read and (keep_state=False) never written.  Returns float64 [n_sets, 3] on the device.
+        `scratch`: complex128 [n_sets, 2^n] working buffer (allocated when missing)."""
+        lib = _lib.load()
+        table = self._param_table(prog, auto, params)
+        n_sets = table.shape[0]
+        dim = 1 << prog.n_qubits
+        if scratch is None:
+            scratch = torch.empty(n_sets, dim, dtype=torch.complex128, device=self.device)
+        assert scratch.is_contiguous() and scratch.numel() >= n_sets * dim
+        mats = torch.empty(max(n_sets * prog.n_matrices * 8, 1), dtype=torch.float64, device=self.device)
+        d_adj = torch.as_tensor(np.asarray([int(a) for a in adj], dtype=np.uint64).view(np.int64), device=self.device)
+        assert d_adj.numel() >= prog.n_qubits
+        ws = torch.empty(int(lib.qdc_sv_score_workspace_bytes(prog.handle, n_sets)) // 8 + 1, dtype=torch.float64,
+                         device=self.device)
+        sums = torch.empty(n_sets, 3, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(lib.qdc_sv_run_score(prog.handle, _lib.ptr(scratch), n_sets, _lib.ptr(table), table.shape[1],
+                                            _lib.ptr(mats), _lib.ptr(d_adj), C.c_uint64(int(node_mask)),
+                                            1 if keep_state else 0, _lib.ptr(ws), _lib.ptr(sums),
+                                            _lib.stream_ptr(stream)), "qdc_sv_run_score")
+        return sums
+
     def probabilities(self, states: torch.Tensor, prog_or_flip, n_qubits: Optional[int] = None,
                       stream=None) -> torch.Tensor:
         """|amp|^2 with the flip frame undone: float64 [batch, 2^n], index = basis state."""

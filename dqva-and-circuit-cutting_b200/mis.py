@@ -73,25 +73,23 @@ def uncut_cost(circuit, backend: B200Backend, graph, params=None, param_order=No
     if table.ndim == 1:
         table = table.reshape(1, -1)
     n_sets = table.shape[0]
-    col_bits = min(n, 14)
-    tabs = _rc.build_tables(n - col_bits, col_bits, list(range(n)), _adjacency(graph, n),
-                            (1 << graph.number_of_nodes()) - 1, device=backend.device,
-                            index_flip=prog.flip_mask)
+    # the MIS reduction is fused into the last gate group (engine.run_scored / qdc_sv_run_score): the final
+    # state is scored tile by tile from shared memory, never re-read and never written back
+    adj = _adjacency(graph, n)
+    node_mask = (1 << graph.number_of_nodes()) - 1
     state_bytes = 16 << n
     if max_states is None:
         max_states = max(1, backend.max_state_bytes // state_bytes)
     chunk = min(n_sets, max_states)
-    states = torch.empty(chunk, 1 << n, dtype=torch.complex128, device=backend.device)
+    scratch = torch.empty(chunk, 1 << n, dtype=torch.complex128, device=backend.device)
     out = np.empty(n_sets)
+    pending = []
     for lo in range(0, n_sets, chunk):
         hi = min(lo + chunk, n_sets)
-        backend.run(prog, auto, table[lo:hi], out=states[:hi - lo])
-        results = [_rc.reduce_and_score(torch.view_as_real(states[s]).reshape(-1), tabs,
-                                        threshold=2.0, k=1, cand_cap=1, amplitudes=True)
-                   for s in range(hi - lo)]
-        for s, res in enumerate(results):
-            sums = res.sums.cpu().numpy()
-            out[lo + s] = -(sums[1] if masked else sums[2])
+        pending.append((lo, hi, backend.run_scored(prog, auto, table[lo:hi], adj, node_mask, scratch=scratch)))
+    for lo, hi, sums in pending:                          # one read-back at the end: the chunks queue behind each other
+        h = sums.cpu().numpy()
+        out[lo:hi] = -(h[:, 1] if masked else h[:, 2])
     return out
 
 

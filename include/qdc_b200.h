@@ -173,6 +173,23 @@ int  qdc_sv_run(const qdc_sv_program* prog, void* d_state, int64_t init_lo, int6
                 const int32_t* h_prep_qubits, int n_prep, const double* h_code_table, int n_codes,
                 double* d_matrices, void* stream);
 
+/* The uncut cost closure f(params) of solve_mis_dqva / solve_mis_qaoa (mis.py:639-665, 485-511, 315-341:
+ * simulate the statevector, then sum p(x) |x| over the outcomes) in one pass: qdc_sv_run for circuits
+ * without preparation variants, with the MIS reduction FUSED INTO THE LAST GATE GROUP -- every tile is
+ * scored from shared memory before (or, with keep_state = 0, instead of) being written back, so the final
+ * state is neither re-read (16 B / amplitude) nor, if unwanted, stored (16 B / amplitude).
+ *   d_sums[set][3] = sum p, sum p w [x independent], sum p w;  w = popcount(x & node_mask), independence
+ *   with respect to d_adj (bit i of d_adj[j] <=> edge (i, j); n_qubits device words; ancilla bits outside
+ *   node_mask are ignored, as strip_ancillas does).  Written, not accumulated; summation order fixed.
+ * d_state: [n_sets][2^n] complex128 working buffer (between groups the state lives there; its final
+ * contents are the state only when keep_state != 0).  d_workspace: qdc_sv_score_workspace_bytes(prog,
+ * n_sets) bytes, 8-byte aligned.  Launches the group kernels + a 4096-entry table kernel + one
+ * finishing kernel; allocates nothing. */
+int64_t qdc_sv_score_workspace_bytes(const qdc_sv_program* prog, int64_t n_sets);
+int  qdc_sv_run_score(const qdc_sv_program* prog, void* d_state, int64_t n_sets, const double* d_params,
+                      int n_params, double* d_matrices, const uint64_t* d_adj, uint64_t node_mask,
+                      int keep_state, void* d_workspace, double* d_sums, void* stream);
+
 /* p[b][x] = |amp_b(x)|^2, undoing the flip frame: d_probs[b * 2^n + x] (float64). */
 int  qdc_sv_probs(const void* d_state, int n_qubits, int64_t n_batch, uint64_t flip_mask,
                   double* d_probs, void* stream);

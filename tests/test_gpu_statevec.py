@@ -192,6 +192,49 @@ def test_uncut_cost_batch_matches_oracle(cuda):
         assert abs(got[s] + s_pw) < TOL and abs(got_masked[s] + s_pwok) < TOL
 
 
+@pytest.mark.parametrize("n,tile_bits", [(10, 6), (10, 12), (13, 5), (7, 3)])
+def test_run_scored_fuses_the_mis_reduction_into_the_last_group(cuda, n, tile_bits):
+    """engine.run_scored (qdc_sv_run_score): the three sums reduced inside the last gate group equal the
+    separate pass over the stored state (qdc_mis_reduce on the amplitudes) and the oracle, for several tile
+    sizes (one group / many groups, local bits scattered over the index); with keep_state the state written
+    is bit-identical to backend.run's, and the sums do not depend on whether it is written."""
+    import networkx as nx
+    import torch
+    from oracle import mis_oracle as mo
+    from qdc_b200 import recombine as rc
+    from qdc_b200.ansatz import dqv_ansatz
+    from qdc_b200.circuit import Parameter
+    G = nx.gnm_random_graph(n, 2 * n, seed=n)
+    syms = [Parameter(f"var_{i}") for i in range(n + 1)]
+    init = "".join("1" if i == 2 else "0" for i in range(n))
+    circ = dqv_ansatz.gen_dqva(G, P=1, params=syms, init_state=init, mixer_order=list(range(n)))
+    used = circ.parameters
+    table = np.random.default_rng(n).uniform(0, 2 * np.pi, (3, len(used)))
+    be = _backend(cuda, tile_bits=tile_bits)
+    prog, auto = be.compile(circ, param_order=used)
+    nq = prog.n_qubits
+    adj = [int(a) for a in mo.adjacency_masks(G, n)] + [0] * (nq - n)
+    node_mask = (1 << n) - 1
+    states = be.run(prog, auto, table)
+    scratch = torch.zeros_like(states)
+    sums_kept = be.run_scored(prog, auto, table, adj, node_mask, scratch=scratch, keep_state=True)
+    assert torch.equal(scratch, states)
+    sums = be.run_scored(prog, auto, table, adj, node_mask).cpu().numpy()
+    assert np.array_equal(sums, sums_kept.cpu().numpy())
+    cb = min(nq, 14)
+    tabs = rc.build_tables(nq - cb, cb, list(range(nq)), adj, node_mask, device=cuda, index_flip=prog.flip_mask)
+    mo_adj = mo.adjacency_masks(G, n)
+    for s in range(3):
+        ref = rc.reduce_and_score(torch.view_as_real(states[s]).reshape(-1), tabs, threshold=2.0, k=1, cand_cap=1,
+                                  amplitudes=True).sums.cpu().numpy()
+        assert np.abs(sums[s] - ref).max() < 1e-12
+        bound = circ.bind_parameters(dict(zip(used, table[s])))
+        p = sv.probabilities(sv.simulate(nq, bound.to_instructions()))
+        _, s_pw = mo.score_array(p, n, nq - n, mo_adj, masked=False)
+        _, s_pwok = mo.score_array(p, n, nq - n, mo_adj, masked=True)
+        assert abs(sums[s][0] - 1.0) < TOL and abs(sums[s][2] - s_pw) < TOL and abs(sums[s][1] - s_pwok) < TOL
+
+
 def test_uncut_cost_on_a_tiny_graph(cuda):
     """Graphs of 3-4 nodes give fewer than 64 table columns, where qdc_mis_reduce takes its scalar
     path: complex128 amplitudes must be scored as |amp|^2 there as well (they were once read as
