@@ -464,3 +464,38 @@ def test_int8_flagged_list_overflow_is_reported(cuda):
     assert [x for x, _ in got["top"]] == [x for x, _ in ref["top"]]
     none = rc.contract_and_score(A_d, B_d, tabs, threshold=float("inf"), k=1, method="i8", slices=4)
     assert none.get()["n_candidates"] == 0 and float(none.block[9:10].view(torch.int64).item()) == 0
+
+
+@pytest.mark.parametrize("slices", [3, 4, 5])
+def test_int8_cta_pair_equals_single_cta_kernel(cuda, slices, monkeypatch):
+    """The CTA-pair form of the contraction (cta_group::2: 256-row units, the streamed tile split between two
+    CTAs, column table staged in shared memory) against the single-CTA kernel on the same prepared operands:
+    integer arithmetic in another tiling, so the masked sum, the candidates and the top-k are bit-identical.
+    Rows are ragged (the last 256-row unit has only its first half, and that half is partial)."""
+    import torch
+    from qdc_b200 import recombine as rc
+    rb, cb, kdim = 11, 9, 256
+    rng = np.random.default_rng(40 + slices)
+    M, N = (1 << rb) - 200, 1 << cb                        # 1848 rows: 14 full units + 56 rows of a 15th
+    A = rng.random((M, kdim)) * 10.0 ** rng.uniform(-3, 0, (M, 1))
+    Bt = rng.random((N, kdim)) * 10.0 ** rng.uniform(-3, 0, (N, 1))
+    A[rng.choice(M, 5, replace=False)] *= 300.0
+    Bt[rng.choice(N, 5, replace=False)] *= 300.0
+    G = __import__("networkx").gnm_random_graph(rb + cb, 25, seed=9)
+    adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
+    full = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
+    tabs = rc.MisTables(rb, cb, full.row_x[:M].contiguous(), full.row_forb[:M].contiguous(), full.row_wok[:M].contiguous(),
+                        full.col_x, full.col_wok, full.bitpos, full.node_mask)
+    A_d, B_d = torch.as_tensor(A, device=cuda), torch.as_tensor(Bt, device=cuda)
+    want = A @ Bt.T
+    want /= want.sum()
+    thr = float(np.sort(want.reshape(-1))[-12])
+    out = {}
+    for pair in ("1", "0"):
+        monkeypatch.setenv("QDC_I8_PAIR", pair)
+        out[pair] = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=8, method="i8", slices=slices).get()
+    assert out["1"] == out["0"]
+    ref = rc.contract_and_score(A_d, B_d, tabs, threshold=thr, k=8).get()
+    assert out["1"]["n_candidates"] == ref["n_candidates"] == 11
+    if slices >= 4:
+        assert [x for x, _ in out["1"]["top"]] == [x for x, _ in ref["top"]]
