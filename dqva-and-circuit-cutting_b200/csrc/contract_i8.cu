@@ -1049,11 +1049,12 @@ int i8_tile_n(int n_slices, int kd, int store) {
 }
 
 // one instantiation for one slice count: geometry, work split, launch
-int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
+int launch_for(I8Args a, int n_slices, int store, cudaStream_t s, bool allow_pair = true) {
+    const I8Args a_in = a;                     // (for the fall-back below: the geometry fields are rewritten here)
     const int kd = a.kdim;
     const int TN = i8_tile_n(n_slices, kd, store ? (a.out32 ? 2 : 1) : 0);
     // CTA pairs (cta_group::2): the scoring-only kernel at 128 columns and kdim 256, at least two 256-row units
-    bool pair = !store && TN == 128 && kd == 256 && n_slices >= 3 && n_slices <= 5 && a.n_rows > 2 * TM;
+    bool pair = allow_pair && !store && TN == 128 && kd == 256 && n_slices >= 3 && n_slices <= 5 && a.n_rows > 2 * TM;
     if (const char* m = getenv("QDC_I8_PAIR")) pair = pair && atoi(m) != 0;
     const long long n_blocks = (a.n_rows + TM - 1) / TM;
     const long long n_rb = pair ? (n_blocks + 1) / 2 : n_blocks, n_cb = (a.n_cols + TN - 1) / TN;
@@ -1089,11 +1090,17 @@ int launch_for(I8Args a, int n_slices, int store, cudaStream_t s) {
     QDC_REQUIRE(n_items < (1ll << 31), "too many work items");
     const int grid = (int)(n_items < sms ? n_items : sms) * (pair ? 2 : 1);
     if (pair) {
+        int rc = QDC_ERR_UNSUPPORTED;
         switch (n_slices) {
-            case 3: return launch_i8_pair<3, 128>(a, grid, smem, s);
-            case 4: return launch_i8_pair<4, 128>(a, grid, smem, s);
-            case 5: return launch_i8_pair<5, 128>(a, grid, smem, s);
+            case 3: rc = launch_i8_pair<3, 128>(a, grid, smem, s); break;
+            case 4: rc = launch_i8_pair<4, 128>(a, grid, smem, s); break;
+            case 5: rc = launch_i8_pair<5, 128>(a, grid, smem, s); break;
         }
+        if (rc == QDC_OK) return rc;
+        // a cluster launch the device configuration refuses (no pair of SMs free for a 2-CTA cluster, e.g. under a
+        // partitioned GPU): the single-CTA kernel computes the same numbers
+        (void)cudaGetLastError();
+        return launch_for(a_in, n_slices, store, s, false);
     }
 #define QDC_I8_CASE(SS, TT)                                                                         \
     if (n_slices == SS && TN == TT && !(TT == 96 && store && a.out32))                               \
