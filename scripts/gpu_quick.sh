@@ -1,2 +1,3 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_gpu_contract_score.py -x -q -m gpu -k "cta_pair" 2>&1 | tail -15
+mkdir -p gpurun_out
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:sv_meas_tensor -s 2 -c 2 -o gpurun_out/r2_meas_tensor python scripts/probe_variant_sims.py > gpurun_out/ncu_mt.log 2>&1; echo rc=$?
