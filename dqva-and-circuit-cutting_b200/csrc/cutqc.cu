@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) merge_kernel(const double* __restrict__ i
 // low bits are resolved through two small tables, so an element costs one shared-memory read, an
 // OR and an add.  Accumulation order is fixed (deterministic).  Algorithmic bytes: the input once,
 // the output once.
-constexpr int TILE_BITS = 12, MARG_THREADS = 256, MARG_ACC = (1 << TILE_BITS) / MARG_THREADS;
+constexpr int TILE_BITS = 12, MARG_THREADS = 256, MARG_ACC_MAX = (1 << TILE_BITS) / MARG_THREADS;
 
 struct MargArgs {
     const void* in;
@@ -130,10 +130,17 @@ struct MargArgs {
     uint64_t keep_mask, sum_mask, fixed_val;
 };
 
-template <typename T, bool LOOP>
+// Round 2 (ncu: the kernel was issue-bound at 62 / 100 thread-instructions per element, profiles/r2_marginal_ncu_full.csv):
+// ACC = accumulator slots a thread really needs (1, 4 or 16: the 16 predicated slots of which 1-4 were live cost a
+// third of the instructions), the high kept bits of a work item are deposited through two 256-entry tables instead
+// of a bit loop per item, the high summed bits advance by the carry trick, and the sign of a loaded element is a
+// per-thread constant times a per-iteration one.
+template <typename T, bool LOOP, int ACC>
 __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(const MargArgs a) {
     __shared__ double tile[1 << TILE_BITS];
-    __shared__ uint16_t lut_a[1 << TILE_BITS], lut_m[1 << TILE_BITS];
+    // the two low-bit tables share one array: 2^n_klo + 2^n_slo <= 2^12 + 1 entries (n_klo + n_slo <= 12)
+    __shared__ uint16_t lut_pool[(1 << TILE_BITS) + 256];
+    __shared__ uint64_t dep_lo[256], dep_hi[256];
     constexpr int VEC = 16 / (int)sizeof(T), VEC_BITS = VEC == 4 ? 2 : 1;
     const int L = a.tile_bits, tid = threadIdx.x;
     const uint64_t low = (1ull << L) - 1ull;
@@ -146,8 +153,14 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
     const uint64_t keep_hi = a.keep_mask >> L, sum_hi = a.sum_mask >> L, fixed_hi = a.fixed_val >> L;
     const int n_klo = __popcll(keep_lo), n_slo = __popcll(sum_lo), n_khi = __popcll(keep_hi), n_shi = __popcll(sum_hi);
     const int n_keep = n_klo + n_khi;
+    uint16_t* lut_a = lut_pool;
+    uint16_t* lut_m = lut_pool + (1 << n_klo);
     for (int i = tid; i < (1 << n_klo); i += MARG_THREADS) lut_a[i] = (uint16_t)(deposit_bits((uint64_t)i, keep_lo) | fixed_lo);
     for (int i = tid; i < (1 << n_slo); i += MARG_THREADS) lut_m[i] = (uint16_t)deposit_bits((uint64_t)i, sum_lo);
+    for (int i = tid; i < 256; i += MARG_THREADS) {
+        dep_lo[i] = deposit_bits((uint64_t)i, keep_hi);
+        dep_hi[i] = deposit_bits((uint64_t)i << 8, keep_hi);
+    }
     // Work split of the low bits: with 2^n_klo >= 256 outputs per tile a thread owns outputs
     // tid, tid + 256, ... and walks all 2^n_slo summed states; with fewer outputs P = 256 / 2^n_klo
     // adjacent lanes share one output and split the summed states (their partial sums meet in a
@@ -159,25 +172,30 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
     const int my_part = tid & (P - 1), my_out0 = tid >> p_bits;     // outputs my_out0 + j * (256 / P)
     const int out_stride = MARG_THREADS >> p_bits;
     const int m_per = (1 << n_slo) >> p_bits, m0 = my_part * m_per;
-    uint32_t la[MARG_ACC];
+    uint32_t la[ACC];
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < MARG_ACC; ++j) la[j] = lut_a[(my_out0 + j * out_stride) & (n_out - 1)];
+    for (int j = 0; j < ACC; ++j) la[j] = lut_a[(my_out0 + j * out_stride) & (n_out - 1)];
     // persistent CTAs: work item = (vector, high kept bits); the tables above are built once
     const long long n_work = a.n_vec << n_khi;
     long long w = blockIdx.x;
     do {
     const long long v = w >> n_khi;
     const uint64_t a_hi = (uint64_t)w & ((1ull << n_khi) - 1ull);
-    const uint64_t x_keep_hi = deposit_bits(a_hi, keep_hi) | fixed_hi;
+    const uint64_t x_keep_hi = (n_khi <= 16 ? (dep_lo[a_hi & 255] | dep_hi[(a_hi >> 8) & 255]) : deposit_bits(a_hi, keep_hi)) | fixed_hi;
     const uint64_t sign = a.sign_masks ? a.sign_masks[v] : 0ull;
     const uint32_t sign_lo = (uint32_t)(sign & low);
     const T* src = reinterpret_cast<const T*>(a.in) + (v << a.d);
-    double acc[MARG_ACC];
+    double acc[ACC];
 #pragma unroll
-    for (int j = 0; j < MARG_ACC; ++j) acc[j] = 0.0;
-    for (long long m_hi = 0; m_hi < (1ll << n_shi); ++m_hi) {
-        const uint64_t x_hi = x_keep_hi | deposit_bits((uint64_t)m_hi, sum_hi);
+    for (int j = 0; j < ACC; ++j) acc[j] = 0.0;
+    // sign of element i + k of a tile = parity((i + k) & sign_lo): i = tid VEC + it VEC 256, the two parts share no bits
+    double sgn_k[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) sgn_k[k] = (__popc((uint32_t)(tid * VEC + k) & sign_lo) & 1) ? -1.0 : 1.0;
+    uint64_t x_sum_hi = 0;                                          // deposit of m_hi into sum_hi, advanced by the carry trick
+    for (long long m_hi = 0; m_hi < (1ll << n_shi); ++m_hi, x_sum_hi = ((x_sum_hi | ~sum_hi) + 1ull) & sum_hi) {
+        const uint64_t x_hi = x_keep_hi | x_sum_hi;
         const double hi_sign = (__popcll((long long)((x_hi << L) & sign)) & 1) ? -1.0 : 1.0;
         const T* t_src = src + (x_hi << L);
         if ((1 << L) >= VEC * MARG_THREADS) {
@@ -185,9 +203,9 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
                 T e[VEC];
                 *reinterpret_cast<int4*>(e) = __ldcs(reinterpret_cast<const int4*>(t_src + i));
                 double f[VEC];
+                const double it_sign = (__popc((uint32_t)(i - tid * VEC) & sign_lo) & 1) ? -hi_sign : hi_sign;
 #pragma unroll
-                for (int k = 0; k < VEC; ++k)
-                    f[k] = (__popc((uint32_t)(i + k) & sign_lo) & 1) ? -hi_sign * (double)e[k] : hi_sign * (double)e[k];
+                for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
                 if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
                 else if (tz == 1) {
 #pragma unroll
@@ -208,14 +226,14 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
         for (int m = m0; m < m0 + m_per; ++m) {
             const uint32_t lm = lut_m[m];
 #pragma unroll
-            for (int j = 0; j < MARG_ACC; ++j)
+            for (int j = 0; j < ACC; ++j)
                 if (my_out0 + j * out_stride < n_out) acc[j] += tile[la[j] | lm];
         }
         __syncthreads();
     }
     double* dst = a.out + (v << n_keep) + ((long long)a_hi << n_klo);
 #pragma unroll
-    for (int j = 0; j < MARG_ACC; ++j) {
+    for (int j = 0; j < ACC; ++j) {
         double r = acc[j];
         for (int o = 1; o < P; o <<= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
         if (my_part == 0 && my_out0 + j * out_stride < n_out) dst[my_out0 + j * out_stride] = r;
@@ -240,10 +258,26 @@ bool launch_marginal(const void* in, double* out, const uint64_t* sign_masks, lo
     const int n_shi = __builtin_popcountll(sum_mask >> L);
     MargArgs a = {in, out, sign_masks, n_vec, d, L, keep_mask, sum_mask, fixed_val};
     const long long resident = 4ll * qdc_sm_count();
-    if ((n_shi == 0 && work > resident) || work >= (1ll << 31))
-        marginal_kernel<T, true><<<(unsigned)resident, MARG_THREADS, 0, s>>>(a);
-    else
-        marginal_kernel<T, false><<<(unsigned)work, MARG_THREADS, 0, s>>>(a);
+    // accumulator slots a thread needs (the kernel's own work split, restated): outputs per tile over the threads
+    // that do not share an output
+    int acc;
+    {
+        const int vec_bits = sizeof(T) == 4 ? 2 : 1;
+        const uint64_t low = (1ull << L) - 1ull;
+        int tz = 0;
+        while (tz < vec_bits && tz < L && ((sum_mask >> tz) & 1ull)) ++tz;
+        const int n_klo = __builtin_popcountll((keep_mask & low) >> tz), n_slo = __builtin_popcountll((sum_mask & low) >> tz);
+        int p_bits = 0;
+        while (((1 << n_klo) << p_bits) < MARG_THREADS && p_bits < 5 && p_bits < n_slo) ++p_bits;
+        const int need = ((1 << n_klo) << p_bits) / MARG_THREADS;
+        acc = need <= 1 ? 1 : (need <= 4 ? 4 : MARG_ACC_MAX);
+    }
+    const bool loop = (n_shi == 0 && work > resident) || work >= (1ll << 31);
+    const unsigned grid = loop ? (unsigned)resident : (unsigned)work;
+#define QDC_MARG(LOOPV, ACCV) marginal_kernel<T, LOOPV, ACCV><<<grid, MARG_THREADS, 0, s>>>(a)
+    if (loop) { if (acc == 1) QDC_MARG(true, 1); else if (acc == 4) QDC_MARG(true, 4); else QDC_MARG(true, MARG_ACC_MAX); }
+    else { if (acc == 1) QDC_MARG(false, 1); else if (acc == 4) QDC_MARG(false, 4); else QDC_MARG(false, MARG_ACC_MAX); }
+#undef QDC_MARG
     return true;
 }
 

@@ -1,3 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:sv_meas_tensor -s 2 -c 2 -o gpurun_out/r2_meas_tensor python scripts/probe_variant_sims.py > gpurun_out/ncu_mt.log 2>&1; echo rc=$?
+timeout 1200 python -m pytest tests/test_gpu_cutqc.py tests/test_gpu_cutqc_pipeline.py -x -q -m gpu 2>&1 | tail -4
+timeout 600 python scripts/time_cutqc.py 2>&1 | grep -E "measure|merge|collapse" | tee gpurun_out/time_marginal.log
