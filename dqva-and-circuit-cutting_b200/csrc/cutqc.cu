@@ -199,20 +199,33 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
         const double hi_sign = (__popcll((long long)((x_hi << L) & sign)) & 1) ? -1.0 : 1.0;
         const T* t_src = src + (x_hi << L);
         if ((1 << L) >= VEC * MARG_THREADS) {
-            for (int i = tid * VEC; i < (1 << L); i += VEC * MARG_THREADS) {
-                T e[VEC];
-                *reinterpret_cast<int4*>(e) = __ldcs(reinterpret_cast<const int4*>(t_src + i));
-                double f[VEC];
-                const double it_sign = (__popc((uint32_t)(i - tid * VEC) & sign_lo) & 1) ? -hi_sign : hi_sign;
+            // four 16-byte loads in flight per thread before the first one is consumed (one at a time left the kernel
+            // waiting on memory: 64 % of its stall samples, profiles/r2_marginal_ncu_full.csv second capture)
+            constexpr int U = 4;
+            for (int i0 = tid * VEC; i0 < (1 << L); i0 += U * VEC * MARG_THREADS) {
+                int4 raw[U];
 #pragma unroll
-                for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
-                if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
-                else if (tz == 1) {
+                for (int u = 0; u < U; ++u)
+                    if (i0 + u * VEC * MARG_THREADS < (1 << L))
+                        raw[u] = __ldcs(reinterpret_cast<const int4*>(t_src + i0 + u * VEC * MARG_THREADS));
 #pragma unroll
-                    for (int k = 0; k < VEC; k += 2) tile[(i + k) >> 1] = f[k] + f[k + 1];
-                } else {
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * VEC * MARG_THREADS;
+                    if (i >= (1 << L)) break;
+                    T e[VEC];
+                    *reinterpret_cast<int4*>(e) = raw[u];
+                    double f[VEC];
+                    const double it_sign = (__popc((uint32_t)(i - tid * VEC) & sign_lo) & 1) ? -hi_sign : hi_sign;
 #pragma unroll
-                    for (int k = 0; k < VEC; ++k) tile[i + k] = f[k];
+                    for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
+                    if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
+                    else if (tz == 1) {
+#pragma unroll
+                        for (int k = 0; k < VEC; k += 2) tile[(i + k) >> 1] = f[k] + f[k + 1];
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < VEC; ++k) tile[i + k] = f[k];
+                    }
                 }
             }
         } else {                                                   // small vectors: tz = 0 path only
