@@ -179,6 +179,18 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
     // persistent CTAs: work item = (vector, high kept bits); the tables above are built once
     const long long n_work = a.n_vec << n_khi;
     long long w = blockIdx.x;
+    // the next tile's loads are issued right after this tile has been written to shared memory, so they are in
+    // flight during the table phase (U 16-byte loads per thread = one whole tile)
+    constexpr int U = (1 << TILE_BITS) / (VEC * MARG_THREADS);
+    int4 raw[U];
+    bool pref = false;
+    const bool vec_path = (1 << L) >= VEC * MARG_THREADS;
+    auto load_tile = [&](const T* p) {
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (tid * VEC + u * VEC * MARG_THREADS < (1 << L))
+                raw[u] = __ldcs(reinterpret_cast<const int4*>(p + tid * VEC + u * VEC * MARG_THREADS));
+    };
     do {
     const long long v = w >> n_khi;
     const uint64_t a_hi = (uint64_t)w & ((1ull << n_khi) - 1ull);
@@ -199,33 +211,24 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
         const double hi_sign = (__popcll((long long)((x_hi << L) & sign)) & 1) ? -1.0 : 1.0;
         const T* t_src = src + (x_hi << L);
         if ((1 << L) >= VEC * MARG_THREADS) {
-            // four 16-byte loads in flight per thread before the first one is consumed (one at a time left the kernel
-            // waiting on memory: 64 % of its stall samples, profiles/r2_marginal_ncu_full.csv second capture)
-            constexpr int U = 4;
-            for (int i0 = tid * VEC; i0 < (1 << L); i0 += U * VEC * MARG_THREADS) {
-                int4 raw[U];
+            if (!pref) load_tile(t_src);
 #pragma unroll
-                for (int u = 0; u < U; ++u)
-                    if (i0 + u * VEC * MARG_THREADS < (1 << L))
-                        raw[u] = __ldcs(reinterpret_cast<const int4*>(t_src + i0 + u * VEC * MARG_THREADS));
+            for (int u = 0; u < U; ++u) {
+                const int i = tid * VEC + u * VEC * MARG_THREADS;
+                if (i >= (1 << L)) break;
+                T e[VEC];
+                *reinterpret_cast<int4*>(e) = raw[u];
+                double f[VEC];
+                const double it_sign = (__popc((uint32_t)(i - tid * VEC) & sign_lo) & 1) ? -hi_sign : hi_sign;
 #pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = i0 + u * VEC * MARG_THREADS;
-                    if (i >= (1 << L)) break;
-                    T e[VEC];
-                    *reinterpret_cast<int4*>(e) = raw[u];
-                    double f[VEC];
-                    const double it_sign = (__popc((uint32_t)(i - tid * VEC) & sign_lo) & 1) ? -hi_sign : hi_sign;
+                for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
+                if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
+                else if (tz == 1) {
 #pragma unroll
-                    for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
-                    if (tz == 2 && VEC == 4) tile[i >> 2] = (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
-                    else if (tz == 1) {
+                    for (int k = 0; k < VEC; k += 2) tile[(i + k) >> 1] = f[k] + f[k + 1];
+                } else {
 #pragma unroll
-                        for (int k = 0; k < VEC; k += 2) tile[(i + k) >> 1] = f[k] + f[k + 1];
-                    } else {
-#pragma unroll
-                        for (int k = 0; k < VEC; ++k) tile[i + k] = f[k];
-                    }
+                    for (int k = 0; k < VEC; ++k) tile[i + k] = f[k];
                 }
             }
         } else {                                                   // small vectors: tz = 0 path only
@@ -236,6 +239,20 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
             }
         }
         __syncthreads();
+        pref = false;
+        if (vec_path) {                                            // (uniform over the CTA)
+            if (m_hi + 1 < (1ll << n_shi)) {
+                const uint64_t nx = ((x_sum_hi | ~sum_hi) + 1ull) & sum_hi;
+                load_tile(src + ((x_keep_hi | nx) << L));
+                pref = true;
+            } else if (LOOP && w + gridDim.x < n_work) {
+                const long long wn = w + gridDim.x;
+                const uint64_t an = (uint64_t)wn & ((1ull << n_khi) - 1ull);
+                const uint64_t xk = (n_khi <= 16 ? (dep_lo[an & 255] | dep_hi[(an >> 8) & 255]) : deposit_bits(an, keep_hi)) | fixed_hi;
+                load_tile(reinterpret_cast<const T*>(a.in) + ((wn >> n_khi) << a.d) + (xk << L));   // (its m_hi = 0: no high summed bits set)
+                pref = true;
+            }
+        }
         for (int m = m0; m < m0 + m_per; ++m) {
             const uint32_t lm = lut_m[m];
 #pragma unroll
