@@ -216,10 +216,15 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
         if (tid == 0) sv_mbar_init(&sh_bar, 1);
         __syncthreads();
         if (tid == 0) sv_mbar_expect_tx(&sh_bar, T * 16u);
+        // (every thread issues its own copy: a few lanes issuing them all in a loop was measured 1.5x slower for the
+        // whole kernel -- the issue of a bulk copy is slow, its parallelism across threads is what hides it)
         for (uint32_t j = tid; j < n_chunks; j += nthr)
             sv_bulk_g2s(tile + ((size_t)j << p0), st + (expand_runs((uint64_t)j << p0, a.n_runs, a.run_pos, a.run_len) | base),
                         chunk_bytes, &sh_bar);
-        sv_mbar_wait(&sh_bar, 0);
+        // only warp 0 polls the barrier; the others sleep at the __syncthreads that follows (256 spinning threads were
+        // 13 % of the issued instructions)
+        if (tid < 32) sv_mbar_wait(&sh_bar, 0);
+        __syncthreads();
     } else {
         // all loads of a batch are issued before the first one is consumed (8 in flight per thread)
         constexpr int U = 8;
