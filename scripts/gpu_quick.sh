@@ -1,3 +1,2 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 1200 python scripts/time_configs.py 2>&1 | tail -25 | tee gpurun_out/time_configs.log
+timeout 900 python -m pytest tests/test_gpu_contract_score.py -x -q -m gpu -k "row_slabs" 2>&1 | tail -12

@@ -220,14 +220,14 @@ def test_int8_sliced_contraction_per_output_bound(cuda, slices):
         assert abs(s32[key] - s[key]) <= 2 * bound.sum() * (rb + cb) + 1e-12 * abs(s[key])
 
 
-def test_int8_contraction_row_slabs_and_given_norm(cuda):
+@pytest.mark.parametrize("rb,cb,kdim,slices", [(9, 8, 64, 6), (11, 8, 256, 5)])     # second: slabs wide enough for the CTA-pair kernel
+def test_int8_contraction_row_slabs_and_given_norm(cuda, rb, cb, kdim, slices):
     """The sharded layout of bench.py's e2e leg on one GPU: every 'rank' holds only its rows of the
     row operand and divides by a norm computed from all slabs (dist.sharded_norm, world size 1 per
     call here, so the column sums are added by hand); slab sums add up to the full evaluation and
     the union of the slab candidates is the full candidate set."""
     import torch
     from qdc_b200 import recombine as rc, dist as qdist
-    rb, cb, kdim = 9, 8, 64
     rng = np.random.default_rng(11)
     M, N = 1 << rb, 1 << cb
     A = torch.as_tensor(rng.random((M, kdim)) * 10.0 ** rng.uniform(-4, 0, (M, 1)), device=cuda)
@@ -236,7 +236,7 @@ def test_int8_contraction_row_slabs_and_given_norm(cuda):
     adj = [sum(1 << int(v) for v in G.neighbors(i)) for i in range(rb + cb)]
     tabs = rc.build_tables(rb, cb, list(range(rb + cb)), adj, (1 << (rb + cb)) - 1, device=cuda)
     scale, thr = 0.125, 2e-5
-    full = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=6).get()
+    full = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=slices).get()
     norm = scale * torch.dot(A.sum(0), Bt.sum(0)).reshape(1)
     assert abs(float(qdist.sharded_norm(A, Bt, scale)) - float(norm)) < 1e-12 * float(norm)
     tot = {"sum_p": 0.0, "sum_pw": 0.0, "sum_pw_indset": 0.0}
@@ -246,9 +246,9 @@ def test_int8_contraction_row_slabs_and_given_norm(cuda):
                                  tabs.row_wok[lo:lo + cnt].contiguous(), tabs.col_x, tabs.col_wok, tabs.bitpos,
                                  tabs.node_mask)
         part = rc.contract_and_score(A[lo:lo + cnt].contiguous(), Bt, slab_tabs, scale=scale, threshold=thr, k=8,
-                                     method="i8", slices=6, norm=norm).get()
+                                     method="i8", slices=slices, norm=norm).get()
         # the same slab addressed inside the full operand (row_lo / n_rows form) must agree exactly
-        part2 = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=6,
+        part2 = rc.contract_and_score(A, Bt, tabs, scale=scale, threshold=thr, k=8, method="i8", slices=slices,
                                       row_lo=lo, n_rows=cnt).get()
         # (the given norm and the library's own differ in the last bit)
         assert abs(part["sum_pw_indset"] - part2["sum_pw_indset"]) < 1e-13
