@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
         __syncthreads();
         for (int i = 0; i < n_chunk;) {
             const SvOp& op = sh_ops[i];
-            if ((base & op.gmask) != op.gval) { ++i; continue; }          // uniform over the CTA
+            if (!(op.kind == 1 && op.diag_run >= 1) && (base & op.gmask) != op.gval) { ++i; continue; }   // uniform over the CTA (a run checks per op)
             const double* m = sh_mats[i];
             if (op.kind == 0) {
                 const double2 m00 = make_double2(m[0], m[1]), m01 = make_double2(m[2], m[3]);
@@ -285,7 +285,8 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
                 }
                 ++i;
             } else if (op.diag_run >= 1) {
-                // joint pass over a run of uncontrolled diagonal gates: the phase of tile index l
+                // joint pass over a run of diagonal gates that depend on at most ONE tile-local bit each (uncontrolled,
+                // or one control with control and target not both in the tile): the phase of tile index l
                 // factors into a table over its low bits times a table over its high bits (the
                 // latter also carries the constant factor of the gates on non-local qubits)
                 const int run = op.diag_run;
@@ -298,8 +299,17 @@ __global__ void __launch_bounds__(512) sv_group_kernel(const GroupArgs a) {
                     for (int k = 0; k < run; ++k) {
                         const SvOp& o = sh_ops[i + k];
                         const double* mk = sh_mats[i + k];
+                        if ((base & o.gmask) != o.gval) continue;          // a control outside the tile that is not satisfied
                         int bit = -1;
-                        if (o.tbit < 0) { if (hi) bit = (int)((base >> o.gtarget) & 1ull); }
+                        if (o.lmask) {
+                            // one control inside the tile and the target outside (the compiler admits no other
+                            // controlled gate to a run): a 1-qubit diagonal diag(1, d) or diag(d, 1) on the control bit
+                            const int cb = __ffs((int)o.lmask) - 1;
+                            int cbit = -1;
+                            if (!hi && cb < h) cbit = (idx >> cb) & 1;
+                            else if (hi && cb >= h) cbit = (idx >> (cb - h)) & 1;
+                            if (cbit >= 0 && cbit == (int)((o.lval >> cb) & 1u)) bit = (int)((base >> o.gtarget) & 1ull);
+                        } else if (o.tbit < 0) { if (hi) bit = (int)((base >> o.gtarget) & 1ull); }
                         else if (!hi && o.tbit < h) bit = (idx >> o.tbit) & 1;
                         else if (hi && o.tbit >= h) bit = (idx >> (o.tbit - h)) & 1;
                         if (bit >= 0) f = cmul(f, bit ? make_double2(mk[6], mk[7]) : make_double2(mk[0], mk[1]));
@@ -1002,6 +1012,24 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
                     fused = true;
                 }
             }
+            // cx(a -> b) . D(b) . cx(a -> b) with D diagonal (the ZZ rotations of QAOA+'s phase separator,
+            // ansatz/qaoa_plus.py:20-24) is diagonal as a whole: D on b where the cx is inactive, X D X where it is
+            // active.  Two controlled diagonal gates instead of two non-diagonal ones + one: diagonal gates need no
+            // tile locality, so the phase separator stops dictating the grouping.
+            if (!fused && a.kind == QDC_G_X && __builtin_popcountll(a.cmask) == 1 && i + 2 < lg.size()) {
+                const LGate& d = lg[i + 1];
+                const LGate& c2 = lg[i + 2];
+                if (d.diag && d.cmask == 0 && d.target == a.target && c2.kind == QDC_G_X && c2.target == a.target &&
+                    c2.cmask == a.cmask && c2.cval == a.cval) {
+                    LGate g0 = d, g1 = d;
+                    g0.cmask = a.cmask; g0.cval = a.cval ^ a.cmask;        // control at the value that leaves the cx inactive
+                    g1.cmask = a.cmask; g1.cval = a.cval; g1.conj ^= 1;    // active: X D X
+                    fg.push_back(g0);
+                    fg.push_back(g1);
+                    i += 3;
+                    fused = true;
+                }
+            }
             if (!fused) {
                 fg.push_back(a);
                 if (!a.diag) zero &= ~(1ull << a.target);
@@ -1055,6 +1083,27 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
             q = e;
         }
         auto local_bit = [&](int q) { return __builtin_popcountll(L & ((1ull << q) - 1ull)); };
+        // Diagonal gates commute with each other: inside every block of consecutive diagonal gates those that can
+        // share a table pass (they depend on at most one tile-local bit: uncontrolled, or one control with control
+        // and target not both local) are moved behind the others, so that they form long runs (QAOA+'s phase
+        // separator: 180 diagonal gates in one group become ~15 separate passes + 6 table passes instead of 135).
+        auto tabled = [&](const LGate& g) {
+            if (!g.diag) return false;
+            const int nc = __builtin_popcountll(g.cmask);
+            if (nc == 0) return true;
+            if (nc > 1) return false;
+            return !(((L >> g.target) & 1ull) && (L & g.cmask));
+        };
+        {
+            std::vector<int>& gg = group_gates[gidx];
+            for (size_t b = 0; b < gg.size();) {
+                if (!fg[gg[b]].diag) { ++b; continue; }
+                size_t e = b;
+                while (e < gg.size() && fg[gg[e]].diag) ++e;
+                std::stable_partition(gg.begin() + b, gg.begin() + e, [&](int gi) { return !tabled(fg[gi]); });
+                b = e;
+            }
+        }
         for (int gi : group_gates[gidx]) {
             const LGate& g = fg[gi];
             SvOp op;
@@ -1101,12 +1150,16 @@ extern "C" int qdc_sv_compile(int n_qubits, const qdc_gate* gates, int n_gates, 
         // runs of uncontrolled diagonal ops (they commute with each other: one joint pass)
         for (int i = gr.first_op; i < gr.first_op + gr.n_ops;) {
             SvOp& o = prog->ops[i];
-            if (o.kind == 1 && o.lmask == 0 && o.gmask == 0) {
+            auto in_run = [&](const SvOp& x) {
+                if (x.kind != 1) return false;
+                const int nc = __builtin_popcount(x.lmask) + __builtin_popcountll(x.gmask);
+                return nc == 0 || (nc == 1 && !(x.lmask != 0 && x.tbit >= 0));
+            };
+            if (in_run(o)) {
                 int e = i;
                 // a run must not straddle a staging chunk of the kernel (OPS_CHUNK ops from first_op)
                 const int chunk_end = gr.first_op + ((i - gr.first_op) / OPS_CHUNK + 1) * OPS_CHUNK;
-                while (e < gr.first_op + gr.n_ops && e < chunk_end && e - i < MAX_DIAG_RUN &&
-                       prog->ops[e].kind == 1 && prog->ops[e].lmask == 0 && prog->ops[e].gmask == 0) ++e;
+                while (e < gr.first_op + gr.n_ops && e < chunk_end && e - i < MAX_DIAG_RUN && in_run(prog->ops[e])) ++e;
                 o.diag_run = (uint8_t)(e - i);
                 i = e;
             } else {

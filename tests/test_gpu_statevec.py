@@ -329,3 +329,36 @@ def test_qaoa_plus_cost_batch_matches_oracle(cuda):
         p = sv.probabilities(sv.simulate(n, bound.to_instructions()))
         counts = {format(x, f"0{n}b"): p[x] for x in range(1 << n)}
         assert abs(got[s] + mo.qaoa_plus_expectation(counts, G, Lambda)) < TOL
+
+
+@pytest.mark.parametrize("n,tile_bits,coalesce", [(9, 3, 1), (10, 5, 2), (11, 7, 3), (12, 8, 2), (13, 12, 5)])
+def test_controlled_diagonal_runs_match_oracle(cuda, n, tile_bits, coalesce):
+    """Diagonal gates with one control join the table pass of a diagonal run whenever control and target are not
+    both tile-local (csrc/statevec.cu: the control bit then selects diag(1, d) / diag(d, 1) in the low or high
+    table, a control outside the tile is a per-tile condition).  QAOA+-style circuits (cx . rz . cx fused to
+    controlled diagonals, with rz and u1 in the middle) mixed with cz, X-frame flips and non-diagonal gates in between, amplitudes
+    against the oracle for tiles small enough that every placement of control and target occurs."""
+    import networkx as nx
+    rng = np.random.default_rng(100 * n + tile_bits)
+    G = nx.gnm_random_graph(n, 3 * n, seed=n)
+    insts = [("h", (q,), (), None) for q in range(n)]
+    for k, (a, b) in enumerate(G.edges()):
+        g = float(rng.uniform(0, 2 * np.pi))
+        if k % 5 == 0:
+            insts.append(("x", (int(rng.integers(n)),), (), None))
+        if k % 4 == 0:
+            insts.append(("cz", (a, b), (), None))
+        elif k % 4 == 1:
+            insts += [("cx", (b, a), (), None), ("u1", (a,), (g,), None), ("cx", (b, a), (), None)]
+        else:
+            insts += [("rz", (a,), (g / 2,), None), ("rz", (b,), (g / 2,), None), ("cx", (a, b), (), None),
+                      ("rz", (b,), (-g / 2,), None), ("cx", (a, b), (), None)]
+        if k % 7 == 6:
+            insts.append(("ry", (int(rng.integers(n)),), (float(rng.uniform(0, 3)),), None))      # breaks the diagonal block
+    insts += [("rx", (q,), (float(rng.uniform(0, 3)),), None) for q in range(n)]
+    be = _backend(cuda, tile_bits=tile_bits, coalesce_bits=coalesce)
+    prog, auto = be.compile_instructions(n, insts)
+    got = be.run(prog, auto, None)[0].cpu().numpy()
+    want = sv.simulate(n, insts)
+    idx = np.arange(1 << n) ^ prog.flip_mask
+    assert np.abs(got[idx] - want).max() < TOL

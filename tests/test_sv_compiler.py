@@ -146,3 +146,34 @@ def test_unknown_gate_is_an_error():
     from qdc_b200 import _lib
     with pytest.raises(_lib.QdcError):
         eng.lower_instructions([("unitary", (0, 1), (), np.eye(4))])
+
+
+@pytest.mark.parametrize("n,tile_bits,seed", [(6, 3, 0), (8, 4, 1), (9, 12, 2)])
+def test_cx_diagonal_cx_becomes_controlled_diagonals(n, tile_bits, seed):
+    """QAOA+'s phase separator (ansatz/qaoa_plus.py:20-24: rz, cx, rz, cx per edge) is diagonal as a whole: the
+    compiler turns every cx . D . cx into two controlled diagonal gates, so no cx is left in the program, the
+    circuit's unitary is unchanged (replayed from the dumped program against the oracle) -- also with X gates
+    around that put control and target into the flipped frame, and with u1 / z / s / sdg as the diagonal."""
+    rng = np.random.default_rng(seed)
+    import networkx as nx
+    G = nx.gnm_random_graph(n, 2 * n, seed=seed)
+    insts = [("h", (q,), (), None) for q in range(n)]
+    diag = ["rz", "u1", "z", "s", "sdg"]
+    for k, (a, b) in enumerate(G.edges()):
+        g = float(rng.uniform(0, 2 * np.pi))
+        if k % 3 == 0:
+            insts.append(("x", (int(rng.integers(n)),), (), None))        # flips the frame of some qubit
+        insts += [("rz", (a,), (g / 2,), None), ("rz", (b,), (g / 2,), None), ("cx", (a, b), (), None)]
+        name = diag[k % len(diag)]
+        insts.append((name, (b,), (-g / 2,) if name in ("rz", "u1") else (), None))
+        insts.append(("cx", (a, b), (), None))
+    insts += [("rx", (q,), (float(rng.uniform(0, 3)),), None) for q in range(n)]
+    be = _HostBackend(tile_bits=tile_bits, coalesce_bits=min(2, tile_bits))
+    prog, auto = be.compile_instructions(n, insts)
+    recs, _ = eng.lower_instructions(insts)
+    want = sv.simulate(n, insts)
+    got = _replay(n, insts, prog, auto, recs)
+    idx = np.arange(1 << n) ^ prog.flip_mask
+    assert np.abs(got[idx] - want).max() < 1e-12
+    # ops: n H + n RX + per edge 2 rz + 2 controlled diagonals; a surviving cx pair would make it 5 per edge
+    assert prog.n_ops == 2 * n + 4 * G.number_of_edges()
