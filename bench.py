@@ -521,13 +521,12 @@ def run_b200(args):
         return res, res
 
     def step_e2e():
-        A_stage.copy_(A_pin_slab, non_blocking=True)
         if ws > 1 and even_cols:
-            Bt_stage[c_lo:c_lo + c_n].copy_(Bt_pin_shard, non_blocking=True)
-            dist.all_gather_into_tensor(Bt_stage.view(-1), Bt_stage[c_lo:c_lo + c_n].reshape(-1))
+            norm = qdist.stage_sharded_operands(A_pin_slab, Bt_pin_shard, A_stage, Bt_stage, c_lo, scale)
         else:
+            A_stage.copy_(A_pin_slab, non_blocking=True)
             Bt_stage.copy_(Bt_pin, non_blocking=True)
-        norm = qdist.sharded_norm(A_stage, Bt_stage, scale) if ws > 1 else None
+            norm = qdist.sharded_norm(A_stage, Bt_stage, scale) if ws > 1 else None
         res = rc.contract_and_score(A_stage, Bt_stage, tabs_slab, scale=scale, threshold=1e-5, k=k,
                                     method=args.method, slices=args.slices, norm=norm, tol=tol)
         if ws > 1:

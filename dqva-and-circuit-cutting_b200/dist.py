@@ -15,7 +15,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "finish_block", "merge_topk",
-           "sharded_over_parameter_sets", "sharded_norm"]
+           "sharded_over_parameter_sets", "sharded_norm", "stage_sharded_operands", "bind_host_near_gpu"]
 
 
 def init_from_env(backend: str | None = None) -> Tuple[int, int, int]:
@@ -34,7 +34,34 @@ def init_from_env(backend: str | None = None) -> Tuple[int, int, int]:
             torch.cuda.set_device(local_rank)
             kwargs["device_id"] = torch.device("cuda", local_rank)
         dist.init_process_group(backend=backend, rank=rank, world_size=world_size, **kwargs)
+        if backend == "nccl":
+            bind_host_near_gpu(local_rank)
     return rank, world_size, local_rank
+
+
+def bind_host_near_gpu(local_rank: int) -> List[int]:
+    """Pin this process to the host cores NVML reports as local to GPU `local_rank` (its NUMA node), so
+    that the pinned staging buffers allocated afterwards are first-touched on the memory next to that
+    GPU's PCIe root: with 8 ranks copying at once, buffers that all sit on one socket share its memory
+    controllers and the inter-socket link.  Returns the cores chosen ([] = left alone: NVML missing,
+    no GPU, or QDC_BIND_NUMA=0)."""
+    if os.environ.get("QDC_BIND_NUMA", "1") == "0" or not torch.cuda.is_available():
+        return []
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local_rank)
+        bus = f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cores = [64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1]
+        allowed = sorted(set(cores) & os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:                          # placement is an optimisation, never a requirement
+        return []
 
 
 def world() -> Tuple[int, int]:
@@ -67,6 +94,31 @@ def sharded_norm(A_slab: torch.Tensor, Bt: torch.Tensor, scale: float) -> torch.
     if ws > 1:
         dist.all_reduce(col, op=dist.ReduceOp.SUM)
     return (scale * torch.dot(col, Bt.sum(dim=0, dtype=torch.float64))).reshape(1)
+
+
+def stage_sharded_operands(A_pin_slab: torch.Tensor, Bt_pin_shard: torch.Tensor, A_stage: torch.Tensor,
+                           Bt_stage: torch.Tensor, col_lo: int, scale: float) -> torch.Tensor:
+    """Host operands -> device for one rank of a sharded contraction, and the normalisation they imply.
+    Every rank owns a slab of rows of the row operand (pinned `A_pin_slab` -> `A_stage`) and 1 / N of
+    the rows of the column operand (`Bt_pin_shard` -> `Bt_stage[col_lo : col_lo + len]`), so the
+    column operand crosses PCIe once in total; the shards are all-gathered over NVLink while the row
+    slab is still arriving over PCIe (the collective is issued asynchronously right after the shard's
+    copy), and the normalisation comes from the column sums of what each rank received from the host
+    -- its row slab and its column SHARD, not the gathered operand -- in one all-reduce of 2 kdim
+    doubles.  Requires equal shards (the all-gather's layout).  Returns the 1-element float64 norm
+    tensor `recombine.contract_and_score(norm=...)` takes; on return the current stream has waited
+    for both collectives."""
+    n_own = Bt_pin_shard.shape[0]
+    own = Bt_stage[col_lo:col_lo + n_own]
+    own.copy_(Bt_pin_shard, non_blocking=True)
+    gather = dist.all_gather_into_tensor(Bt_stage.view(-1), own.reshape(-1), async_op=True)
+    A_stage.copy_(A_pin_slab, non_blocking=True)
+    cols = torch.cat([A_stage.sum(dim=0, dtype=torch.float64), own.sum(dim=0, dtype=torch.float64)])
+    reduce = dist.all_reduce(cols, op=dist.ReduceOp.SUM, async_op=True)
+    gather.wait()
+    reduce.wait()
+    kd = A_stage.shape[1]
+    return (scale * torch.dot(cols[:kd], cols[kd:])).reshape(1)
 
 
 def merge_topk(cands: Sequence[Tuple[int, float]], k: int) -> List[Tuple[int, float]]:

@@ -116,6 +116,42 @@ def test_sharded_norm_world_size_2():
     assert out[0][0] == out[1][0]
 
 
+def _worker_stage(rank, ws, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
+    import importlib, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    importlib.import_module("dqva-and-circuit-cutting_b200")
+    from qdc_b200 import dist as qd
+    qd.init_from_env(backend="gloo")
+    g = torch.Generator().manual_seed(11)
+    A = torch.randn(38, 16, dtype=torch.float64, generator=g)
+    Bt = torch.randn(24, 16, dtype=torch.float64, generator=g)
+    lo, cnt = qd.row_shard(A.shape[0], rank, ws)
+    c_lo, c_n = qd.row_shard(Bt.shape[0], rank, ws)
+    A_stage = torch.empty(cnt, 16, dtype=torch.float64)
+    Bt_stage = torch.full_like(Bt, float("nan"))
+    norm = qd.stage_sharded_operands(A[lo:lo + cnt], Bt[c_lo:c_lo + c_n], A_stage, Bt_stage, c_lo, 0.25)
+    out[rank] = (float(norm.item()), float(0.25 * (A @ Bt.T).sum().item()),
+                 bool(torch.equal(Bt_stage, Bt)), bool(torch.equal(A_stage, A[lo:lo + cnt])))
+    dist.destroy_process_group()
+
+
+def test_stage_sharded_operands_world_size_2():
+    """Each rank brings its row slab and half of the column operand; afterwards every rank holds the
+    whole column operand (all-gather) and the norm of the whole product (one all-reduce of the
+    column sums of what each rank brought)."""
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_stage, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    for rank in range(ws):
+        got, want, bt_ok, a_ok = out[rank]
+        assert bt_ok and a_ok
+        assert abs(got - want) < 1e-12 * max(1.0, abs(want))
+    assert out[0][0] == out[1][0]
+
+
 def _block_worker(rank, ws, port, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
                       WORLD_SIZE=str(ws), LOCAL_RANK=str(rank))
