@@ -60,6 +60,11 @@ def parse_args():
                          "a-posteriori bounds for these operands (per output and on the MIS cost, "
                          "recombine.i8_error_bounds) stay below --tol")
     ap.add_argument("--tol", type=float, default=1e-10)
+    ap.add_argument("--e2e", default="streamed", choices=["streamed", "plain"],
+                    help="end-to-end leg: streamed = host operands copied in pieces under the contraction "
+                         "(streamed.StreamedContraction, i8 method), plain = both copies, then contract_and_score")
+    ap.add_argument("--e2e-chunks", type=int, nargs=2, default=[2, 4], metavar=("R", "C"),
+                    help="row slabs and column chunks per rank of the streamed e2e leg")
     ap.add_argument("--workload", default="c4", choices=["c4", "c4-circuit", "c5"],
                     help="c4 (default, the headline): contraction + MIS scoring of synthetic fragment tensors at 2^34 "
                          "outputs (BASELINE.json configs[3]); c4-circuit: one whole avg_cost evaluation (sim_with_cutting "
@@ -520,7 +525,21 @@ def run_b200(args):
             return (qdist.finish_block(res, k) if i8 else qdist.finish(res.sums, res.top_x, res.top_p, k)), res
         return res, res
 
+    streamed = None
+    if i8 and args.e2e == "streamed" and (N // (args.e2e_chunks[1] * ws)) * args.e2e_chunks[1] * ws == N:
+        # host operands in pieces, copies under the contraction, norm speculated from the previous step's and
+        # verified (streamed.py); the first warm-up step has no hint and takes the ordinary path
+        from qdc_b200.streamed import StreamedContraction
+        streamed = StreamedContraction(tabs, KDIM, row_chunks=args.e2e_chunks[0], col_chunks=args.e2e_chunks[1], k=k,
+                                       device=dev)
+        hint = {"norm": None}
+
     def step_e2e():
+        if streamed is not None:
+            out = streamed.run(A_pin_slab, Bt_pin, scale=scale, threshold=1e-5, norm_hint=hint["norm"],
+                               slices=args.slices, tol=args.tol)
+            hint["norm"] = out["norm"]
+            return out
         if ws > 1 and even_cols:
             norm = qdist.stage_sharded_operands(A_pin_slab, Bt_pin_shard, A_stage, Bt_stage, c_lo, scale)
         else:
@@ -573,8 +592,10 @@ def run_b200(args):
     if i8:
         chosen = {"slices": last_res.slices, "bounds": last_res.error_bound}
     # the end-to-end leg (host operands, sharded operands at N > 1) must land on the same numbers
-    if ws == 1:
+    if ws == 1 or streamed is not None:
         e2e_sum_p, e2e_cost = last_e2e["sum_p"], last_e2e["sum_pw_indset"]
+        assert streamed is None or (last_e2e["streamed"] and streamed.fallbacks == 1), \
+            f"the streamed e2e leg fell back to the ordinary path {streamed.fallbacks} times"
     else:
         e2e_sum_p, e2e_cost = float(last_e2e[0][0]), float(last_e2e[0][1])
     assert abs(e2e_sum_p - sum_p) < 1e-12 and abs(e2e_cost - cost) < 1e-12, \
@@ -652,7 +673,11 @@ def run_b200(args):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "probs/s", "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(A_pin.numel() * 8 + (1 if even_cols else ws) * Bt_pin.numel() * 8),
-                "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16)},
+                "d2h_bytes_per_step": int(3 * 8 + 8 + k * 16) if streamed is None else
+                int(ws * (streamed.R * streamed.C * (16 + 2 * k) + 2 * KDIM) * 8),
+                "path": "recombine.contract_and_score after both copies" if streamed is None else
+                f"streamed.StreamedContraction: {streamed.R} x {streamed.C} pieces per rank, copies under the contraction, "
+                "norm speculated from the previous step and verified"},
         "gpu_launches": launches,
         "roofline": roofline,
         "result": {"sum_p": sum_p, "avg_cost": -cost, "top": top[:k]},
