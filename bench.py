@@ -63,8 +63,9 @@ def parse_args():
     ap.add_argument("--e2e", default="streamed", choices=["streamed", "plain"],
                     help="end-to-end leg: streamed = host operands copied in pieces under the contraction "
                          "(streamed.StreamedContraction, i8 method), plain = both copies, then contract_and_score")
-    ap.add_argument("--e2e-chunks", type=int, nargs=2, default=[2, 4], metavar=("R", "C"),
-                    help="row slabs and column chunks per rank of the streamed e2e leg")
+    ap.add_argument("--e2e-chunks", type=int, nargs=2, default=None, metavar=("R", "C"),
+                    help="row slabs and column chunks per rank of the streamed e2e leg (default 2 4 on one GPU, "
+                         "2 2 on several: profiles/r2_streamed_e2e.log)")
     ap.add_argument("--workload", default="c4", choices=["c4", "c4-circuit", "c5"],
                     help="c4 (default, the headline): contraction + MIS scoring of synthetic fragment tensors at 2^34 "
                          "outputs (BASELINE.json configs[3]); c4-circuit: one whole avg_cost evaluation (sim_with_cutting "
@@ -526,6 +527,8 @@ def run_b200(args):
         return res, res
 
     streamed = None
+    if args.e2e_chunks is None:
+        args.e2e_chunks = [2, 4] if ws == 1 else [2, 2]
     if i8 and args.e2e == "streamed" and (N // (args.e2e_chunks[1] * ws)) * args.e2e_chunks[1] * ws == N:
         # host operands in pieces, copies under the contraction, norm speculated from the previous step's and
         # verified (streamed.py); the first warm-up step has no hint and takes the ordinary path

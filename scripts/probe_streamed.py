@@ -50,7 +50,7 @@ def main():
 
     G4, G3 = (1, 1, 2, 4), (1, 1, 2)
     configs = [(1, 1), (2, 4), (G4, 4), (G3, 4), (G4, 2), ((1, 3), 4), ((1, 1, 2), 2), ((1, 3, 4), 4), (2, (1, 1, 2)), (2, 8)] \
-        if ws == 1 else [(1, 1), (2, 2), (2, 4), (1, 4), (G3, 2), (1, 2)]
+        if ws == 1 else [(1, 1), (2, 2), (2, 1), (4, 1), (1, 2), (2, 4)]
     for slices in ("auto",):
         for R, C in configs:
             sc = StreamedContraction(tabs, bench.KDIM, row_chunks=R, col_chunks=C, k=8, device=dev)
