@@ -1,5 +1,7 @@
 #!/bin/bash
-N=${1:-2}
 mkdir -p gpurun_out
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 \
-  scripts/probe_streamed.py > gpurun_out/streamed_n$N.log 2>&1; echo "probe rc=$?"; grep -E "^N=|Error|error" gpurun_out/streamed_n$N.log | tail -12
+timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_short.json 2> gpurun_out/bench_short.err; rc=$?; echo "plain rc=$rc"
+[ $rc -eq 0 ] || exit 1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches.csv \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "launch list rc=$?"
+wc -l gpurun_out/launches.csv
