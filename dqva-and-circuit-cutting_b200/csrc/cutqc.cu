@@ -273,6 +273,79 @@ __global__ void __launch_bounds__(MARG_THREADS, LOOP ? 4 : 3) marginal_kernel(co
     (void)Lt;
 }
 
+// The same sum when NO summed (and no fixed-to-one) bit lies between the trailing bits a 16-byte load covers and
+// bit TILE_BITS: every element of a tile then belongs to its own output (summed bits are either added inside the
+// loaded vector or are high bits, i.e. other tiles), so a thread keeps its U loads' outputs in registers across
+// the high summed bits and writes them back itself -- no shared-memory tile, no table phase, no barrier: a
+// streaming pass.  Arithmetic and summation order are those of marginal_kernel (bit-identical results).
+// TZ (trailing summed bits inside a load) is a template parameter: a thread keeps VEC >> TZ sums per load, and with
+// only those live more CTAs fit an SM -- the kernel has nothing but its loads in flight to hide HBM latency with.
+template <typename T, int TZ>
+__global__ void __launch_bounds__(MARG_THREADS, TZ == 0 ? 3 : (TZ == 1 && sizeof(T) == 4 ? 4 : 6)) marginal_direct_kernel(const MargArgs a) {
+    constexpr int tz = TZ;
+    constexpr int VEC = 16 / (int)sizeof(T), U = (1 << TILE_BITS) / (VEC * MARG_THREADS);
+    constexpr int L = TILE_BITS;
+    const int tid = threadIdx.x;
+    const uint64_t low = (1ull << L) - 1ull;
+    const uint64_t keep_hi = a.keep_mask >> L, sum_hi = a.sum_mask >> L, fixed_hi = a.fixed_val >> L;
+    const int n_khi = __popcll(keep_hi), n_shi = __popcll(sum_hi), n_klo = L - tz, n_keep = n_klo + n_khi;
+    const long long n_work = a.n_vec << n_khi;
+    for (long long w = blockIdx.x; w < n_work; w += gridDim.x) {
+        const long long v = w >> n_khi;
+        const uint64_t a_hi = (uint64_t)w & ((1ull << n_khi) - 1ull);
+        const uint64_t x_keep_hi = deposit_bits(a_hi, keep_hi) | fixed_hi;
+        const uint64_t sign = a.sign_masks ? a.sign_masks[v] : 0ull;
+        const uint32_t sign_lo = (uint32_t)(sign & low);
+        const T* src = reinterpret_cast<const T*>(a.in) + (v << a.d);
+        double acc[U][VEC >> TZ];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int k = 0; k < (VEC >> TZ); ++k) acc[u][k] = 0.0;
+        double sgn_k[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) sgn_k[k] = (__popc((uint32_t)(tid * VEC + k) & sign_lo) & 1) ? -1.0 : 1.0;
+        uint64_t x_sum_hi = 0;
+        for (long long m_hi = 0; m_hi < (1ll << n_shi); ++m_hi, x_sum_hi = ((x_sum_hi | ~sum_hi) + 1ull) & sum_hi) {
+            const uint64_t x_hi = x_keep_hi | x_sum_hi;
+            const double hi_sign = (__popcll((long long)((x_hi << L) & sign)) & 1) ? -1.0 : 1.0;
+            const T* t_src = src + (x_hi << L);
+            int4 raw[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) raw[u] = __ldcs(reinterpret_cast<const int4*>(t_src + tid * VEC + u * VEC * MARG_THREADS));
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                T e[VEC];
+                *reinterpret_cast<int4*>(e) = raw[u];
+                double f[VEC];
+                const double it_sign = (__popc((uint32_t)(u * VEC * MARG_THREADS) & sign_lo) & 1) ? -hi_sign : hi_sign;
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) f[k] = (double)e[k] * (sgn_k[k] * it_sign);
+                if constexpr (TZ == 2) acc[u][0] += (f[0] + f[1]) + (f[2 % VEC] + f[3 % VEC]);
+                else if constexpr (TZ == 1) {
+#pragma unroll
+                    for (int k = 0; k < VEC; k += 2) acc[u][k >> 1] += f[k] + f[k + 1];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) acc[u][k] += f[k];
+                }
+            }
+        }
+        double* dst = a.out + (v << n_keep) + ((long long)a_hi << n_klo);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            double* o = dst + ((tid * VEC + u * VEC * MARG_THREADS) >> tz);
+            constexpr int n_out = VEC >> TZ;                           // 4, 2 or 1 consecutive outputs
+            if constexpr (n_out == 1) __stcs(o, acc[u][0]);
+            else {
+#pragma unroll
+                for (int k = 0; k < n_out; k += 2)
+                    __stcs(reinterpret_cast<double2*>(o + k), make_double2(acc[u][k], acc[u][k + 1]));
+            }
+        }
+    }
+}
+
 // true when the tiled kernel applies (enough index bits for a tile, a launchable grid)
 template <typename T>
 bool launch_marginal(const void* in, double* out, const uint64_t* sign_masks, long long n_vec, int d,
@@ -301,6 +374,23 @@ bool launch_marginal(const void* in, double* out, const uint64_t* sign_masks, lo
         while (((1 << n_klo) << p_bits) < MARG_THREADS && p_bits < 5 && p_bits < n_slo) ++p_bits;
         const int need = ((1 << n_klo) << p_bits) / MARG_THREADS;
         acc = need <= 1 ? 1 : (need <= 4 ? 4 : MARG_ACC_MAX);
+    }
+    {
+        // streaming form: all low bits kept except the trailing ones a load adds up (QDC_MARG_DIRECT=0: tiled form)
+        const int vec_bits = sizeof(T) == 4 ? 2 : 1;
+        int tz = 0;
+        while (tz < vec_bits && ((sum_mask >> tz) & 1ull)) ++tz;
+        const uint64_t low = (1ull << TILE_BITS) - 1ull;
+        const char* knob = getenv("QDC_MARG_DIRECT");
+        const bool direct_ok = !(knob && atoi(knob) == 0);
+        if (direct_ok && L == TILE_BITS && ((keep_mask & low) >> tz) == (low >> tz) && (fixed_val & low) == 0 &&
+            (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+            const unsigned grid = (unsigned)(work < (1ll << 30) ? work : (1ll << 30));
+            if (tz == 0) marginal_direct_kernel<T, 0><<<grid, MARG_THREADS, 0, s>>>(a);
+            else if (tz == 1) marginal_direct_kernel<T, 1><<<grid, MARG_THREADS, 0, s>>>(a);
+            else if constexpr (sizeof(T) == 4) marginal_direct_kernel<T, 2><<<grid, MARG_THREADS, 0, s>>>(a);
+            return true;
+        }
     }
     const bool loop = (n_shi == 0 && work > resident) || work >= (1ll << 31);
     const unsigned grid = loop ? (unsigned)resident : (unsigned)work;

@@ -229,3 +229,54 @@ def test_build_int8_contraction_matches_fp64(cuda, out_dtype):
     tol = 1e-10 * scale if out_dtype == "f64" else 2e-7 * scale
     assert got.shape == ref.shape == (1 << sum(actives),)
     assert np.abs(got - ref).max() <= tol, np.abs(got - ref).max() / scale
+
+
+@pytest.mark.parametrize("dtype,d,summed", [
+    ("float32", 14, (0, 1)),            # both summed bits inside one 16-byte load of floats
+    ("float32", 15, (0, 13)),           # one trailing, one above the tile
+    ("float32", 14, (12, 13)),          # high summed bits only: nothing added inside a load
+    ("float64", 14, (0,)),              # doubles: one trailing bit per load
+    ("float64", 15, (0, 12, 14)),
+    ("float32", 13, (1,)),              # bit 1 summed but bit 0 kept: NOT the streaming form (tiled kernel)
+])
+def test_measure_streaming_form_equals_tiled_form(cuda, monkeypatch, dtype, d, summed):
+    """measure / merge when no summed bit lies between the bits a 16-byte load covers and bit 12 go through
+    `marginal_direct_kernel` (no shared-memory tile): against float64 numpy, and bit for bit against the tiled
+    kernel (QDC_MARG_DIRECT=0) -- same arithmetic in the same order."""
+    from qdc_b200.cutqc import kernels
+    rng = np.random.default_rng(d + len(summed))
+    n_inst = 5
+    raw = (rng.random((n_inst, 1 << d)) - 0.3).astype(dtype)
+    keep = ((1 << d) - 1) & ~sum(1 << b for b in summed)
+    signs = [0] + [int(rng.integers(0, 1 << d)) & ~keep | (int(rng.integers(0, 1 << d)) & keep & 0x5) for _ in range(n_inst - 1)]
+    dev = torch.as_tensor(raw, device=cuda)
+    out = {}
+    for knob in ("1", "0"):
+        monkeypatch.setenv("QDC_MARG_DIRECT", knob)
+        out[knob] = kernels.measure(dev, keep, signs).cpu().numpy()
+    assert np.array_equal(out["1"], out["0"])
+    x = np.arange(1 << d)
+    e = np.zeros_like(x)
+    for j, q in enumerate([q for q in range(d) if (keep >> q) & 1]):
+        e |= ((x >> q) & 1) << j
+    for i in range(n_inst):
+        sgn = 1 - 2 * (np.array([bin(int(v) & signs[i]).count("1") for v in x]) & 1)
+        want = np.bincount(e, weights=raw[i].astype(np.float64) * sgn, minlength=1 << bin(keep).count("1"))
+        assert np.abs(out["1"][i] - want).max() < 1e-10
+
+
+def test_merge_streaming_form(cuda, monkeypatch):
+    """merge with the merged (summed) qubits at the top and the bottom of the index and no zoomed qubit."""
+    from qdc_b200.cutqc import kernels
+    rng = np.random.default_rng(9)
+    n_eff = 15
+    states = [-2, -1, -2] + [-1] * 11 + [-2]               # MSB first: bits 14, 12 and 0 are merged
+    vec = rng.random((3, 1 << n_eff))
+    dev = torch.as_tensor(vec, device=cuda)
+    out = {}
+    for knob in ("1", "0"):
+        monkeypatch.setenv("QDC_MARG_DIRECT", knob)
+        out[knob] = kernels.merge(dev, states).cpu().numpy()
+    assert np.array_equal(out["1"], out["0"])
+    want = vec.reshape(3, 2, 2, 2, 1 << 11, 2).sum(axis=(1, 3, 5)).reshape(3, -1)
+    assert np.abs(out["1"] - want).max() < 1e-12
