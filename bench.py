@@ -523,7 +523,9 @@ def run_b200(args):
                                     row_lo=row_lo, n_rows=n_rows, kernel_events=kernel_events,
                                     method=args.method, slices=args.slices, tol=tol)
         if ws > 1:
-            return (qdist.finish_block(res, k) if i8 else qdist.finish(res.sums, res.top_x, res.top_p, k)), res
+            # the ranks' blocks are all-gathered every step; like the single-GPU step (`res`), the host reads
+            # the gathered result after the timed region only
+            return (qdist.finish_block(res, k, wait=False) if i8 else qdist.finish(res.sums, res.top_x, res.top_p, k)), res
         return res, res
 
     streamed = None
@@ -588,7 +590,7 @@ def run_b200(args):
         sum_p, cost = final["sum_p"], final["sum_pw_indset"]
         top = final["top"]
     else:
-        sums, top = last_dev
+        sums, top = last_dev.get() if i8 else last_dev
         sum_p, cost = float(sums[0]), float(sums[1])
     assert abs(sum_p - 1.0) < 1e-9, f"distribution does not sum to 1: {sum_p}"
     chosen = {}

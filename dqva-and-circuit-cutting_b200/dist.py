@@ -14,7 +14,7 @@ from typing import List, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-__all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "finish_block", "merge_topk",
+__all__ = ["init_from_env", "world", "row_shard", "round_robin", "finish", "finish_block", "PendingFinish", "merge_topk",
            "sharded_over_parameter_sets", "sharded_norm", "stage_sharded_operands", "bind_host_near_gpu"]
 
 
@@ -150,29 +150,42 @@ def finish(sums: torch.Tensor, top_x: torch.Tensor, top_p: torch.Tensor, k: int)
     return total, merge_topk(cands, k)
 
 
-def finish_block(res, k: int):
+class PendingFinish:
+    """`finish_block(..., wait=False)`: the all-gather has been issued, nothing has been read back.  `get()`
+    copies the gathered blocks to the host (the synchronisation) and returns what `finish_block` returns."""
+
+    def __init__(self, gathered: torch.Tensor, ws: int, k: int, cand_cap: int):
+        self.gathered, self.ws, self.k, self.cand_cap = gathered, ws, k, cand_cap
+
+    def get(self):
+        import numpy as np
+        h = self.gathered.cpu().numpy().reshape(self.ws, -1)
+        k, cands = self.k, []
+        for r in range(self.ws):
+            xs = h[r, 16:16 + k].view(np.int64)
+            ps = h[r, 16 + k:16 + 2 * k]
+            n_cand = int(h[r, 7:8].view(np.int64)[0])
+            if n_cand > self.cand_cap:
+                raise RuntimeError(f"rank {r}: top-k candidate buffer overflow ({n_cand} > {self.cand_cap})")
+            cands += [(int(x), float(p)) for x, p in zip(xs, ps) if x != -1]
+        return h[:, 0:3].sum(axis=0), merge_topk(cands, k)
+
+
+def finish_block(res, k: int, wait: bool = True):
     """`finish` for a `ScoreResult` of the int8 path, whose sums, candidate count and top-k live in
     ONE device block: the block itself is all-gathered (indices travel as their 64-bit patterns) and
     read back once -- no packing kernels.  Returns (global sums as a numpy array[3], global top-k
-    list) on every rank."""
-    import numpy as np
+    list) on every rank; with wait=False a `PendingFinish` whose `get()` does the read-back, so a loop
+    of evaluations whose results are only looked at afterwards never stalls the device on the host."""
     rank, ws = world()
     block = res.block
     if ws == 1:
-        h = block.cpu().numpy()[None, :]
+        gathered = block
     else:
         gathered = torch.empty(ws * block.numel(), dtype=block.dtype, device=block.device)
         dist.all_gather_into_tensor(gathered, block)
-        h = gathered.cpu().numpy().reshape(ws, -1)
-    cands = []
-    for r in range(ws):
-        xs = h[r, 16:16 + k].view(np.int64)
-        ps = h[r, 16 + k:16 + 2 * k]
-        n_cand = int(h[r, 7:8].view(np.int64)[0])
-        if n_cand > res.cand_cap:
-            raise RuntimeError(f"rank {r}: top-k candidate buffer overflow ({n_cand} > {res.cand_cap})")
-        cands += [(int(x), float(p)) for x, p in zip(xs, ps) if x != -1]
-    return h[:, 0:3].sum(axis=0), merge_topk(cands, k)
+    pending = PendingFinish(gathered, ws, k, res.cand_cap)
+    return pending.get() if wait else pending
 
 
 def sharded_over_parameter_sets(fn, table, device=None):

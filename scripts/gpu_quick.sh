@@ -1,3 +1,7 @@
 #!/bin/bash
+N=${1:-2}
 mkdir -p gpurun_out
-for g in 0 6 12 24; do echo "grid per SM $g"; QDC_MARG_DIRECT_GRID=$g timeout 600 python scripts/time_cutqc.py 2>&1 | grep -E "measure" | tail -3; done
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
+   bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench N=$N rc=$?"
+tail -n 1 gpurun_out/bench_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e'], d['roofline']['kernel_ms'])"
+tail -c 600 gpurun_out/bench_n$N.err

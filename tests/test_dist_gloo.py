@@ -172,6 +172,9 @@ def _block_worker(rank, ws, port, out):
     res = rc.ScoreResult(block[0:3], block[16:16 + k].view(torch.int64), block[16 + k:], block[7:8].view(torch.int64),
                          cand_cap=8, block=block)
     total, top = qd.finish_block(res, k)
+    pending = qd.finish_block(res, k, wait=False)              # read-back deferred: same answer
+    total2, top2 = pending.get()
+    assert total2.tolist() == total.tolist() and top2 == top
     out[rank] = (total.tolist(), top)
     dist.destroy_process_group()
 
