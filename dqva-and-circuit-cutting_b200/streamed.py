@@ -62,9 +62,10 @@ class StreamedContraction:
     """Reusable plan (staging buffers, sliced-operand buffers, per-pair tables, streams, events) for
     `P~ = scale * A @ Bt.T` scored on the fly, with A [M, kdim] and Bt [N, kdim] float64 in PINNED
     host memory.  `tables`: `recombine.build_tables` for the whole distribution.  row_chunks /
-    col_chunks: R and C above as counts of equal pieces, or sequences of relative piece sizes such as (1, 1, 2).  In a process group every rank owns rows `dist.row_shard(M, rank, ws)`
-    (pass the rank's slab of the pinned row operand to `run`, and the WHOLE pinned column operand:
-    the rank reads only its 1 / N of every chunk)."""
+    col_chunks: R and C above as counts of equal pieces, or sequences of relative piece sizes such
+    as (1, 1, 2).  In a process group every rank owns rows `dist.row_shard(M, rank, ws)` (pass the
+    rank's slab of the pinned row operand to `run`, and the WHOLE pinned column operand: the rank
+    reads only its 1 / N of every chunk)."""
 
     def __init__(self, tables: rc.MisTables, kdim: int, *, row_chunks=2, col_chunks=4, k: int = 1, device=None):
         self.tables = tables
@@ -94,12 +95,12 @@ class StreamedContraction:
                                      t.row_forb[self.row_lo:self.row_lo + self.n_rows].contiguous(),
                                      t.row_wok[self.row_lo:self.row_lo + self.n_rows].contiguous(),
                                      t.col_x, t.col_wok, t.bitpos, t.node_mask)
-        lib = rc._lib.load()
+        lib = _lib.load()
 
         def prepared(n):
             nb = int(lib.qdc_i8_operand_bytes(n, kdim, 6))
             if nb <= 0:
-                raise rc._lib.QdcError(f"int8 contraction: unsupported piece shape ({n}, {kdim})")
+                raise _lib.QdcError(f"int8 contraction: unsupported piece shape ({n}, {kdim})")
             raw = torch.empty(nb + 256, dtype=torch.uint8, device=self.dev)
             off = (-raw.data_ptr()) % 256
             return raw[off:off + nb]
