@@ -1,10 +1,4 @@
 #!/bin/bash
-N=${1:-4}
 mkdir -p gpurun_out
-timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_short.json 2> gpurun_out/bench_short.err; echo "N=1 rc=$?"
-tail -n 1 gpurun_out/bench_short.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e'])"
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
-   bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench N=$N rc=$?"
-tail -n 1 gpurun_out/bench_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e'], d['roofline']['kernel_ms'])"
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
-   bench.py --impl reference --gpus $N --steps 1 --warmup 1 2>/dev/null | tail -n 1 | cut -c1-200
+timeout 600 python -m pytest tests/test_gpu_c4_full_size.py -m gpu -x -q > gpurun_out/q_tests.log 2>&1; echo "tests rc=$?"
+tail -25 gpurun_out/q_tests.log
