@@ -39,7 +39,7 @@ from . import _lib
 from . import dist as qdist
 from . import recombine as rc
 
-__all__ = ["StreamedContraction", "SLACK"]
+__all__ = ["StreamedContraction", "combine_blocks", "SLACK"]
 
 SLACK = 0.5          # candidates are flagged against threshold * SLACK; the hint may overshoot the norm by 1 / SLACK
 
@@ -56,6 +56,32 @@ def _splits(n: int, parts, align: int = 1) -> List[Tuple[int, int]]:
         cuts.append(n * acc // total // align * align)
     cuts.append(n)
     return [(a, b - a) for a, b in zip(cuts, cuts[1:])]
+
+
+def combine_blocks(blocks: np.ndarray, caps, norm_hint: float, threshold: float, k: int) -> dict:
+    """Host side of a speculated step: `blocks[i]` is the result block of one (slab, chunk) pair of one rank
+    (csrc/i8_layout.cuh: [0..2] sums, [4] slices, [7] candidates, [10] lost, [16..] top-k indices then
+    probabilities), all computed with 1 / norm_hint and threshold * SLACK; caps[i] its candidate capacity.
+    Every pair's "sum p" is scale / hint x <column sums of its slab, column sums of its chunk>, so over all pairs
+    they add up to norm / hint: the true norm needs no extra pass.  Returns the evaluation's dict with
+    "streamed": True, or {"streamed": False, "norm": norm} when the speculation has to be refused (norm below
+    SLACK x hint: candidates may have been missed; or a pair ran out of candidate room)."""
+    norm = float(norm_hint * blocks[:, 0].sum())
+    if not (norm >= SLACK * norm_hint):
+        return {"streamed": False, "norm": norm}
+    f = norm_hint / norm
+    cands, n_cand, used = [], 0, []
+    for b, cap in zip(blocks, caps):
+        n_b = int(b[7:8].view(np.int64)[0])
+        if int(b[10:11].view(np.int64)[0]) > 0 or n_b > cap:
+            return {"streamed": False, "norm": norm}
+        n_cand += n_b
+        used.append(int(b[4]))
+        xs, ps = b[16:16 + k].view(np.int64), b[16 + k:16 + 2 * k]
+        cands += [(int(x), float(p) * f) for x, p in zip(xs, ps) if x != -1 and float(p) * f > threshold]
+    sums = blocks[:, 0:3].sum(axis=0) * f
+    return {"sum_p": float(sums[0]), "sum_pw_indset": float(sums[1]), "sum_pw": float(sums[2]),
+            "top": qdist.merge_topk(cands, k), "n_candidates": n_cand, "norm": norm, "streamed": True, "slices": used}
 
 
 class StreamedContraction:
@@ -241,25 +267,10 @@ class StreamedContraction:
         if not speculate:
             cols = h.reshape(self.ws, 2, self.kdim).sum(axis=0)
             return self._unstreamed(scale, threshold, slices, tol, float(scale * np.dot(cols[0], cols[1])))
-        # every pair's sum_p is scale / hint x <column sums of its slab, column sums of its chunk> (the moments,
-        # not the tensor cores): over all pairs of all ranks they add up to norm / hint
-        blocks = h.reshape(-1, n_blk)
-        norm = float(norm_hint * blocks[:, 0].sum())
-        if not (norm >= SLACK * norm_hint):
-            return self._unstreamed(scale, threshold, slices, tol, norm)
-        f = norm_hint / norm
-        cands, n_cand, used = [], 0, []
-        for b, cap in zip(blocks, caps * self.ws):
-            if int(b[10:11].view(np.int64)[0]) > 0 or int(b[7:8].view(np.int64)[0]) > cap:
-                return self._unstreamed(scale, threshold, slices, tol, norm)
-            n_cand += int(b[7:8].view(np.int64)[0])
-            used.append(int(b[4]))
-            xs, ps = b[16:16 + k].view(np.int64), b[16 + k:16 + 2 * k]
-            cands += [(int(x), float(p) * f) for x, p in zip(xs, ps) if x != -1 and float(p) * f > threshold]
-        sums = blocks[:, 0:3].sum(axis=0) * f
-        return {"sum_p": float(sums[0]), "sum_pw_indset": float(sums[1]), "sum_pw": float(sums[2]),
-                "top": qdist.merge_topk(cands, k), "n_candidates": n_cand, "norm": norm, "streamed": True,
-                "slices": used}
+        out = combine_blocks(h.reshape(-1, n_blk), caps * self.ws, norm_hint, threshold, k)
+        if out["streamed"]:
+            return out
+        return self._unstreamed(scale, threshold, slices, tol, out["norm"])
 
     def _unstreamed(self, scale, threshold, slices, tol, norm) -> dict:
         """The operands are in HBM; the ordinary path with the norm just computed."""

@@ -235,3 +235,37 @@ def test_top_strings_merges_ancilla_partners_before_threshold_and_cutoff():
     d.score = Score(full[:1], 5)
     d.P = None                                            # nothing stored: best effort from the fused list
     assert mis.top_strings(d, G, cutoff=1) == [("010", 1)]
+
+
+def test_streamed_combine_blocks_rescales_and_refilters():
+    """Host side of streamed.StreamedContraction: pair blocks computed with a norm HINT are rescaled to the true
+    norm (hint x total of the pairs' sum p), candidates re-tested against the exact threshold, and a hint more
+    than twice the norm (or a pair out of candidate room) refuses the speculation."""
+    import numpy as np
+    from qdc_b200.streamed import combine_blocks, SLACK
+    k, thr, hint, true = 2, 0.1, 2.0, 1.6                        # true norm = 0.8 x hint
+    def block(sum_p, cost, top, n_cand=2, lost=0, slices=5):
+        b = np.zeros(16 + 2 * k)
+        b[0:3] = [sum_p, cost, 2 * cost]
+        b[4] = slices
+        b[7:8].view(np.int64)[0] = n_cand
+        b[10:11].view(np.int64)[0] = lost
+        xs = [x for x, _ in top] + [-1] * (k - len(top))
+        ps = [p for _, p in top] + [float("-inf")] * (k - len(top))
+        b[16:16 + k].view(np.int64)[:] = xs
+        b[16 + k:] = ps
+        return b
+    # probabilities as the kernels report them (divided by the hint): exact value = reported x hint / true
+    blocks = np.stack([block(0.5, 0.05, [(7, 0.30), (3, 0.09)]), block(0.3, 0.01, [(9, 0.07)], n_cand=1, slices=4)])
+    out = combine_blocks(blocks, [8, 8], hint, thr, k)
+    f = hint / true
+    assert out["streamed"] and abs(out["norm"] - true) < 1e-15
+    assert abs(out["sum_p"] - 1.0) < 1e-15 and abs(out["sum_pw_indset"] - 0.06 * f) < 1e-15
+    assert [x for x, _ in out["top"]] == [7, 3]                  # 0.09 f = 0.1125 > thr stays, 0.07 f = 0.0875 goes
+    assert abs(out["top"][0][1] - 0.30 * f) < 1e-15 and out["slices"] == [5, 4] and out["n_candidates"] == 3
+    low = np.stack([block(0.25, 0.02, []), block(0.15, 0.01, [])])                       # pairs add up to 0.4 = norm / hint
+    assert combine_blocks(low, [8, 8], hint, thr, k) == {"streamed": False, "norm": 0.8}   # norm < SLACK x hint
+    assert SLACK == 0.5
+    assert combine_blocks(blocks, [1, 8], hint, thr, k)["streamed"] is False            # candidate room exceeded
+    lost = np.stack([block(0.8, 0.0, [], n_cand=0, lost=3)])
+    assert combine_blocks(lost, [8], hint, thr, k) == {"streamed": False, "norm": 1.6}
