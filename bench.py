@@ -11,7 +11,9 @@ parameter vector on the synthetic 2-fragment, 17+17-output-qubit, K=4-cut worklo
 
   value : device-timed whole-job throughput, operands already resident in HBM
   e2e   : the same step through the public Python API with HOST operands (pinned -> device copy
-          and device -> host read of the result inside the timed region)
+          and device -> host read of the result inside the timed region, every step); by default
+          `streamed.StreamedContraction`, which copies the operands in pieces under the contraction
+          (--e2e plain: both copies, then `recombine.contract_and_score`)
 
 Run:  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
       (N > 1: launched under torchrun, one rank per GPU; rows of the row operand = bitstring
