@@ -29,17 +29,6 @@ def _setup(cuda, rb=11, cb=10, kdim=256, seed=3):
     return A, Bt, tabs, thr
 
 
-def test_piece_boundaries():
-    from qdc_b200.streamed import _splits
-    assert _splits(64, (1, 1, 2, 4)) == [(0, 8), (8, 8), (16, 16), (32, 32)]
-    assert _splits(64, 4) == [(0, 16), (16, 16), (32, 16), (48, 16)]
-    assert _splits(10, 2) == [(0, 5), (5, 5)]
-    assert [n % 8 for _, n in _splits(1 << 17, (1, 1, 2, 4), align=8)] == [0] * 4
-    for n, parts in [(100, (1, 1, 2)), (7, 4), (1 << 17, (1, 1, 2, 4, 8))]:
-        sp = _splits(n, parts)
-        assert sp[0][0] == 0 and sum(c for _, c in sp) == n and all(a + c == b for (a, c), (b, _) in zip(sp, sp[1:]))
-
-
 @pytest.mark.parametrize("chunks", [(4, 4), (1, 1), ((1, 1, 2), 2)])
 def test_streamed_equals_unstreamed(cuda, chunks):
     from qdc_b200 import recombine as rc

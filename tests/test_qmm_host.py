@@ -269,3 +269,23 @@ def test_streamed_combine_blocks_rescales_and_refilters():
     assert combine_blocks(blocks, [1, 8], hint, thr, k)["streamed"] is False            # candidate room exceeded
     lost = np.stack([block(0.8, 0.0, [], n_cand=0, lost=3)])
     assert combine_blocks(lost, [8], hint, thr, k) == {"streamed": False, "norm": 1.6}
+
+
+def test_piece_boundaries():
+    from qdc_b200.streamed import _splits
+    assert _splits(64, (1, 1, 2, 4)) == [(0, 8), (8, 8), (16, 16), (32, 32)]
+    assert _splits(64, 4) == [(0, 16), (16, 16), (32, 16), (48, 16)]
+    assert _splits(10, 2) == [(0, 5), (5, 5)]
+    assert [n % 8 for _, n in _splits(1 << 17, (1, 1, 2, 4), align=8)] == [0] * 4
+    for n, parts in [(100, (1, 1, 2)), (7, 4), (1 << 17, (1, 1, 2, 4, 8))]:
+        sp = _splits(n, parts)
+        assert sp[0][0] == 0 and sum(c for _, c in sp) == n and all(a + c == b for (a, c), (b, _) in zip(sp, sp[1:]))
+
+
+def test_bind_host_near_gpu_is_a_no_op_without_a_gpu(monkeypatch):
+    from qdc_b200 import dist as qd
+    import torch
+    if not torch.cuda.is_available():
+        assert qd.bind_host_near_gpu(0) == []
+    monkeypatch.setenv("QDC_BIND_NUMA", "0")
+    assert qd.bind_host_near_gpu(0) == []
