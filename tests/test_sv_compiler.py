@@ -177,3 +177,45 @@ def test_cx_diagonal_cx_becomes_controlled_diagonals(n, tile_bits, seed):
     assert np.abs(got[idx] - want).max() < 1e-12
     # ops: n H + n RX + per edge 2 rz + 2 controlled diagonals; a surviving cx pair would make it 5 per edge
     assert prog.n_ops == 2 * n + 4 * G.number_of_edges()
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_compiler_fuzz_mixed_circuits(seed):
+    """Random circuits that mix everything the compiler rewrites -- X gates (frame), cx . D . cx sandwiches (some broken
+    by a gate in between, some with control and target swapped between the two cx, which must NOT fuse), faithful
+    partial mixers on an ancilla, runs of diagonal gates with and without controls, and plain random gates --
+    over 2 to 3 layers, random width and tile size: the replayed program equals the oracle on the original list."""
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(4, 11))
+    tile_bits = int(rng.integers(1, n + 1))
+    anc = n - 1
+    insts = []
+    for layer in range(int(rng.integers(2, 4))):
+        for _ in range(int(rng.integers(3, 9))):
+            r = rng.random()
+            a, b = (int(v) for v in rng.choice(n - 1, size=2, replace=False))
+            g = float(rng.uniform(0, 2 * np.pi))
+            if r < 0.35:                                        # a proper sandwich
+                name = ["rz", "u1", "z", "s", "t"][int(rng.integers(5))]
+                insts += [("cx", (a, b), (), None), (name, (b,), (g,) if name in ("rz", "u1") else (), None),
+                          ("cx", (a, b), (), None)]
+            elif r < 0.45:                                      # broken sandwich: a non-diagonal gate in the middle
+                insts += [("cx", (a, b), (), None), ("rz", (b,), (g,), None), ("h", (b,), (), None), ("cx", (a, b), (), None)]
+            elif r < 0.55:                                      # swapped control / target: not a sandwich
+                insts += [("cx", (a, b), (), None), ("rz", (b,), (g,), None), ("cx", (b, a), (), None)]
+            elif r < 0.7 and n >= 5:                            # the reference's partial mixer through the ancilla
+                q = int(rng.integers(n - 1))
+                nb = [int(v) for v in rng.choice([k for k in range(n - 1) if k != q],
+                                                 size=int(rng.integers(1, min(3, n - 2) + 1)), replace=False)]
+                _faithful_mixer(insts, nb, anc, q, g)
+            elif r < 0.85:                                      # diagonal run with a controlled member
+                insts += [("rz", (a,), (g,), None), ("cz", (a, b), (), None), ("u1", (b,), (g / 3,), None), ("x", (a,), (), None)]
+            else:
+                insts += _random_circuit(rng, n - 1, 4)
+    be = _HostBackend(tile_bits=tile_bits, coalesce_bits=min(2, tile_bits))
+    prog, auto = be.compile_instructions(n, insts)
+    recs, _ = eng.lower_instructions(insts)
+    want = sv.simulate(n, insts)
+    got = _replay(n, insts, prog, auto, recs)
+    idx = np.arange(1 << n) ^ prog.flip_mask
+    assert np.abs(got[idx] - want).max() < 1e-12
